@@ -1,0 +1,694 @@
+// engine.cu — host side of librpe_b200.so: the C ABI of include/rpe.h, workspace management,
+// pyramid geometry / tap tables, and the launch sequence of the batched hot path
+//   H2D -> pyramid -> FAST+NMS -> retainBest/Harris -> blur -> orientation+rBRIEF
+//       -> Hamming k-NN -> cross-check|ratio + stable sort + cut -> 5-pt RANSAC -> recoverPose -> D2H
+// on one CUDA stream, with no host synchronisation between stages.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "rpe_device.cuh"
+
+using namespace rpe;
+
+static thread_local std::string g_last_error;
+
+#define RPE_CK(call)                                                                          \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      char buf_[512];                                                                         \
+      snprintf(buf_, sizeof buf_, "%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      g_last_error = buf_;                                                                    \
+      return RPE_ERR_CUDA;                                                                    \
+    }                                                                                         \
+  } while (0)
+
+static int fail(int code, const char* msg) {
+  g_last_error = msg;
+  return code;
+}
+
+static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
+static inline int pow2_ge(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+struct Geometry {
+  OrbGeom g;
+  std::vector<int2> taps;   // host copy
+  int2* d_taps = nullptr;
+};
+
+struct rpe_handle {
+  rpe_config cfg;
+  int device = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  int NI = 0, NP = 0;
+  int kp_stride = 0, cand_stride = 0, mcap = 0, sort_cap_orb = 0, sort_cap_match = 0;
+  size_t pyr_stride = 0;
+  OrbBuffers ob{};
+  MatchBuffers mb{};
+  GeomBuffers gb{};
+  double* dK = nullptr;
+  std::vector<void*> allocs;
+  std::map<std::pair<int, int>, Geometry> geoms;
+  const Geometry* last_geom = nullptr;
+  int last_pairs = 0;
+  // pinned host staging for results: R(9) t(3) euler(3) doubles, status + 4 info ints, K
+  double* h_out_d = nullptr;
+  int32_t* h_out_i = nullptr;
+  double* h_K = nullptr;
+  // profiling
+  bool profiling = false;
+  cudaEvent_t ev[RPE_T_COUNT + 1] = {};
+  float ms[RPE_T_COUNT] = {};
+  int launches[RPE_T_COUNT] = {};
+};
+
+// ---------------------------------------------------------------------------------------------
+// Pyramid geometry exactly as ORB_Impl: f32 scale factor, f32 level scales,
+// cvRound level sizes, f32 per-level quotas; plus INTER_LINEAR_EXACT tap tables in f64.
+static void compute_levels(const rpe_config& c, int W, int H, int* w, int* h, float* scale, int* quota) {
+  const double sf = (double)c.scale_factor;
+  for (int l = 0; l < c.nlevels; ++l) {
+    scale[l] = (float)std::pow(sf, (double)l);
+    w[l] = (int)lrintf((float)W / scale[l]);
+    h[l] = (int)lrintf((float)H / scale[l]);
+  }
+  const float factor = (float)(1.0 / sf);
+  float nd = c.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)c.nlevels));
+  int sum = 0;
+  for (int l = 0; l < c.nlevels - 1; ++l) {
+    quota[l] = (int)lrintf(nd);
+    sum += quota[l];
+    nd *= factor;
+  }
+  quota[c.nlevels - 1] = std::max(c.nfeatures - sum, 0);
+}
+
+static void linear_exact_taps(int src, int dst, std::vector<int2>& out) {
+  const double scale = 1.0 / ((double)dst / (double)src);
+  for (int d = 0; d < dst; ++d) {
+    const double f = scale * (d + 0.5) - 0.5;
+    int i = (int)std::floor(f);
+    int c1 = (int)lrint((f - i) * 256.0);
+    if (i < 0 || src <= 1) { i = 0; c1 = 0; }
+    else if (i >= src - 1) { i = src - 1; c1 = 0; }
+    out.push_back(make_int2(i, c1));
+  }
+}
+
+static int kp_cap_of(int quota) { return quota + std::max(64, quota / 4); }
+static int cand_cap_of(int w, int h) { return std::max(1024, (w * h) / 16); }
+
+static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
+  OrbGeom& g = G.g;
+  memset(&g, 0, sizeof g);
+  int w[RPE_MAX_LEVELS], h[RPE_MAX_LEVELS], quota[RPE_MAX_LEVELS];
+  float scale[RPE_MAX_LEVELS];
+  compute_levels(c, W, H, w, h, scale, quota);
+  g.nlevels = c.nlevels;
+  g.fast_threshold = c.fast_threshold;
+  size_t off = 0;
+  int cand_off = 0, kp_off = 0, tile0 = 0, max_kp_cap = 1;
+  G.taps.clear();
+  for (int l = 0; l < c.nlevels; ++l) {
+    LevelGeom& L = g.lv[l];
+    L.w = w[l]; L.h = h[l]; L.pitch = align_up(std::max(w[l], 1), 16);
+    L.quota = quota[l];
+    L.scale = scale[l];
+    L.off = (uint32_t)off;
+    off += (size_t)align_up(L.pitch * std::max(L.h, 1), 256);
+    L.cand_off = cand_off; L.cand_cap = cand_cap_of(L.w, L.h); cand_off += L.cand_cap;
+    L.kp_off = kp_off; L.kp_cap = kp_cap_of(L.quota); kp_off += L.kp_cap;
+    max_kp_cap = std::max(max_kp_cap, L.kp_cap);
+    L.tiles_x = (L.w + kTileW - 1) / kTileW; L.tiles_y = (L.h + kTileH - 1) / kTileH;
+    L.tile0 = tile0; tile0 += L.tiles_x * L.tiles_y;
+    if (l > 0) {
+      L.xtab = (int)G.taps.size(); linear_exact_taps(w[l - 1], w[l], G.taps);
+      L.ytab = (int)G.taps.size(); linear_exact_taps(h[l - 1], h[l], G.taps);
+    }
+  }
+  g.total_tiles = tile0;
+  g.cand_stride = cand_off;
+  g.kp_stride = kp_off;
+  g.sort_cap = pow2_ge(max_kp_cap);
+  g.pyr_stride = off;
+}
+
+template <typename T>
+static int dalloc(rpe_handle* h, T** p, size_t n) {
+  void* q = nullptr;
+  RPE_CK(cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T)));
+  RPE_CK(cudaMemset(q, 0, std::max<size_t>(n, 1) * sizeof(T)));
+  h->allocs.push_back(q);
+  *p = (T*)q;
+  return RPE_OK;
+}
+#define RPE_TRY(x)            \
+  do {                        \
+    int r_ = (x);             \
+    if (r_ != RPE_OK) return r_; \
+  } while (0)
+
+static int get_geometry(rpe_handle* h, int W, int H, const Geometry** out) {
+  auto key = std::make_pair(W, H);
+  auto it = h->geoms.find(key);
+  if (it == h->geoms.end()) {
+    Geometry G;
+    build_geometry(h->cfg, W, H, G);
+    // strides are those of the handle (max image), so every slot has the same footprint
+    if (G.g.pyr_stride > h->pyr_stride || G.g.cand_stride > h->cand_stride) return fail(RPE_ERR_CAPACITY, "image larger than handle capacity");
+    G.g.pyr_stride = h->pyr_stride;
+    G.g.cand_stride = h->cand_stride;
+    G.g.kp_stride = h->kp_stride;
+    G.g.sort_cap = h->sort_cap_orb;
+    RPE_CK(cudaMalloc((void**)&G.d_taps, std::max<size_t>(G.taps.size(), 1) * sizeof(int2)));
+    RPE_CK(cudaMemcpy(G.d_taps, G.taps.data(), G.taps.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    it = h->geoms.emplace(key, std::move(G)).first;
+  }
+  *out = &it->second;
+  return RPE_OK;
+}
+
+extern "C" {
+
+int rpe_abi_version(void) { return RPE_ABI_VERSION; }
+const char* rpe_last_error(void) { return g_last_error.c_str(); }
+
+void rpe_default_config(rpe_config* c) {
+  memset(c, 0, sizeof *c);
+  c->max_width = 640; c->max_height = 480; c->max_pairs = 1;
+  c->nfeatures = 4000; c->nlevels = 12; c->scale_factor = 1.1f; c->fast_threshold = 15;
+  c->match_mode = RPE_MATCH_CROSSCHECK; c->ratio = 0.75; c->max_matches = 500;
+  c->ransac_prob = 0.999; c->ransac_threshold = 1.0; c->ransac_max_iters = 1000;
+  c->euler_convention = RPE_EULER_YUP;
+}
+
+int rpe_create(const rpe_config* cfg, int device, rpe_handle** out) {
+  if (!cfg || !out) return fail(RPE_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (cfg->nlevels < 1 || cfg->nlevels > RPE_MAX_LEVELS || cfg->nfeatures < 1 || cfg->max_pairs < 1 ||
+      cfg->max_width < 1 || cfg->max_height < 1 || cfg->max_width > RPE_MAX_DIM || cfg->max_height > RPE_MAX_DIM ||
+      !(cfg->scale_factor > 1.0f) || cfg->fast_threshold < 1 || cfg->fast_threshold > 254 ||
+      (cfg->match_mode != RPE_MATCH_CROSSCHECK && cfg->match_mode != RPE_MATCH_RATIO) || cfg->ransac_max_iters < 1)
+    return fail(RPE_ERR_INVALID, "invalid rpe_config");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || device < 0 || device >= ndev)
+    return fail(RPE_ERR_NO_DEVICE, "no usable CUDA device (this library has no CPU fallback)");
+  cudaDeviceProp prop;
+  RPE_CK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(RPE_ERR_NO_DEVICE, "device is not sm_100 (B200); kernels are built for sm_100a only");
+  RPE_CK(cudaSetDevice(device));
+  rpe_handle* h = new rpe_handle();
+  h->cfg = *cfg;
+  h->device = device;
+  h->NP = cfg->max_pairs;
+  h->NI = 2 * cfg->max_pairs;
+  Geometry G;
+  build_geometry(*cfg, cfg->max_width, cfg->max_height, G);
+  // a narrower-but-taller image can need more pyramid bytes through pitch rounding: pad a little
+  h->pyr_stride = G.g.pyr_stride + 4096;
+  h->cand_stride = G.g.cand_stride + 1024 * cfg->nlevels;
+  h->kp_stride = G.g.kp_stride;
+  h->sort_cap_orb = G.g.sort_cap;
+  if (h->kp_stride >= (1 << 20)) { delete h; return fail(RPE_ERR_INVALID, "nfeatures too large (index packs in 20 bits)"); }
+  h->mcap = cfg->max_matches > 0 ? std::min(cfg->max_matches, h->kp_stride) : h->kp_stride;
+  h->sort_cap_match = pow2_ge(h->mcap);
+  if ((size_t)h->sort_cap_match * 4 > 200 * 1024 || (size_t)h->sort_cap_orb * 8 > 200 * 1024) {
+    delete h;
+    return fail(RPE_ERR_INVALID, "max_matches / nfeatures exceed the shared-memory sort capacity");
+  }
+  *out = h;   // so that rpe_destroy can clean up on failure below
+  int rc = RPE_OK;
+  auto A = [&](int r) { if (rc == RPE_OK) rc = r; };
+  const size_t NI = h->NI, NP = h->NP, L = cfg->nlevels, KS = h->kp_stride, CS = h->cand_stride, MC = h->mcap;
+  A(dalloc(h, &h->ob.pyr, NI * h->pyr_stride));
+  A(dalloc(h, &h->ob.blur, NI * h->pyr_stride));
+  A(dalloc(h, &h->ob.cand_key, NI * CS));
+  // cand_cnt, hist and img_flags are cleared with one memset per batch: keep them contiguous
+  uint32_t* ctr = nullptr;
+  A(dalloc(h, &ctr, NI * L + NI * L * 256 + NI));
+  h->ob.cand_cnt = ctr; h->ob.hist = ctr + NI * L; h->ob.img_flags = ctr + NI * L + NI * L * 256;
+  A(dalloc(h, &h->ob.sel_key, NI * CS));
+  A(dalloc(h, &h->ob.sel_resp, NI * CS));
+  A(dalloc(h, &h->ob.lvl_key, NI * KS));
+  A(dalloc(h, &h->ob.lvl_resp, NI * KS));
+  A(dalloc(h, &h->ob.lvl_cnt, NI * L));
+  A(dalloc(h, &h->ob.kp_x, NI * KS)); A(dalloc(h, &h->ob.kp_y, NI * KS)); A(dalloc(h, &h->ob.kp_size, NI * KS));
+  A(dalloc(h, &h->ob.kp_angle, NI * KS)); A(dalloc(h, &h->ob.kp_resp, NI * KS)); A(dalloc(h, &h->ob.kp_oct, NI * KS));
+  A(dalloc(h, &h->ob.desc, NI * KS * 32));
+  A(dalloc(h, &h->ob.kp_n, NI));
+  A(dalloc(h, &h->mb.fwd1, NP * KS)); A(dalloc(h, &h->mb.fwd2, NP * KS)); A(dalloc(h, &h->mb.bwd1, NP * KS));
+  A(dalloc(h, &h->mb.m_q, NP * MC)); A(dalloc(h, &h->mb.m_t, NP * MC)); A(dalloc(h, &h->mb.m_d, NP * MC));
+  A(dalloc(h, &h->mb.m_n, NP));
+  A(dalloc(h, &h->mb.pts1, NP * MC * 2)); A(dalloc(h, &h->mb.pts2, NP * MC * 2));
+  A(dalloc(h, &h->gb.npts, NP * MC * 4));
+  A(dalloc(h, &h->gb.E, NP * 9));
+  A(dalloc(h, &h->gb.rmask, NP * MC)); A(dalloc(h, &h->gb.pmask, NP * MC));
+  A(dalloc(h, &h->gb.rinfo, NP * 4));
+  A(dalloc(h, &h->gb.R, NP * 9)); A(dalloc(h, &h->gb.t, NP * 3)); A(dalloc(h, &h->gb.euler, NP * 3));
+  A(dalloc(h, &h->gb.pose_cnt, NP)); A(dalloc(h, &h->gb.status, NP));
+  A(dalloc(h, &h->dK, 9));
+  if (rc == RPE_OK && cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaStreamCreate failed");
+  h->stream = h->own_stream;
+  if (rc == RPE_OK && cudaMallocHost((void**)&h->h_out_d, NP * 15 * sizeof(double)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
+  if (rc == RPE_OK && cudaMallocHost((void**)&h->h_out_i, NP * 5 * sizeof(int32_t)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
+  if (rc == RPE_OK && cudaMallocHost((void**)&h->h_K, 9 * sizeof(double)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
+  if (rc == RPE_OK) {
+    for (int i = 0; i <= RPE_T_COUNT; ++i)
+      if (cudaEventCreate(&h->ev[i]) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
+  }
+  if (rc == RPE_OK && (setup_orb_attributes(h->sort_cap_orb) || setup_match_attributes(h->sort_cap_match) || setup_geom_attributes()))
+    rc = fail(RPE_ERR_CUDA, "cudaFuncSetAttribute failed");
+  if (rc != RPE_OK) {
+    std::string keep = g_last_error;
+    rpe_destroy(h);
+    g_last_error = keep;
+    *out = nullptr;
+  }
+  return rc;
+}
+
+void rpe_destroy(rpe_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  for (void* p : h->allocs) cudaFree(p);
+  for (auto& kv : h->geoms) cudaFree(kv.second.d_taps);
+  if (h->gb.tr_subset) { cudaFree(h->gb.tr_subset); cudaFree(h->gb.tr_nmodels); cudaFree(h->gb.tr_counts); cudaFree(h->gb.tr_models); }
+  if (h->h_out_d) cudaFreeHost(h->h_out_d);
+  if (h->h_out_i) cudaFreeHost(h->h_out_i);
+  if (h->h_K) cudaFreeHost(h->h_K);
+  for (int i = 0; i <= RPE_T_COUNT; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+}
+
+int rpe_set_stream(rpe_handle* h, void* s) {
+  if (!h) return fail(RPE_ERR_INVALID, "null handle");
+  h->stream = s ? (cudaStream_t)s : h->own_stream;
+  return RPE_OK;
+}
+
+int rpe_get_capacity(const rpe_handle* h, int32_t* kp_cap, int32_t* match_cap) {
+  if (!h) return fail(RPE_ERR_INVALID, "null handle");
+  if (kp_cap) *kp_cap = h->kp_stride;
+  if (match_cap) *match_cap = h->mcap;
+  return RPE_OK;
+}
+
+int rpe_set_profiling(rpe_handle* h, int32_t on) {
+  if (!h) return fail(RPE_ERR_INVALID, "null handle");
+  h->profiling = on != 0;
+  return RPE_OK;
+}
+
+int rpe_get_stage_times(rpe_handle* h, float* ms, int32_t* launches) {
+  if (!h) return fail(RPE_ERR_INVALID, "null handle");
+  for (int i = 0; i < RPE_T_COUNT; ++i) {
+    if (ms) ms[i] = h->ms[i];
+    if (launches) launches[i] = h->launches[i];
+  }
+  return RPE_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+static inline void mark(rpe_handle* h, int i) {
+  if (h->profiling) cudaEventRecord(h->ev[i], h->stream);
+}
+
+static int finish_profile(rpe_handle* h) {
+  if (!h->profiling) return RPE_OK;
+  for (int i = 0; i < RPE_T_COUNT; ++i) RPE_CK(cudaEventElapsedTime(&h->ms[i], h->ev[i], h->ev[i + 1]));
+  return RPE_OK;
+}
+
+static int run_orb(rpe_handle* h, const Geometry& G, int n_img, int first_mark) {
+  OrbBuffers b = h->ob;
+  b.taps = G.d_taps;
+  const size_t nctr = (size_t)h->NI * h->cfg.nlevels * 257 + h->NI;
+  RPE_CK(cudaMemsetAsync(h->ob.cand_cnt, 0, nctr * sizeof(uint32_t), h->stream));
+  int* ln = h->launches;
+  if (first_mark >= 0) mark(h, RPE_T_PYRAMID);
+  launch_pyramid(G.g, b, n_img, h->stream, &ln[RPE_T_PYRAMID]);
+  if (first_mark >= 0) mark(h, RPE_T_FAST);
+  launch_fast(G.g, b, n_img, h->stream, &ln[RPE_T_FAST]);
+  if (first_mark >= 0) mark(h, RPE_T_SELECT);
+  launch_select(G.g, b, n_img, h->stream, &ln[RPE_T_SELECT]);
+  if (first_mark >= 0) mark(h, RPE_T_BLUR);
+  launch_blur(G.g, b, n_img, h->stream, &ln[RPE_T_BLUR]);
+  if (first_mark >= 0) mark(h, RPE_T_DESCRIBE);
+  launch_describe(G.g, b, n_img, h->stream, &ln[RPE_T_DESCRIBE]);
+  RPE_CK(cudaGetLastError());
+  return RPE_OK;
+}
+
+static RansacParams ransac_params(const rpe_handle* h) {
+  RansacParams rp;
+  rp.prob = h->cfg.ransac_prob; rp.threshold = h->cfg.ransac_threshold;
+  rp.max_iters = h->cfg.ransac_max_iters; rp.euler_convention = h->cfg.euler_convention;
+  return rp;
+}
+
+static int run_pairs(rpe_handle* h, int B) {
+  int* ln = h->launches;
+  mark(h, RPE_T_MATCH);
+  launch_match(h->ob, h->mb, h->kp_stride, B, h->cfg.match_mode, h->stream, &ln[RPE_T_MATCH]);
+  mark(h, RPE_T_MATCH_SORT);
+  launch_build_matches(h->ob, h->mb, h->kp_stride, h->mcap, h->sort_cap_match, B, h->cfg.match_mode, h->cfg.ratio,
+                       h->cfg.max_matches, h->stream, &ln[RPE_T_MATCH_SORT]);
+  mark(h, RPE_T_RANSAC);
+  GeomBuffers gb = h->gb;
+  gb.tr_subset = nullptr;
+  launch_normalize(h->mb, gb, h->mcap, B, h->dK, h->stream, &ln[RPE_T_RANSAC]);
+  launch_ransac(h->mb, gb, h->mcap, B, h->dK, ransac_params(h), h->stream, &ln[RPE_T_RANSAC]);
+  mark(h, RPE_T_POSE);
+  launch_pose(h->mb, gb, h->mcap, B, ransac_params(h), h->ob.img_flags, h->ob.kp_n, h->stream, &ln[RPE_T_POSE]);
+  RPE_CK(cudaGetLastError());
+  return RPE_OK;
+}
+
+static int upload_K(rpe_handle* h, const double K[9]) {
+  memcpy(h->h_K, K, 9 * sizeof(double));
+  RPE_CK(cudaMemcpyAsync(h->dK, h->h_K, 9 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  return RPE_OK;
+}
+
+static int download_results(rpe_handle* h, int B, double* R, double* t, double* euler, int32_t* status, int32_t* info) {
+  mark(h, RPE_T_D2H);
+  double* hd = h->h_out_d;
+  int32_t* hi = h->h_out_i;
+  cudaStream_t s = h->stream;
+  RPE_CK(cudaMemcpyAsync(hd, h->gb.R, (size_t)B * 9 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hd + (size_t)h->NP * 9, h->gb.t, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hd + (size_t)h->NP * 12, h->gb.euler, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hi, h->gb.status, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  if (info) {
+    RPE_CK(cudaMemcpyAsync(hi + h->NP, h->mb.m_n, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    RPE_CK(cudaMemcpyAsync(hi + 2 * h->NP, h->gb.pose_cnt, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  }
+  if (h->profiling) cudaEventRecord(h->ev[RPE_T_COUNT], s);
+  RPE_CK(cudaStreamSynchronize(s));
+  if (R) memcpy(R, hd, (size_t)B * 9 * sizeof(double));
+  if (t) memcpy(t, hd + (size_t)h->NP * 9, (size_t)B * 3 * sizeof(double));
+  if (euler) memcpy(euler, hd + (size_t)h->NP * 12, (size_t)B * 3 * sizeof(double));
+  if (status) memcpy(status, hi, (size_t)B * sizeof(int32_t));
+  if (info) {
+    // rinfo is small: fetch {best, iters} synchronously (stream already idle)
+    std::vector<int32_t> ri((size_t)B * 4);
+    RPE_CK(cudaMemcpy(ri.data(), h->gb.rinfo, ri.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < B; ++i) {
+      info[4 * i + 0] = hi[h->NP + i];
+      info[4 * i + 1] = hi[2 * h->NP + i];
+      info[4 * i + 2] = ri[4 * i + 1];
+      info[4 * i + 3] = ri[4 * i + 2];
+    }
+  }
+  return finish_profile(h);
+}
+
+static int check_batch(rpe_handle* h, int B, int H, int W, size_t pitch) {
+  if (!h) return fail(RPE_ERR_INVALID, "null handle");
+  if (B < 1 || H < 1 || W < 1 || pitch < (size_t)W) return fail(RPE_ERR_INVALID, "bad batch arguments");
+  if (B > h->NP) return fail(RPE_ERR_CAPACITY, "batch larger than max_pairs");
+  if (W > RPE_MAX_DIM || H > RPE_MAX_DIM) return fail(RPE_ERR_CAPACITY, "image dimension above 4095");
+  RPE_CK(cudaSetDevice(h->device));
+  return RPE_OK;
+}
+
+static void reset_profile(rpe_handle* h) {
+  for (int i = 0; i < RPE_T_COUNT; ++i) { h->launches[i] = 0; h->ms[i] = 0.f; }
+}
+
+extern "C" {
+
+int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* const* img2, int32_t B, int32_t H,
+                       int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
+                       int32_t* status, int32_t* info) {
+  RPE_TRY(check_batch(h, B, H, W, pitch));
+  if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
+  const Geometry* G;
+  RPE_TRY(get_geometry(h, W, H, &G));
+  reset_profile(h);
+  mark(h, RPE_T_H2D);
+  RPE_TRY(upload_K(h, K));
+  const int p0 = G->g.lv[0].pitch;
+  // fast path: all 2B images equally spaced in one host buffer with the device pitch -> one copy
+  bool contiguous = (pitch == (size_t)p0);
+  const ptrdiff_t stride = (const uint8_t*)img2[0] - (const uint8_t*)img1[0];
+  if (contiguous && stride >= (ptrdiff_t)(pitch * H)) {
+    for (int i = 0; i < B && contiguous; ++i)
+      contiguous = (img1[i] == img1[0] + (ptrdiff_t)2 * i * stride) && (img2[i] == img1[i] + stride);
+  } else contiguous = false;
+  if (contiguous) {
+    RPE_CK(cudaMemcpy2DAsync(h->ob.pyr, h->pyr_stride, img1[0], (size_t)stride, (size_t)pitch * H, 2 * B,
+                             cudaMemcpyHostToDevice, h->stream));
+  } else {
+    for (int i = 0; i < B; ++i) {
+      RPE_CK(cudaMemcpy2DAsync(h->ob.pyr + (size_t)(2 * i) * h->pyr_stride, p0, img1[i], pitch, W, H,
+                               cudaMemcpyHostToDevice, h->stream));
+      RPE_CK(cudaMemcpy2DAsync(h->ob.pyr + (size_t)(2 * i + 1) * h->pyr_stride, p0, img2[i], pitch, W, H,
+                               cudaMemcpyHostToDevice, h->stream));
+    }
+  }
+  RPE_TRY(run_orb(h, *G, 2 * B, 0));
+  RPE_TRY(run_pairs(h, B));
+  h->last_geom = G;
+  h->last_pairs = B;
+  return download_results(h, B, R, t, euler, status, info);
+}
+
+int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img_stride, int32_t B, int32_t H,
+                              int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
+                              int32_t* status, int32_t* info) {
+  RPE_TRY(check_batch(h, B, H, W, pitch));
+  if (!d_images || !K || img_stride < pitch * (size_t)H) return fail(RPE_ERR_INVALID, "bad device image arguments");
+  const Geometry* G;
+  RPE_TRY(get_geometry(h, W, H, &G));
+  reset_profile(h);
+  mark(h, RPE_T_H2D);
+  RPE_TRY(upload_K(h, K));
+  const int p0 = G->g.lv[0].pitch;
+  if (pitch == (size_t)p0) {
+    RPE_CK(cudaMemcpy2DAsync(h->ob.pyr, h->pyr_stride, d_images, img_stride, pitch * H, 2 * B,
+                             cudaMemcpyDeviceToDevice, h->stream));
+  } else {
+    for (int i = 0; i < 2 * B; ++i)
+      RPE_CK(cudaMemcpy2DAsync(h->ob.pyr + (size_t)i * h->pyr_stride, p0, d_images + (size_t)i * img_stride, pitch, W,
+                               H, cudaMemcpyDeviceToDevice, h->stream));
+  }
+  RPE_TRY(run_orb(h, *G, 2 * B, 0));
+  RPE_TRY(run_pairs(h, B));
+  h->last_geom = G;
+  h->last_pairs = B;
+  return download_results(h, B, R, t, euler, status, info);
+}
+
+int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size_t pitch, float* x, float* y,
+                   float* size, float* angle, float* response, int32_t* octave, uint8_t* desc, int32_t* n_out,
+                   int32_t* flags_out) {
+  RPE_TRY(check_batch(h, 1, H, W, pitch));
+  if (!img || !n_out) return fail(RPE_ERR_INVALID, "null argument");
+  const Geometry* G;
+  RPE_TRY(get_geometry(h, W, H, &G));
+  reset_profile(h);
+  RPE_CK(cudaMemcpy2DAsync(h->ob.pyr, G->g.lv[0].pitch, img, pitch, W, H, cudaMemcpyHostToDevice, h->stream));
+  RPE_TRY(run_orb(h, *G, 1, -1));
+  h->last_geom = G;
+  h->last_pairs = 0;
+  int32_t n = 0;
+  uint32_t fl = 0;
+  RPE_CK(cudaMemcpyAsync(&n, h->ob.kp_n, sizeof n, cudaMemcpyDeviceToHost, h->stream));
+  RPE_CK(cudaMemcpyAsync(&fl, h->ob.img_flags, sizeof fl, cudaMemcpyDeviceToHost, h->stream));
+  RPE_CK(cudaStreamSynchronize(h->stream));
+  *n_out = n;
+  if (flags_out) *flags_out = (int32_t)fl;
+  auto get = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
+    return dst ? cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost) : cudaSuccess;
+  };
+  RPE_CK(get(x, h->ob.kp_x, n * sizeof(float)));
+  RPE_CK(get(y, h->ob.kp_y, n * sizeof(float)));
+  RPE_CK(get(size, h->ob.kp_size, n * sizeof(float)));
+  RPE_CK(get(angle, h->ob.kp_angle, n * sizeof(float)));
+  RPE_CK(get(response, h->ob.kp_resp, n * sizeof(float)));
+  RPE_CK(get(octave, h->ob.kp_oct, n * sizeof(int32_t)));
+  RPE_CK(get(desc, h->ob.desc, (size_t)n * 32));
+  return RPE_OK;
+}
+
+int rpe_match(rpe_handle* h, const uint8_t* desc1, int32_t n1, const uint8_t* desc2, int32_t n2, int32_t* matches,
+              int32_t* m_out) {
+  if (!h || !m_out || n1 < 0 || n2 < 0) return fail(RPE_ERR_INVALID, "bad argument");
+  if (n1 > h->kp_stride || n2 > h->kp_stride) return fail(RPE_ERR_CAPACITY, "more descriptors than the handle's keypoint capacity");
+  RPE_CK(cudaSetDevice(h->device));
+  reset_profile(h);
+  cudaStream_t s = h->stream;
+  const size_t KS = h->kp_stride;
+  if (n1) RPE_CK(cudaMemcpyAsync(h->ob.desc, desc1, (size_t)n1 * 32, cudaMemcpyHostToDevice, s));
+  if (n2) RPE_CK(cudaMemcpyAsync(h->ob.desc + KS * 32, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice, s));
+  const int32_t nn[2] = {n1, n2};
+  RPE_CK(cudaMemcpyAsync(h->ob.kp_n, nn, sizeof nn, cudaMemcpyHostToDevice, s));
+  RPE_CK(cudaStreamSynchronize(s));   // nn is a stack buffer
+  int* ln = h->launches;
+  launch_match(h->ob, h->mb, h->kp_stride, 1, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
+  launch_build_matches(h->ob, h->mb, h->kp_stride, h->mcap, h->sort_cap_match, 1, h->cfg.match_mode, h->cfg.ratio,
+                       h->cfg.max_matches, s, &ln[RPE_T_MATCH_SORT]);
+  RPE_CK(cudaGetLastError());
+  int32_t m = 0;
+  RPE_CK(cudaMemcpyAsync(&m, h->mb.m_n, sizeof m, cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaStreamSynchronize(s));
+  *m_out = m;
+  if (matches && m) {
+    std::vector<int32_t> q(m), t(m), d(m);
+    RPE_CK(cudaMemcpy(q.data(), h->mb.m_q, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    RPE_CK(cudaMemcpy(t.data(), h->mb.m_t, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    RPE_CK(cudaMemcpy(d.data(), h->mb.m_d, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < m; ++i) { matches[3 * i] = q[i]; matches[3 * i + 1] = t[i]; matches[3 * i + 2] = d[i]; }
+  }
+  return RPE_OK;
+}
+
+static int upload_points(rpe_handle* h, const float* pts1, const float* pts2, int32_t m, const double K[9]) {
+  if (m < 0 || m > h->mcap) return fail(RPE_ERR_CAPACITY, "more points than the handle's match capacity");
+  cudaStream_t s = h->stream;
+  if (m) {
+    RPE_CK(cudaMemcpyAsync(h->mb.pts1, pts1, (size_t)m * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
+    RPE_CK(cudaMemcpyAsync(h->mb.pts2, pts2, (size_t)m * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
+  }
+  RPE_CK(cudaMemcpyAsync(h->mb.m_n, &m, sizeof m, cudaMemcpyHostToDevice, s));
+  RPE_TRY(upload_K(h, K));
+  RPE_CK(cudaStreamSynchronize(s));
+  int dummy = 0;
+  launch_normalize(h->mb, h->gb, h->mcap, 1, h->dK, s, &dummy);
+  return RPE_OK;
+}
+
+int rpe_find_essential(rpe_handle* h, const float* pts1, const float* pts2, int32_t m, const double K[9], double* E,
+                       uint8_t* mask, int32_t* info) {
+  if (!h || !K || (m > 0 && (!pts1 || !pts2))) return fail(RPE_ERR_INVALID, "bad argument");
+  RPE_CK(cudaSetDevice(h->device));
+  reset_profile(h);
+  if (!h->gb.tr_subset) {
+    const int cap = (h->cfg.ransac_max_iters + 63) / 64 * 64;
+    RPE_CK(cudaMalloc((void**)&h->gb.tr_subset, (size_t)cap * 5 * sizeof(int32_t)));
+    RPE_CK(cudaMalloc((void**)&h->gb.tr_nmodels, (size_t)cap * sizeof(int32_t)));
+    RPE_CK(cudaMalloc((void**)&h->gb.tr_counts, (size_t)cap * 10 * sizeof(int32_t)));
+    RPE_CK(cudaMalloc((void**)&h->gb.tr_models, (size_t)cap * 90 * sizeof(double)));
+    h->gb.tr_cap = cap;
+  }
+  RPE_TRY(upload_points(h, pts1, pts2, m, K));
+  launch_ransac(h->mb, h->gb, h->mcap, 1, h->dK, ransac_params(h), h->stream, &h->launches[RPE_T_RANSAC]);
+  RPE_CK(cudaGetLastError());
+  RPE_CK(cudaStreamSynchronize(h->stream));
+  if (E) RPE_CK(cudaMemcpy(E, h->gb.E, 9 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (mask && m) RPE_CK(cudaMemcpy(mask, h->gb.rmask, m, cudaMemcpyDeviceToHost));
+  if (info) RPE_CK(cudaMemcpy(info, h->gb.rinfo, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  return RPE_OK;
+}
+
+int rpe_ransac_trace(rpe_handle* h, int32_t max_hyp, int32_t* subset, int32_t* nmodels, int32_t* counts,
+                     double* models, int32_t* n_hyp) {
+  if (!h || !h->gb.tr_subset || !n_hyp) return fail(RPE_ERR_INVALID, "no trace available");
+  RPE_CK(cudaSetDevice(h->device));
+  int32_t ri[4];
+  RPE_CK(cudaMemcpy(ri, h->gb.rinfo, sizeof ri, cudaMemcpyDeviceToHost));
+  const int n = std::min(std::min(ri[3], max_hyp), h->gb.tr_cap);
+  *n_hyp = n;
+  if (n <= 0) return RPE_OK;
+  if (subset) RPE_CK(cudaMemcpy(subset, h->gb.tr_subset, (size_t)n * 5 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (nmodels) RPE_CK(cudaMemcpy(nmodels, h->gb.tr_nmodels, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (counts) RPE_CK(cudaMemcpy(counts, h->gb.tr_counts, (size_t)n * 10 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (models) RPE_CK(cudaMemcpy(models, h->gb.tr_models, (size_t)n * 90 * sizeof(double), cudaMemcpyDeviceToHost));
+  return RPE_OK;
+}
+
+int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const float* pts2, int32_t m,
+                     const double K[9], double* R, double* t, double* euler, int32_t* count, uint8_t* mask) {
+  if (!h || !E || !K || (m > 0 && (!pts1 || !pts2))) return fail(RPE_ERR_INVALID, "bad argument");
+  RPE_CK(cudaSetDevice(h->device));
+  reset_profile(h);
+  RPE_CK(cudaMemcpy(h->gb.E, E, 9 * sizeof(double), cudaMemcpyHostToDevice));
+  RPE_TRY(upload_points(h, pts1, pts2, m, K));
+  GeomBuffers gb = h->gb;
+  gb.rinfo = nullptr;
+  launch_pose(h->mb, gb, h->mcap, 1, ransac_params(h), nullptr, nullptr, h->stream, &h->launches[RPE_T_POSE]);
+  RPE_CK(cudaGetLastError());
+  RPE_CK(cudaStreamSynchronize(h->stream));
+  if (R) RPE_CK(cudaMemcpy(R, h->gb.R, 9 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (t) RPE_CK(cudaMemcpy(t, h->gb.t, 3 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (euler) RPE_CK(cudaMemcpy(euler, h->gb.euler, 3 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (count) RPE_CK(cudaMemcpy(count, h->gb.pose_cnt, sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (mask && m) RPE_CK(cudaMemcpy(mask, h->gb.pmask, m, cudaMemcpyDeviceToHost));
+  return RPE_OK;
+}
+
+int rpe_get_stage(rpe_handle* h, int32_t pair, int32_t view, int32_t stage, int32_t arg, void* out, size_t* n) {
+  if (!h || !n || !out) return fail(RPE_ERR_INVALID, "null argument");
+  if (pair < 0 || pair >= h->NP || view < 0 || view > 1) return fail(RPE_ERR_INVALID, "bad pair/view");
+  RPE_CK(cudaSetDevice(h->device));
+  RPE_CK(cudaStreamSynchronize(h->stream));
+  const size_t img = 2 * (size_t)pair + view, KS = h->kp_stride, MC = h->mcap;
+  const size_t cap = *n;
+  auto copy = [&](const void* src, size_t bytes) -> int {
+    const size_t c = std::min(bytes, cap);
+    if (c) RPE_CK(cudaMemcpy(out, src, c, cudaMemcpyDeviceToHost));
+    *n = c;
+    return RPE_OK;
+  };
+  int32_t kn = 0, mn = 0;
+  RPE_CK(cudaMemcpy(&kn, h->ob.kp_n + img, sizeof kn, cudaMemcpyDeviceToHost));
+  RPE_CK(cudaMemcpy(&mn, h->mb.m_n + pair, sizeof mn, cudaMemcpyDeviceToHost));
+  switch (stage) {
+    case RPE_STAGE_PYRAMID_LEVEL:
+    case RPE_STAGE_BLURRED_LEVEL: {
+      if (!h->last_geom || arg < 0 || arg >= h->cfg.nlevels) return fail(RPE_ERR_INVALID, "no geometry / bad level");
+      const LevelGeom& L = h->last_geom->g.lv[arg];
+      const uint8_t* base = (stage == RPE_STAGE_PYRAMID_LEVEL ? h->ob.pyr : h->ob.blur) + img * h->pyr_stride + L.off;
+      const size_t bytes = (size_t)L.w * L.h;
+      if (cap < bytes) return fail(RPE_ERR_INVALID, "buffer too small");
+      RPE_CK(cudaMemcpy2D(out, L.w, base, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost));
+      *n = bytes;
+      return RPE_OK;
+    }
+    case RPE_STAGE_KP_X: return copy(h->ob.kp_x + img * KS, kn * sizeof(float));
+    case RPE_STAGE_KP_Y: return copy(h->ob.kp_y + img * KS, kn * sizeof(float));
+    case RPE_STAGE_KP_SIZE: return copy(h->ob.kp_size + img * KS, kn * sizeof(float));
+    case RPE_STAGE_KP_ANGLE: return copy(h->ob.kp_angle + img * KS, kn * sizeof(float));
+    case RPE_STAGE_KP_RESPONSE: return copy(h->ob.kp_resp + img * KS, kn * sizeof(float));
+    case RPE_STAGE_KP_OCTAVE: return copy(h->ob.kp_oct + img * KS, kn * sizeof(int32_t));
+    case RPE_STAGE_DESCRIPTORS: return copy(h->ob.desc + img * KS * 32, (size_t)kn * 32);
+    case RPE_STAGE_MATCHES: {
+      std::vector<int32_t> q(mn), t(mn), d(mn), o((size_t)mn * 3);
+      if (mn) {
+        RPE_CK(cudaMemcpy(q.data(), h->mb.m_q + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        RPE_CK(cudaMemcpy(t.data(), h->mb.m_t + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        RPE_CK(cudaMemcpy(d.data(), h->mb.m_d + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
+      }
+      for (int i = 0; i < mn; ++i) { o[3 * i] = q[i]; o[3 * i + 1] = t[i]; o[3 * i + 2] = d[i]; }
+      const size_t c = std::min(o.size() * sizeof(int32_t), cap);
+      memcpy(out, o.data(), c);
+      *n = c;
+      return RPE_OK;
+    }
+    case RPE_STAGE_PTS1: return copy(h->mb.pts1 + pair * MC * 2, (size_t)mn * 2 * sizeof(float));
+    case RPE_STAGE_PTS2: return copy(h->mb.pts2 + pair * MC * 2, (size_t)mn * 2 * sizeof(float));
+    case RPE_STAGE_E: return copy(h->gb.E + pair * 9, 9 * sizeof(double));
+    case RPE_STAGE_RANSAC_MASK: return copy(h->gb.rmask + pair * MC, mn);
+    case RPE_STAGE_POSE_MASK: return copy(h->gb.pmask + pair * MC, mn);
+    default: return fail(RPE_ERR_INVALID, "unknown stage");
+  }
+}
+
+}  // extern "C"

@@ -1,0 +1,220 @@
+// kernels_match.cu — brute-force Hamming matcher on sm_100a.  Replaces
+// cv2.BFMatcher(NORM_HAMMING, crossCheck=True).match + the reference's stable sort and
+// max_matches cut (src/core/pose_estimator.py:131, :144-151) and, for BASELINE configs 3-5,
+// knnMatch(k=2) + ratio test.
+//
+// k_hamming: INT-pipe bound (xor + popc), not HBM bound: each thread keeps kQPT query
+// descriptors (8 x u32 each) in registers, train descriptors stream through a shared-memory
+// tile read with 128-bit broadcast loads; nearest / second nearest are tracked as packed
+// (dist << 20 | index) keys, which reproduces OpenCV's tie rule (lowest index) for free.
+#include "rpe_device.cuh"
+
+namespace rpe {
+
+constexpr int kMatchThreads = 128;
+constexpr int kQPT = 2;                       // queries per thread
+constexpr int kQPB = kMatchThreads * kQPT;    // queries per block
+constexpr int kTrainTile = 128;               // train descriptors per shared-memory tile
+
+template <bool kTop2>
+__global__ void __launch_bounds__(kMatchThreads)
+k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride,
+          uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
+  __shared__ uint4 s_train[kTrainTile * 2];
+  const int pair = blockIdx.y;
+  const int dir = blockIdx.z;                  // 0: view1 -> view2, 1: view2 -> view1
+  const int qi = 2 * pair + dir, ti = 2 * pair + 1 - dir;
+  const int nq = kp_n[qi], nt = kp_n[ti];
+  const int q0 = blockIdx.x * kQPB;
+  if (q0 >= nq) return;
+  const uint4* dq = reinterpret_cast<const uint4*>(desc + (size_t)qi * kp_stride * 32);
+  const uint4* dt = reinterpret_cast<const uint4*>(desc + (size_t)ti * kp_stride * 32);
+  const int tid = threadIdx.x;
+
+  uint32_t q[kQPT][8];
+  uint32_t best1[kQPT], best2[kQPT];
+#pragma unroll
+  for (int k = 0; k < kQPT; ++k) {
+    const int qq = min(q0 + tid + k * kMatchThreads, nq - 1);
+    const uint4 a = dq[2 * qq], b = dq[2 * qq + 1];
+    q[k][0] = a.x; q[k][1] = a.y; q[k][2] = a.z; q[k][3] = a.w;
+    q[k][4] = b.x; q[k][5] = b.y; q[k][6] = b.z; q[k][7] = b.w;
+    best1[k] = 0xffffffffu;
+    best2[k] = 0xffffffffu;
+  }
+  for (int t0 = 0; t0 < nt; t0 += kTrainTile) {
+    const int tn = min(kTrainTile, nt - t0);
+    __syncthreads();
+    for (int i = tid; i < tn * 2; i += kMatchThreads) s_train[i] = dt[2 * t0 + i];
+    __syncthreads();
+#pragma unroll 4
+    for (int j = 0; j < tn; ++j) {
+      const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
+#pragma unroll
+      for (int k = 0; k < kQPT; ++k) {
+        const uint32_t d = __popc(q[k][0] ^ a.x) + __popc(q[k][1] ^ a.y) + __popc(q[k][2] ^ a.z) +
+                           __popc(q[k][3] ^ a.w) + __popc(q[k][4] ^ b.x) + __popc(q[k][5] ^ b.y) +
+                           __popc(q[k][6] ^ b.z) + __popc(q[k][7] ^ b.w);
+        const uint32_t key = pack_nn(d, (uint32_t)(t0 + j));
+        if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
+        best1[k] = min(best1[k], key);
+      }
+    }
+  }
+  uint32_t* o1 = (dir == 0 ? fwd1 : bwd1) + (size_t)pair * kp_stride;
+#pragma unroll
+  for (int k = 0; k < kQPT; ++k) {
+    const int qq = q0 + tid + k * kMatchThreads;
+    if (qq < nq) {
+      o1[qq] = best1[k];
+      if (kTop2) fwd2[(size_t)pair * kp_stride + qq] = best2[k];
+    }
+  }
+}
+
+void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int mode,
+                  cudaStream_t s, int* launches) {
+  const int qblocks = (kp_stride + kQPB - 1) / kQPB;
+  if (mode == RPE_MATCH_RATIO) {
+    dim3 grid(qblocks, n_pairs, 1);
+    k_hamming<true><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, mb.fwd1, mb.fwd2, mb.bwd1);
+  } else {
+    dim3 grid(qblocks, n_pairs, 2);
+    k_hamming<false><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, mb.fwd1, mb.fwd2, mb.bwd1);
+  }
+  ++*launches;
+}
+
+// ------------------------------------------------------------------ K9: filter + stable sort + cut + gather
+// One CTA per pair.  Valid matches (cross-check or ratio test) are ranked by the unique key
+// (dist << 20 | queryIdx), which is exactly the order of Python's stable sort by distance of a
+// query-ascending list; the first max_matches are kept: everything below the cut distance,
+// plus the first few (in query order) at the cut distance.
+constexpr int kBuildThreads = 512;
+
+__device__ __forceinline__ uint32_t match_key(int q, int mode, double ratio, int n1, int n2,
+                                              const uint32_t* f1, const uint32_t* f2, const uint32_t* b1) {
+  // returns packed (dist << 20 | q) or 0xffffffff when query q yields no match
+  if (q >= n1 || n2 <= 0) return 0xffffffffu;
+  const uint32_t k1 = f1[q];
+  const uint32_t d = k1 >> 20, t = k1 & 0xfffffu;
+  if (mode == RPE_MATCH_RATIO) {
+    if (n2 < 2) return 0xffffffffu;
+    const uint32_t d2 = f2[q] >> 20;
+    if (!((double)d < ratio * (double)d2)) return 0xffffffffu;
+  } else {
+    if ((b1[t] & 0xfffffu) != (uint32_t)q) return 0xffffffffu;
+  }
+  return pack_nn(d, (uint32_t)q);
+}
+
+__global__ void __launch_bounds__(kBuildThreads)
+k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, const int32_t* __restrict__ kp_n,
+                int kp_stride, const uint32_t* __restrict__ fwd1, const uint32_t* __restrict__ fwd2,
+                const uint32_t* __restrict__ bwd1, int mode, double ratio, int max_matches, int mcap,
+                int sort_cap, int32_t* __restrict__ m_q, int32_t* __restrict__ m_t, int32_t* __restrict__ m_d,
+                int32_t* __restrict__ m_n, float* __restrict__ pts1, float* __restrict__ pts2) {
+  extern __shared__ uint32_t s_keys[];          // sort_cap entries
+  __shared__ uint32_t s_hist[258];
+  __shared__ uint32_t s_warp[kBuildThreads / 32];
+  __shared__ uint32_t s_cut, s_take, s_n, s_running;
+  const int pair = blockIdx.x, tid = threadIdx.x;
+  const int n1 = kp_n[2 * pair], n2 = kp_n[2 * pair + 1];
+  const uint32_t* f1 = fwd1 + (size_t)pair * kp_stride;
+  const uint32_t* f2 = fwd2 + (size_t)pair * kp_stride;
+  const uint32_t* b1 = bwd1 + (size_t)pair * kp_stride;
+  const uint32_t limit = (uint32_t)min(max_matches > 0 ? max_matches : mcap, mcap);
+
+  for (int i = tid; i < 258; i += kBuildThreads) s_hist[i] = 0;
+  if (tid == 0) { s_n = 0; s_running = 0; }
+  for (int i = tid; i < sort_cap; i += kBuildThreads) s_keys[i] = 0xffffffffu;
+  __syncthreads();
+  for (int q = tid; q < n1; q += kBuildThreads) {
+    const uint32_t k = match_key(q, mode, ratio, n1, n2, f1, f2, b1);
+    if (k != 0xffffffffu) atomicAdd(&s_hist[k >> 20], 1u);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    uint32_t cum = 0, cut = 257, take = 0;
+    for (uint32_t d = 0; d <= 256; ++d) {
+      if (cum + s_hist[d] >= limit) { cut = d; take = limit - cum; break; }
+      cum += s_hist[d];
+    }
+    s_cut = cut;     // distances < cut are all kept; `take` more at distance == cut, in query order
+    s_take = take;
+  }
+  __syncthreads();
+  const uint32_t cut = s_cut, take = s_take;
+  // ordered pass over queries (chunks of blockDim) for the rank among distance == cut
+  for (int base = 0; base < n1; base += kBuildThreads) {
+    const int q = base + tid;
+    const uint32_t k = match_key(q, mode, ratio, n1, n2, f1, f2, b1);
+    const uint32_t d = k >> 20;
+    const bool valid = k != 0xffffffffu;
+    const bool at_cut = valid && d == cut;
+    const uint32_t bal = __ballot_sync(0xffffffffu, at_cut);
+    const int lane = tid & 31, warp = tid >> 5;
+    if (lane == 0) s_warp[warp] = __popc(bal);
+    __syncthreads();
+    uint32_t before = s_running;
+    for (int w = 0; w < warp; ++w) before += s_warp[w];
+    const uint32_t rank = before + __popc(bal & ((1u << lane) - 1u));
+    const bool keep = valid && (d < cut || (at_cut && rank < take));
+    if (keep) {
+      const uint32_t j = atomicAdd(&s_n, 1u);
+      if (j < (uint32_t)sort_cap) s_keys[j] = k;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t tot = 0;
+      for (int w = 0; w < kBuildThreads / 32; ++w) tot += s_warp[w];
+      s_running += tot;
+    }
+    __syncthreads();
+  }
+  const uint32_t n = min(s_n, (uint32_t)sort_cap);
+  uint32_t m = 1;
+  while (m < n) m <<= 1;
+  for (uint32_t k = 2; k <= m; k <<= 1) {
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t i = tid; i < m; i += kBuildThreads) {
+        const uint32_t ixj = i ^ j;
+        if (ixj > i) {
+          const uint32_t a = s_keys[i], b = s_keys[ixj];
+          const bool up = (i & k) == 0;
+          if ((a > b) == up) { s_keys[i] = b; s_keys[ixj] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  const float* x1 = kp_x + (size_t)(2 * pair) * kp_stride;
+  const float* y1 = kp_y + (size_t)(2 * pair) * kp_stride;
+  const float* x2 = kp_x + (size_t)(2 * pair + 1) * kp_stride;
+  const float* y2 = kp_y + (size_t)(2 * pair + 1) * kp_stride;
+  for (uint32_t i = tid; i < n; i += kBuildThreads) {
+    const uint32_t k = s_keys[i];
+    const int q = k & 0xfffffu, d = k >> 20;
+    const int t = f1[q] & 0xfffffu;
+    const size_t o = (size_t)pair * mcap + i;
+    m_q[o] = q; m_t[o] = t; m_d[o] = d;
+    pts1[2 * o] = x1[q]; pts1[2 * o + 1] = y1[q];
+    pts2[2 * o] = x2[t]; pts2[2 * o + 1] = y2[t];
+  }
+  if (tid == 0) m_n[pair] = (int32_t)n;
+}
+
+void launch_build_matches(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int mcap, int sort_cap,
+                          int n_pairs, int mode, double ratio, int max_matches, cudaStream_t s, int* launches) {
+  k_build_matches<<<n_pairs, kBuildThreads, (size_t)sort_cap * 4, s>>>(
+      ob.kp_x, ob.kp_y, ob.kp_n, kp_stride, mb.fwd1, mb.fwd2, mb.bwd1, mode, ratio, max_matches, mcap, sort_cap,
+      mb.m_q, mb.m_t, mb.m_d, mb.m_n, mb.pts1, mb.pts2);
+  ++*launches;
+}
+
+int setup_match_attributes(int sort_cap_match) {
+  return (int)cudaFuncSetAttribute(k_build_matches, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   sort_cap_match * 4);
+}
+
+}  // namespace rpe

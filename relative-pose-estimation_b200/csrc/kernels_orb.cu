@@ -1,0 +1,379 @@
+// kernels_orb.cu — ORB stage on sm_100a: pyramid, FAST-9 + NMS, two-step retainBest with
+// Harris scoring, 7x7 blur, orientation + steered rBRIEF.  Replaces
+// cv2.ORB.detectAndCompute as the reference calls it (src/core/pose_estimator.py:85-91, :108).
+// Every launch covers the whole batch (grid.y / grid.z = image slot); the dense kernels
+// (FAST, blur) cover all pyramid levels in one launch through a flat tile table.
+#include "rpe_device.cuh"
+#include "orb_math.cuh"
+
+namespace rpe {
+
+// ------------------------------------------------------------------ K1: pyramid level l from l-1
+__global__ void __launch_bounds__(256)
+k_resize(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,
+         int level) {
+  const LevelGeom& d = g.lv[level];
+  const LevelGeom& s = g.lv[level - 1];
+  const int img = blockIdx.z;
+  const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int y = blockIdx.y * 8 + threadIdx.y;
+  if (y >= d.h || x4 >= d.pitch) return;
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + s.off;
+  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
+  const int2 ty = taps[d.ytab + y];
+  uint32_t out = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int x = min(x4 + k, d.w - 1);
+    const int2 tx = taps[d.xtab + x];
+    out |= (uint32_t)resize_px(src, s.pitch, s.w, s.h, tx.x, tx.y, ty.x, ty.y) << (8 * k);
+  }
+  *reinterpret_cast<uint32_t*>(dst + (size_t)y * d.pitch + x4) = out;
+}
+
+void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
+  for (int l = 1; l < g.nlevels; ++l) {
+    const LevelGeom& d = g.lv[l];
+    dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 7) / 8, n_img), block(32, 8);
+    k_resize<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
+    ++*launches;
+  }
+}
+
+// flat tile index -> (level, tile x, tile y)
+__device__ __forceinline__ int find_level(const OrbGeom& g, int tile) {
+  int l = 0;
+#pragma unroll 1
+  for (int i = 1; i < g.nlevels; ++i)
+    if (tile >= g.lv[i].tile0) l = i;
+  return l;
+}
+
+// ------------------------------------------------------------------ K2: FAST-9 + 3x3 NMS + border
+// One CTA = one 64x32 tile of one level of one image.  The image tile (+4 halo) is staged in
+// shared memory with 32-bit loads; scores for the tile (+1 halo) are kept in shared memory for
+// the NMS; survivors inside the 31-px border are appended to the level's candidate list and
+// counted in its score histogram.
+constexpr int kFastIW = kTileW + 8;   // 72
+constexpr int kFastIH = kTileH + 8;   // 40
+constexpr int kFastSW = kTileW + 4;   // 68 (pitch of the score tile; 66 used)
+constexpr int kFastSH = kTileH + 2;   // 34
+
+__global__ void __launch_bounds__(256)
+k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand_key,
+       uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
+  __shared__ __align__(16) uint8_t simg[kFastIH * kFastIW];
+  __shared__ uint8_t ssc[kFastSH * kFastSW];
+  const int img = blockIdx.y;
+  const int level = find_level(g, blockIdx.x);
+  const LevelGeom& L = g.lv[level];
+  const int t = blockIdx.x - L.tile0;
+  const int x0 = (t % L.tiles_x) * kTileW, y0 = (t / L.tiles_x) * kTileH;
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
+  const int tid = threadIdx.x;
+
+  // stage (x0-4 .. x0+68) x (y0-4 .. y0+36) as 18 words x 40 rows
+  for (int i = tid; i < kFastIH * (kFastIW / 4); i += 256) {
+    const int r = i / (kFastIW / 4), cw = i % (kFastIW / 4);
+    const int y = y0 - 4 + r, x = x0 - 4 + cw * 4;
+    uint32_t v = 0;
+    if (y >= 0 && y < L.h && x >= 0 && x < L.pitch)
+      v = *reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch + x);
+    *reinterpret_cast<uint32_t*>(&simg[r * kFastIW + cw * 4]) = v;
+  }
+  __syncthreads();
+  // scores on (x0-1 .. x0+64) x (y0-1 .. y0+32)
+  for (int i = tid; i < kFastSH * (kTileW + 2); i += 256) {
+    const int sy = i / (kTileW + 2), sx = i % (kTileW + 2);
+    const int x = x0 - 1 + sx, y = y0 - 1 + sy;
+    int sc = 0;
+    if (x >= 3 && x < L.w - 3 && y >= 3 && y < L.h - 3)
+      sc = fast9_score(&simg[(sy + 3) * kFastIW + sx + 3], kFastIW, g.fast_threshold);
+    ssc[sy * kFastSW + sx] = (uint8_t)sc;
+  }
+  __syncthreads();
+  // NMS + border filter + append
+  uint32_t* cnt = cand_cnt + img * g.nlevels + level;
+  uint32_t* hst = hist + (size_t)(img * g.nlevels + level) * 256;
+  uint32_t* out = cand_key + (size_t)img * g.cand_stride + L.cand_off;
+  for (int i = tid; i < kTileW * kTileH; i += 256) {
+    const int ty = i / kTileW, tx = i % kTileW;
+    const uint8_t* c = &ssc[(ty + 1) * kFastSW + tx + 1];
+    const int s = c[0];
+    if (s == 0) continue;
+    const int x = x0 + tx, y = y0 + ty;
+    if (x < 31 || x >= L.w - 31 || y < 31 || y >= L.h - 31) continue;
+    const bool keep = s > c[-kFastSW - 1] && s > c[-kFastSW] && s > c[-kFastSW + 1] && s > c[-1] &&
+                      s > c[1] && s > c[kFastSW - 1] && s > c[kFastSW] && s > c[kFastSW + 1];
+    if (!keep) continue;
+    const uint32_t pos = atomicAdd(cnt, 1u);
+    if (pos < (uint32_t)L.cand_cap) out[pos] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+    atomicAdd(&hst[s], 1u);
+  }
+}
+
+void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
+  dim3 grid(g.total_tiles, n_img);
+  k_fast<<<grid, 256, 0, s>>>(g, b.pyr, b.cand_key, b.cand_cnt, b.hist);
+  ++*launches;
+}
+
+// ------------------------------------------------------------------ K3/K4: retainBest x2 + Harris
+// One CTA per (level, image).  (1) FAST-score threshold for 2*quota from the histogram (ties
+// kept), (2) Harris response of the survivors, (3) exact quota-th largest response by 4-pass
+// radix select (ties kept), (4) bitonic sort of the kept keypoints by (y, x) -> canonical order.
+__device__ __forceinline__ uint32_t f32_orderable(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+constexpr int kSelThreads = 512;
+
+__global__ void __launch_bounds__(kSelThreads)
+k_select(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr,
+         const uint32_t* __restrict__ cand_key, const uint32_t* __restrict__ cand_cnt,
+         const uint32_t* __restrict__ hist, uint32_t* __restrict__ sel_key, float* __restrict__ sel_resp,
+         uint32_t* __restrict__ lvl_key, float* __restrict__ lvl_resp, uint32_t* __restrict__ lvl_cnt,
+         uint32_t* __restrict__ img_flags) {
+  extern __shared__ __align__(16) unsigned long long s_sort[];   // g.sort_cap entries
+  __shared__ uint32_t s_hist[256];
+  __shared__ uint32_t s_cnt, s_thr1, s_prefix, s_k, s_keep;
+  const int level = blockIdx.x, img = blockIdx.y;
+  const LevelGeom& L = g.lv[level];
+  const int tid = threadIdx.x;
+  const uint32_t raw = cand_cnt[img * g.nlevels + level];
+  const uint32_t n = min(raw, (uint32_t)L.cand_cap);
+  if (raw > (uint32_t)L.cand_cap && tid == 0) atomicOr(&img_flags[img], 1u);
+  const uint32_t quota = (uint32_t)L.quota;
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
+  const uint32_t* ck = cand_key + (size_t)img * g.cand_stride + L.cand_off;
+  uint32_t* sk = sel_key + (size_t)img * g.cand_stride + L.cand_off;
+  float* sr = sel_resp + (size_t)img * g.cand_stride + L.cand_off;
+
+  // (1) threshold on the FAST score for retainBest(2 * quota)
+  if (tid == 0) {
+    uint32_t thr = 0;
+    if (n > 2 * quota) {
+      const uint32_t* h = hist + (size_t)(img * g.nlevels + level) * 256;
+      uint32_t cum = 0;
+      for (int s = 255; s >= 0; --s) {
+        cum += h[s];
+        if (cum >= 2 * quota) { thr = (uint32_t)s; break; }
+      }
+    }
+    s_thr1 = thr;
+    s_cnt = 0;
+  }
+  __syncthreads();
+  const uint32_t thr1 = s_thr1;
+  // (2) survivors + Harris
+  if (quota > 0) {
+    for (uint32_t i = tid; i < n; i += kSelThreads) {
+      const uint32_t key = ck[i];
+      if ((key >> 24) < thr1) continue;
+      const int x = key & 0xfff, y = (key >> 12) & 0xfff;
+      const float r = harris_response(src + (size_t)y * L.pitch + x, L.pitch);
+      const uint32_t j = atomicAdd(&s_cnt, 1u);
+      sk[j] = key & 0xffffffu;
+      sr[j] = r;
+    }
+  }
+  __syncthreads();
+  const uint32_t n1 = s_cnt;
+  // (3) quota-th largest response (exact), ties kept
+  uint32_t thr_key = 0;
+  if (n1 > quota) {
+    if (tid == 0) { s_prefix = 0; s_k = quota; }
+    for (int pass = 3; pass >= 0; --pass) {
+      const int shift = pass * 8;
+      const uint32_t mask = (pass == 3) ? 0u : (0xffffffffu << (shift + 8));
+      if (tid < 256) s_hist[tid] = 0;
+      __syncthreads();
+      const uint32_t prefix = s_prefix;
+      for (uint32_t i = tid; i < n1; i += kSelThreads) {
+        const uint32_t k = f32_orderable(sr[i]);
+        if ((k & mask) == (prefix & mask)) atomicAdd(&s_hist[(k >> shift) & 255u], 1u);
+      }
+      __syncthreads();
+      if (tid == 0) {
+        uint32_t k = s_k;
+        int b = 255;
+        for (; b > 0; --b) {
+          if (s_hist[b] >= k) break;
+          k -= s_hist[b];
+        }
+        s_k = k;
+        s_prefix = prefix | ((uint32_t)b << shift);
+      }
+      __syncthreads();
+    }
+    thr_key = s_prefix;
+  }
+  // (4) keep, sort by (y, x), write
+  if (tid == 0) s_keep = 0;
+  for (int i = tid; i < g.sort_cap; i += kSelThreads) s_sort[i] = ~0ull;
+  __syncthreads();
+  for (uint32_t i = tid; i < n1; i += kSelThreads) {
+    const float r = sr[i];
+    if (f32_orderable(r) < thr_key) continue;
+    const uint32_t j = atomicAdd(&s_keep, 1u);
+    if (j < (uint32_t)g.sort_cap) s_sort[j] = ((unsigned long long)sk[i] << 32) | __float_as_uint(r);
+  }
+  __syncthreads();
+  const uint32_t nk_raw = s_keep;
+  const uint32_t nk = min(nk_raw, (uint32_t)L.kp_cap);
+  if (nk_raw > (uint32_t)L.kp_cap && tid == 0) atomicOr(&img_flags[img], 2u);
+  // bitonic sort (ascending) over the smallest power of two covering the kept items
+  uint32_t m = 1;
+  while (m < min(nk_raw, (uint32_t)g.sort_cap)) m <<= 1;
+  for (uint32_t k = 2; k <= m; k <<= 1) {
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t i = tid; i < m; i += kSelThreads) {
+        const uint32_t ixj = i ^ j;
+        if (ixj > i) {
+          const unsigned long long a = s_sort[i], b = s_sort[ixj];
+          const bool up = (i & k) == 0;
+          if ((a > b) == up) { s_sort[i] = b; s_sort[ixj] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  uint32_t* ok = lvl_key + (size_t)img * g.kp_stride + L.kp_off;
+  float* orr = lvl_resp + (size_t)img * g.kp_stride + L.kp_off;
+  for (uint32_t i = tid; i < nk; i += kSelThreads) {
+    const unsigned long long v = s_sort[i];
+    ok[i] = (uint32_t)(v >> 32);
+    orr[i] = __uint_as_float((uint32_t)v);
+  }
+  if (tid == 0) lvl_cnt[img * g.nlevels + level] = nk;
+}
+
+void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
+  dim3 grid(g.nlevels, n_img);
+  k_select<<<grid, kSelThreads, (size_t)g.sort_cap * 8, s>>>(g, b.pyr, b.cand_key, b.cand_cnt, b.hist, b.sel_key,
+                                                             b.sel_resp, b.lvl_key, b.lvl_resp, b.lvl_cnt,
+                                                             b.img_flags);
+  ++*launches;
+}
+
+// ------------------------------------------------------------------ K6: 7x7 sigma-2 blur (f32 FMA separable)
+constexpr int kBlurIW = kTileW + 8;   // staged columns x0-4 .. x0+67 (only -3..+66 used)
+constexpr int kBlurIH = kTileH + 6;   // rows y0-3 .. y0+34
+
+__global__ void __launch_bounds__(256)
+k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur) {
+  __shared__ __align__(16) uint8_t simg[kBlurIH * kBlurIW];
+  __shared__ float srow[kBlurIH * kTileW];
+  const int img = blockIdx.y;
+  const int level = find_level(g, blockIdx.x);
+  const LevelGeom& L = g.lv[level];
+  const int t = blockIdx.x - L.tile0;
+  const int x0 = (t % L.tiles_x) * kTileW, y0 = (t / L.tiles_x) * kTileH;
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
+  uint8_t* dst = blur + (size_t)img * g.pyr_stride + L.off;
+  const int tid = threadIdx.x;
+  const bool interior = x0 >= 4 && x0 + kTileW + 4 <= L.w && y0 >= 3 && y0 + kTileH + 3 <= L.h;
+  if (interior) {
+    for (int i = tid; i < kBlurIH * (kBlurIW / 4); i += 256) {
+      const int r = i / (kBlurIW / 4), cw = i % (kBlurIW / 4);
+      *reinterpret_cast<uint32_t*>(&simg[r * kBlurIW + cw * 4]) =
+          *reinterpret_cast<const uint32_t*>(src + (size_t)(y0 - 3 + r) * L.pitch + x0 - 4 + cw * 4);
+    }
+  } else {
+    for (int i = tid; i < kBlurIH * kBlurIW; i += 256) {
+      const int r = i / kBlurIW, c = i % kBlurIW;
+      const int y = reflect101(min(y0 - 3 + r, L.h + 2), L.h);
+      const int x = reflect101(min(x0 - 4 + c, L.w + 2), L.w);
+      simg[i] = src[(size_t)y * L.pitch + x];
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < kBlurIH * kTileW; i += 256) {
+    const int r = i / kTileW, c = i % kTileW;
+    const uint8_t* p = &simg[r * kBlurIW + c + 1];   // column x0 + c - 3
+    srow[i] = blur_row7((float)p[0], (float)p[1], (float)p[2], (float)p[3], (float)p[4], (float)p[5],
+                        (float)p[6]);
+  }
+  __syncthreads();
+  // each thread: 4 adjacent columns x 2 rows -> two 32-bit stores
+  {
+    const int cx = (tid % 16) * 4, ry = (tid / 16) * 2;
+#pragma unroll
+    for (int rr = 0; rr < 2; ++rr) {
+      const int r = ry + rr;
+      const int y = y0 + r;
+      uint32_t out = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float* q = &srow[r * kTileW + cx + k];
+        out |= (uint32_t)blur_col7(q[0], q[kTileW], q[2 * kTileW], q[3 * kTileW], q[4 * kTileW],
+                                   q[5 * kTileW], q[6 * kTileW]) << (8 * k);
+      }
+      if (y < L.h && x0 + cx < L.pitch)
+        *reinterpret_cast<uint32_t*>(dst + (size_t)y * L.pitch + x0 + cx) = out;
+    }
+  }
+}
+
+void launch_blur(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
+  dim3 grid(g.total_tiles, n_img);
+  k_blur<<<grid, 256, 0, s>>>(g, b.pyr, b.blur);
+  ++*launches;
+}
+
+// ------------------------------------------------------------------ K5/K7: orientation + rBRIEF + keypoint fields
+__global__ void __launch_bounds__(128)
+k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
+           const uint32_t* __restrict__ lvl_key, const float* __restrict__ lvl_resp,
+           const uint32_t* __restrict__ lvl_cnt, float* __restrict__ kp_x, float* __restrict__ kp_y,
+           float* __restrict__ kp_size, float* __restrict__ kp_angle, float* __restrict__ kp_resp,
+           int32_t* __restrict__ kp_oct, uint8_t* __restrict__ desc, int32_t* __restrict__ kp_n) {
+  const int img = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  // locate (level, index in level)
+  int level = -1, base = 0, total = 0;
+  for (int l = 0; l < g.nlevels; ++l) {
+    const int c = (int)lvl_cnt[img * g.nlevels + l];
+    if (level < 0 && i < total + c) { level = l; base = total; }
+    total += c;
+  }
+  if (i == 0) kp_n[img] = total;
+  if (level < 0) return;
+  const LevelGeom& L = g.lv[level];
+  const int j = i - base;
+  const uint32_t key = lvl_key[(size_t)img * g.kp_stride + L.kp_off + j];
+  const int x = key & 0xfff, y = (key >> 12) & 0xfff;
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
+  const uint8_t* bl = blur + (size_t)img * g.pyr_stride + L.off;
+  const float angle = ic_angle(src + (size_t)y * L.pitch + x, L.pitch);
+  const float px = f32_mul((float)x, L.scale), py = f32_mul((float)y, L.scale);
+  const size_t o = (size_t)img * g.kp_stride + i;
+  kp_x[o] = px;
+  kp_y[o] = py;
+  kp_size[o] = f32_mul(31.0f, L.scale);
+  kp_angle[o] = angle;
+  kp_resp[o] = lvl_resp[(size_t)img * g.kp_stride + L.kp_off + j];
+  kp_oct[o] = level;
+  // descriptor centre exactly as computeOrbDescriptors: cvRound(pt * (1.f / scale))
+  const float inv = f32_div(1.0f, L.scale);
+  const int cx = f32_rint(f32_mul(px, inv)), cy = f32_rint(f32_mul(py, inv));
+  uint32_t d[8];
+  brief256(bl + (size_t)cy * L.pitch + cx, L.pitch, angle, d);
+  uint4* dp = reinterpret_cast<uint4*>(desc + o * 32);
+  dp[0] = make_uint4(d[0], d[1], d[2], d[3]);
+  dp[1] = make_uint4(d[4], d[5], d[6], d[7]);
+}
+
+void launch_describe(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
+  dim3 grid((g.kp_stride + 127) / 128, n_img);
+  k_describe<<<grid, 128, 0, s>>>(g, b.pyr, b.blur, b.lvl_key, b.lvl_resp, b.lvl_cnt, b.kp_x, b.kp_y, b.kp_size,
+                                  b.kp_angle, b.kp_resp, b.kp_oct, b.desc, b.kp_n);
+  ++*launches;
+}
+
+int setup_orb_attributes(int sort_cap) {
+  return (int)cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_cap * 8);
+}
+
+}  // namespace rpe

@@ -1,0 +1,223 @@
+// orb_math.cuh — per-pixel / per-keypoint arithmetic of the ORB stage, bit-exact with what
+// cv2.ORB.detectAndCompute computes (reference call site: src/core/pose_estimator.py:85-91,
+// :108; arithmetic spec: SURVEY.md Appendix A.1-A.8).  All functions take a pointer to the
+// centre pixel and a row pitch so they work on global memory and shared-memory tiles alike.
+#pragma once
+#include "rpe_hd.cuh"
+
+namespace rpe {
+
+// ------------------------------------------------------------------ A.1 pyramid (resize)
+// One INTER_LINEAR_EXACT output pixel from host-built per-axis tap tables: ofs = left/top
+// source index, c1 = 8.8 weight of the right/bottom neighbour (c0 = 256 - c1).
+RPE_HD uint8_t resize_px(const uint8_t* src, int pitch, int sw, int sh, int x0, int cx1, int y0,
+                         int cy1) {
+  const int x1 = imin(x0 + 1, sw - 1), y1 = imin(y0 + 1, sh - 1);
+  const uint32_t cx0 = 256u - (uint32_t)cx1, cy0 = 256u - (uint32_t)cy1;
+  const uint8_t* r0 = src + (size_t)y0 * pitch;
+  const uint8_t* r1 = src + (size_t)y1 * pitch;
+  const uint32_t h0 = cx0 * r0[x0] + (uint32_t)cx1 * r0[x1];  // 8.8
+  const uint32_t h1 = cx0 * r1[x0] + (uint32_t)cx1 * r1[x1];
+  const uint32_t v = cy0 * h0 + (uint32_t)cy1 * h1;           // 16.16
+  const uint32_t o = (v + 32768u) >> 16;
+  return (uint8_t)(o > 255u ? 255u : o);
+}
+
+// ------------------------------------------------------------------ A.2 FAST-9/16
+// returns 0 for a non-corner, else score = max(a, b) - 1 (always >= threshold).
+RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
+  const int v = c[0];
+  int d[16];
+#define RPE_LD(k, dx, dy) d[k] = v - (int)c[(dy) * pitch + (dx)]
+#define RPE_PAIR(k)                                      \
+  pos = pos && ((d[k] > t) || (d[(k) + 8] > t));         \
+  neg = neg && ((d[k] < -t) || (d[(k) + 8] < -t));       \
+  if (!(pos || neg)) return 0;
+  bool pos = true, neg = true;
+  RPE_LD(0, 0, 3);  RPE_LD(8, 0, -3);   RPE_PAIR(0)
+  RPE_LD(4, 3, 0);  RPE_LD(12, -3, 0);  RPE_PAIR(4)
+  RPE_LD(2, 2, 2);  RPE_LD(10, -2, -2); RPE_PAIR(2)
+  RPE_LD(6, 2, -2); RPE_LD(14, -2, 2);  RPE_PAIR(6)
+  RPE_LD(1, 1, 3);  RPE_LD(9, -1, -3);  RPE_PAIR(1)
+  RPE_LD(3, 3, 1);  RPE_LD(11, -3, -1); RPE_PAIR(3)
+  RPE_LD(5, 3, -1); RPE_LD(13, -3, 1);  RPE_PAIR(5)
+  RPE_LD(7, 1, -3); RPE_LD(15, -1, 3);  RPE_PAIR(7)
+#undef RPE_LD
+#undef RPE_PAIR
+  uint32_t mp = 0, mn = 0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    mp |= (uint32_t)(d[k] > t) << k;
+    mn |= (uint32_t)(d[k] < -t) << k;
+  }
+  // 9 contiguous set bits on the 16-ring
+  uint32_t xp = mp | (mp << 16), xn = mn | (mn << 16);
+  uint32_t ap = xp & (xp >> 1); ap &= ap >> 2; ap &= ap >> 4; ap &= xp >> 8;
+  uint32_t an = xn & (xn >> 1); an &= an >> 2; an &= an >> 4; an &= xn >> 8;
+  if (((ap | an) & 0xffffu) == 0) return 0;
+  // score: a = max over arcs of min(d), b = max over arcs of min(-d) = -min over arcs of max(d)
+  int lo2[16], hi2[16], lo4[16], hi4[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    lo2[k] = imin(d[k], d[(k + 1) & 15]);
+    hi2[k] = imax(d[k], d[(k + 1) & 15]);
+  }
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    lo4[k] = imin(lo2[k], lo2[(k + 2) & 15]);
+    hi4[k] = imax(hi2[k], hi2[(k + 2) & 15]);
+  }
+  int a = -1000, bmin = 1000;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const int lo9 = imin(imin(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]);
+    const int hi9 = imax(imax(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]);
+    a = imax(a, lo9);
+    bmin = imin(bmin, hi9);
+  }
+  return imax(a, -bmin) - 1;
+}
+
+// ------------------------------------------------------------------ A.5 Harris response
+RPE_HD float harris_response(const uint8_t* c, int pitch) {
+  int a = 0, b = 0, cc = 0;
+  // 9x9 neighbourhood, rows -4..4; three-row sliding window
+  int r0[9], r1[9], r2[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) {
+    r0[i] = c[-4 * pitch + (i - 4)];
+    r1[i] = c[-3 * pitch + (i - 4)];
+  }
+#pragma unroll
+  for (int y = -3; y <= 3; ++y) {
+#pragma unroll
+    for (int i = 0; i < 9; ++i) r2[i] = c[(y + 1) * pitch + (i - 4)];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) {
+      const int Ix = (r1[i + 1] - r1[i - 1]) * 2 + (r0[i + 1] - r0[i - 1]) + (r2[i + 1] - r2[i - 1]);
+      const int Iy = (r2[i] - r0[i]) * 2 + (r2[i - 1] - r0[i - 1]) + (r2[i + 1] - r0[i + 1]);
+      a += Ix * Ix;
+      b += Iy * Iy;
+      cc += Ix * Iy;
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) { r0[i] = r1[i]; r1[i] = r2[i]; }
+  }
+  const float s = f32_div(1.0f, f32_mul(28.0f, 255.0f));   // 1.f/(4*7*255.f)
+  const float s4 = f32_mul(f32_mul(f32_mul(s, s), s), s);
+  const float fa = (float)a, fb = (float)b, fc = (float)cc;
+  const float apb = f32_add(fa, fb);
+  const float t1 = f32_mul(fa, fb);
+  const float t2 = f32_mul(fc, fc);
+  const float t3 = f32_mul(f32_mul(0.04f, apb), apb);
+  return f32_mul(f32_sub(f32_sub(t1, t2), t3), s4);
+}
+
+// ------------------------------------------------------------------ A.6 orientation
+RPE_DEFINE_TABLE(int8_t, kUmax, 16, {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3})
+
+RPE_HD float fast_atan2_deg(float y, float x) {
+  // cv::fastAtan2 scalar path: 7th-order odd polynomial, non-fused f32
+  const float k = 57.29577951308232f;  // (float)(180/CV_PI)
+  const float p1 = f32_mul(0.9997878412794807f, k), p3 = f32_mul(-0.3258083974640975f, k);
+  const float p5 = f32_mul(0.1555786518463281f, k), p7 = f32_mul(-0.04432655554792128f, k);
+  const float eps = 2.220446049250313e-16f;  // (float)DBL_EPSILON
+  const float ax = fabsf(x), ay = fabsf(y);
+  float a, c, c2;
+  if (ax >= ay) {
+    c = f32_div(ay, f32_add(ax, eps));
+    c2 = f32_mul(c, c);
+    a = f32_mul(f32_add(f32_mul(f32_add(f32_mul(f32_add(f32_mul(p7, c2), p5), c2), p3), c2), p1), c);
+  } else {
+    c = f32_div(ax, f32_add(ay, eps));
+    c2 = f32_mul(c, c);
+    a = f32_sub(90.0f, f32_mul(f32_add(f32_mul(f32_add(f32_mul(f32_add(f32_mul(p7, c2), p5), c2), p3), c2), p1), c));
+  }
+  if (x < 0) a = f32_sub(180.0f, a);
+  if (y < 0) a = f32_sub(360.0f, a);
+  return a;
+}
+
+RPE_HD float ic_angle(const uint8_t* c, int pitch) {
+  int m01 = 0, m10 = 0;
+  for (int u = -15; u <= 15; ++u) m10 += u * (int)c[u];
+  for (int v = 1; v <= 15; ++v) {
+    int vsum = 0;
+    const int d = RPE_TBL(kUmax)[v];
+    const uint8_t* pp = c + v * pitch;
+    const uint8_t* pm = c - v * pitch;
+    for (int u = -d; u <= d; ++u) {
+      const int vp = pp[u], vm = pm[u];
+      vsum += vp - vm;
+      m10 += u * (vp + vm);
+    }
+    m01 += v * vsum;
+  }
+  return fast_atan2_deg((float)m01, (float)m10);
+}
+
+// ------------------------------------------------------------------ A.8 blur taps
+// f32 bit patterns of getGaussianKernel(7, 2): k[0..3] (symmetric)
+#define RPE_BLUR_K0 0.0701593235135078430f /* 0x3d8fafb1 */
+#define RPE_BLUR_K1 0.1310748755931854248f /* 0x3e06387e */
+#define RPE_BLUR_K2 0.1907128244638442993f /* 0x3e434a39 */
+#define RPE_BLUR_K3 0.2161059379577636719f /* 0x3e5d4ae0 */
+
+// row pass on 7 consecutive u8: s = k0*x0; s = fma(k_j, x_j, s) left to right
+RPE_HD float blur_row7(float x0, float x1, float x2, float x3, float x4, float x5, float x6) {
+  float s = f32_mul(RPE_BLUR_K0, x0);
+  s = f32_fma(RPE_BLUR_K1, x1, s);
+  s = f32_fma(RPE_BLUR_K2, x2, s);
+  s = f32_fma(RPE_BLUR_K3, x3, s);
+  s = f32_fma(RPE_BLUR_K2, x4, s);
+  s = f32_fma(RPE_BLUR_K1, x5, s);
+  s = f32_fma(RPE_BLUR_K0, x6, s);
+  return s;
+}
+// column pass on 7 row-pass results r[-3..3]: symmetric pairing, then round + saturate
+RPE_HD uint8_t blur_col7(float r0, float r1, float r2, float r3, float r4, float r5, float r6) {
+  float s = f32_mul(RPE_BLUR_K3, r3);
+  s = f32_fma(RPE_BLUR_K2, f32_add(r2, r4), s);
+  s = f32_fma(RPE_BLUR_K1, f32_add(r1, r5), s);
+  s = f32_fma(RPE_BLUR_K0, f32_add(r0, r6), s);
+  int v = f32_rint(s);
+  return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
+}
+RPE_HD int reflect101(int i, int n) {
+  if (i < 0) i = -i;
+  if (i >= n) i = 2 * n - 2 - i;
+  return i;
+}
+
+// ------------------------------------------------------------------ A.8 steered rBRIEF
+static const int8_t kBriefPattern_host[1024] = {
+#include "orb_pattern.inc"
+};
+#if defined(__CUDACC__)
+static __device__ __constant__ int8_t kBriefPattern_dev[1024] = {
+#include "orb_pattern.inc"
+};
+#endif
+
+// c = blurred level at the keypoint centre; angle in degrees; out = 8 x u32 (32 bytes, LSB first)
+RPE_HD void brief256(const uint8_t* c, int pitch, float angle_deg, uint32_t out[8]) {
+  const float theta = f32_mul(angle_deg, 0.017453292519943295f);  // (float)(CV_PI/180)
+  const float a = (float)cos((double)theta), b = (float)sin((double)theta);
+  const int8_t* P = RPE_TBL(kBriefPattern);
+  for (int w = 0; w < 8; ++w) {
+    uint32_t bits = 0;
+    for (int j = 0; j < 32; ++j) {
+      const int8_t* p = P + 4 * (32 * w + j);
+      const float xa = (float)p[0], ya = (float)p[1], xb = (float)p[2], yb = (float)p[3];
+      const int ixa = f32_rint(f32_sub(f32_mul(xa, a), f32_mul(ya, b)));
+      const int iya = f32_rint(f32_add(f32_mul(xa, b), f32_mul(ya, a)));
+      const int ixb = f32_rint(f32_sub(f32_mul(xb, a), f32_mul(yb, b)));
+      const int iyb = f32_rint(f32_add(f32_mul(xb, b), f32_mul(yb, a)));
+      const int va = c[iya * pitch + ixa], vb = c[iyb * pitch + ixb];
+      bits |= (uint32_t)(va < vb) << j;
+    }
+    out[w] = bits;
+  }
+}
+
+}  // namespace rpe

@@ -1,0 +1,116 @@
+// rpe_device.cuh — device-side data layout shared by the kernels and the host engine.
+//
+// HBM layout (per handle; NI = 2 * max_pairs image slots, NP = max_pairs pair slots):
+//   pyr / blur   u8  [NI][pyr_stride]      all pyramid levels of one image back to back, each
+//                                          level 256-B aligned, row pitch = align16(w)
+//   cand_key     u32 [NI][cand_stride]     FAST+NMS candidates per level (score<<24 | y<<12 | x)
+//   cand_cnt     u32 [NI][L],  hist u32 [NI][L][256] (FAST-score histogram per level)
+//   sel_key/resp u32/f32 [NI][cand_stride] survivors of the first retainBest + Harris response
+//   lvl_key/resp u32/f32 [NI][kp_stride]   final per-level keypoints in (y, x) order; lvl_cnt [NI][L]
+//   kp_*         f32/i32 [NI][kp_stride]   final keypoints, canonical (octave, y, x) order; kp_n [NI]
+//   desc         u8  [NI][kp_stride][32]
+//   fwd1/fwd2/bwd1 u32 [NP][kp_stride]     packed (dist<<20 | index) nearest / second nearest
+//   m_q/m_t/m_d  i32 [NP][mcap], pts1/pts2 f32 [NP][mcap][2], npts f64 [NP][mcap][4], m_n [NP]
+//   E f64 [NP][9], rmask/pmask u8 [NP][mcap], rinfo i32 [NP][4], R/t/euler f64, status i32 [NP]
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/rpe.h"
+
+namespace rpe {
+
+struct LevelGeom {
+  int w, h, pitch;
+  int quota;
+  float scale;
+  uint32_t off;            // byte offset inside one image's pyramid slab
+  int cand_off, cand_cap;  // slice of the per-image candidate arrays
+  int kp_off, kp_cap;      // slice of the per-image per-level keypoint arrays
+  int xtab, ytab;          // tap-table offsets for producing this level from the previous one
+  int tile0, tiles_x, tiles_y;
+};
+
+struct OrbGeom {
+  int nlevels;
+  int fast_threshold;
+  int total_tiles;
+  int cand_stride;
+  int kp_stride;
+  int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)
+  size_t pyr_stride;
+  LevelGeom lv[RPE_MAX_LEVELS];
+};
+
+constexpr int kTileW = 64;
+constexpr int kTileH = 32;
+
+struct OrbBuffers {
+  uint8_t* pyr;
+  uint8_t* blur;
+  uint32_t* cand_key;
+  uint32_t* cand_cnt;
+  uint32_t* hist;
+  uint32_t* sel_key;
+  float* sel_resp;
+  uint32_t* lvl_key;
+  float* lvl_resp;
+  uint32_t* lvl_cnt;
+  uint32_t* img_flags;
+  const int2* taps;
+  float* kp_x; float* kp_y; float* kp_size; float* kp_angle; float* kp_resp;
+  int32_t* kp_oct;
+  uint8_t* desc;
+  int32_t* kp_n;
+};
+
+struct MatchBuffers {
+  uint32_t* fwd1; uint32_t* fwd2; uint32_t* bwd1;
+  int32_t* m_q; int32_t* m_t; int32_t* m_d; int32_t* m_n;
+  float* pts1; float* pts2;
+};
+
+struct GeomBuffers {
+  double* npts;     // [NP][mcap][4] normalised (x1, y1, x2, y2)
+  double* E;        // [NP][9]
+  uint8_t* rmask;   // [NP][mcap]
+  int32_t* rinfo;   // [NP][4] {ok, best count, iterations, hypotheses solved}
+  double* R; double* t; double* euler;
+  int32_t* pose_cnt;
+  uint8_t* pmask;
+  int32_t* status;
+  // optional per-hypothesis trace of pair 0 (stage entry point only)
+  int32_t* tr_subset; int32_t* tr_nmodels; int32_t* tr_counts; double* tr_models; int32_t tr_cap;
+};
+
+struct RansacParams {
+  double prob;
+  double threshold;   // pixels
+  int max_iters;
+  int euler_convention;
+};
+
+// packed nearest-neighbour key
+__host__ __device__ inline uint32_t pack_nn(uint32_t dist, uint32_t idx) { return (dist << 20) | idx; }
+
+// launchers (defined in the kernel .cu files)
+void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
+void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
+void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
+void launch_blur(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
+void launch_describe(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
+void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int mode,
+                  cudaStream_t s, int* launches);
+void launch_build_matches(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int mcap,
+                          int sort_cap, int n_pairs, int mode, double ratio, int max_matches,
+                          cudaStream_t s, int* launches);
+void launch_normalize(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, const double* dK,
+                      cudaStream_t s, int* launches);
+void launch_ransac(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, const double* dK,
+                   RansacParams rp, cudaStream_t s, int* launches);
+void launch_pose(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, RansacParams rp,
+                 const uint32_t* img_flags, const int32_t* kp_n, cudaStream_t s, int* launches);
+int setup_orb_attributes(int sort_cap);
+int setup_match_attributes(int sort_cap);
+int setup_geom_attributes();
+
+}  // namespace rpe
