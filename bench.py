@@ -1,0 +1,336 @@
+#!/usr/bin/env python
+"""bench.py — pose pairs/sec of the two-view hot path on N B200s (BASELINE.json metric).
+
+A "step" is one pass of the whole hot path (ORB x2 -> Hamming match -> 5-pt RANSAC -> recoverPose
+-> Euler) over one batch of synthetic pairs per GPU.  Workload = BASELINE config 3
+("synthetic 1280x720 pair batch, ORB 5000 features, BF-Hamming ratio 0.75, RANSAC 5-pt 2000
+iters"; other ORB parameters as the reference hard-codes them; max_matches 500).
+
+  value : device-timed throughput, inputs resident in HBM (rpe_estimate_batch_device)
+  e2e   : same metric through the host-buffer C ABI call (rpe_estimate_batch): pinned host
+          images -> H2D -> kernels -> D2H of R|t|euler|status, all inside the timed region
+  --impl reference : the reference's own CPU path (the same cv2 calls PoseEstimator.estimate
+          makes; oracle/reference_path.py) on the host cores, bounded sample per step.
+
+Pairs are independent, so N GPUs = N shards with no data-path collective ("scaling": "weak").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG = dict(W=1280, H=720, nfeatures=5000, nlevels=12, match_mode="ratio", ratio=0.75, max_matches=500,
+           ransac_max_iters=2000, synth_cfg=3)
+METRIC = "pose pairs/sec (ORB 5k -> BF-Hamming ratio 0.75 -> 5-pt RANSAC 2000 -> recoverPose), synthetic 1280x720"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=128, help="pairs per GPU per step")
+    ap.add_argument("--cpu-pairs", type=int, default=24, help="pairs in the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.lines: list[str] = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ data
+def make_batch(rank: int, B: int):
+    from oracle.synth import synth_batch, synth_K   # input generator (host), not the checker
+    frames = synth_batch(CFG["synth_cfg"], rank * 100000, B, CFG["W"], CFG["H"])
+    return frames, synth_K(CFG["W"], CFG["H"])
+
+
+def level_pixels():
+    """Pyramid pixel counts for the algorithmic-byte model."""
+    W, H, L = CFG["W"], CFG["H"], CFG["nlevels"]
+    sf = float(np.float32(1.1))
+    px = []
+    for l in range(L):
+        s = np.float32(sf ** l)
+        px.append(int(np.rint(np.float32(W) / s)) * int(np.rint(np.float32(H) / s)))
+    return px
+
+
+def stage_models(B: int, nkp_mean: float):
+    """Algorithmic bytes per STEP (B pairs = 2B images) for each stage."""
+    px = level_pixels()
+    P, P0, Plast = sum(px), px[0], px[-1]
+    n_img = 2 * B
+    N = nkp_mean
+    return {
+        "pyramid": n_img * ((P - Plast) + (P - P0)),
+        "fast": n_img * P,
+        "blur": n_img * 2 * P,
+        "describe": n_img * N * (32 + 24),
+        "match": B * (32 * 2 * N + 8 * 2 * N),
+    }
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+def cpu_reference_rate(n_pairs: int, first_pair: int = 900000):
+    """The reference's CPU path (cv2, all host threads) on a bounded sample of the same workload."""
+    import cv2
+    from oracle.reference_path import PathConfig, ReferencePath
+    from oracle.synth import synth_K, synth_pair
+    cv2.setNumThreads(-1)
+    K = synth_K(CFG["W"], CFG["H"])
+    ref = ReferencePath(K, PathConfig(nfeatures=CFG["nfeatures"], nlevels=CFG["nlevels"], match_mode=CFG["match_mode"],
+                                      ratio=CFG["ratio"], max_matches=CFG["max_matches"],
+                                      ransac_max_iters=CFG["ransac_max_iters"]))
+    pairs = [synth_pair(CFG["synth_cfg"], first_pair + i, CFG["W"], CFG["H"])[:2] for i in range(n_pairs)]
+    ref.estimate(*pairs[0])                       # warm-up call
+    t0 = time.perf_counter()
+    ok = 0
+    for a, b in pairs:
+        try:
+            ref.estimate(a, b)
+            ok += 1
+        except RuntimeError:
+            pass
+    dt = time.perf_counter() - t0
+    return n_pairs / dt, dt, cv2.getNumThreads(), ok
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    rates, t_all = [], 0.0
+    n = max(2, args.cpu_pairs // 4)
+    for _ in range(args.warmup):
+        cpu_reference_rate(2)
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        r, dt, threads, _ = cpu_reference_rate(n, 900000 + s * n)
+        rates.append(r); t_all += dt
+    value = args.steps * n / t_all
+    sample = f"{n} synthetic 1280x720 pairs per step x {args.steps} steps, cv2 threads={threads}"
+    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps,
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f32/f64", "data": "synthetic",
+           "config": {"workload": "cfg3: synthetic 1280x720 pair batch, ORB 5000, ratio 0.75, RANSAC 2000",
+                      "pairs_per_step": n, **{k: CFG[k] for k in ("nfeatures", "nlevels", "match_mode", "max_matches")}},
+           "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": sample},
+           "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
+    print(json.dumps(out), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ B200 arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    import rpe_b200
+    from rpe_b200 import _lib as L
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: the CUDA library has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B = args.batch
+    W, H = CFG["W"], CFG["H"]
+
+    frames_np, K = make_batch(rank, B)
+    host = torch.from_numpy(frames_np).pin_memory()
+    dev = host.cuda(non_blocking=False)
+    eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=W, max_height=H, max_pairs=B, nfeatures=CFG["nfeatures"],
+                                                nlevels=CFG["nlevels"], match_mode=CFG["match_mode"], ratio=CFG["ratio"],
+                                                max_matches=CFG["max_matches"], ransac_max_iters=CFG["ransac_max_iters"]),
+                          device=local)
+    stream = torch.cuda.Stream()
+    eng.set_stream(stream.cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        return eng.estimate_batch_device(dev.data_ptr(), H * W, B, H, W, W, K)
+
+    def step_host():
+        return eng.estimate_batch_interleaved(host.numpy(), K)
+
+    for _ in range(max(args.warmup, 1)):
+        out = step_device()
+    nkp = float(np.mean([eng.keypoints(i, v)["x"].shape[0] for i in range(min(B, 4)) for v in (0, 1)]))
+    ok_frac = float((out["status"] & 0xFF == 0).mean())
+
+    def timed(fn, profile):
+        eng.set_profiling(profile)
+        acc = {k: 0.0 for k in L.RPE_T_NAMES}
+        launches = 0
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(args.steps):
+                fn()
+                if profile:
+                    ms, ln = eng.stage_times()
+                    for k in acc:
+                        acc[k] += ms[k]
+                    launches += sum(ln.values())
+            e1.record(stream)
+        barrier()
+        ms_total = e0.elapsed_time(e1)
+        if world > 1:
+            tt = torch.tensor([ms_total], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms_total = float(tt.item())
+        eng.set_profiling(False)
+        return ms_total, acc, launches
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_dev, stage_ms, launches = timed(step_device, True)
+    clocks = sampler.stop() if rank == 0 else None
+    for _ in range(2):
+        step_host()
+    ms_e2e, _, _ = timed(step_host, False)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    total_pairs = world * args.steps * B
+    value = total_pairs / (ms_dev * 1e-3)
+    e2e = total_pairs / (ms_e2e * 1e-3)
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    model = stage_models(B, nkp)
+    stages = {}
+    for k, byts in model.items():
+        ms = stage_ms[k] / args.steps
+        gbs = byts / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        stages[k] = {"ms_per_step": ms, "algorithmic_bytes_per_step": int(byts), "gbs": gbs, "frac_hbm": gbs / hbm_peak}
+    for k in ("select", "match_sort", "ransac", "pose", "h2d", "d2h"):
+        stages[k] = {"ms_per_step": stage_ms[k] / args.steps}
+    # matcher extras: operand-stream-equivalent bytes and popc32 rate
+    mm = stages["match"]["ms_per_step"] * 1e-3
+    if mm > 0:
+        stages["match"]["operand_stream_gbs"] = B * 64 * nkp * nkp / mm / 1e9
+        stages["match"]["popc32_per_s"] = B * 8 * nkp * nkp / mm
+    kernel_stages = ["pyramid", "fast", "select", "blur", "describe", "match", "match_sort", "ransac", "pose"]
+    dom = max(kernel_stages, key=lambda k: stages[k]["ms_per_step"])
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+    except Exception:
+        pass
+    rf_stage = dom if dom in model else "match"
+    roofline = {"kernel": rf_stage, "bound": "hbm", "achieved": stages[rf_stage]["gbs"], "peak": hbm_peak,
+                "unit": "GB/s", "frac": stages[rf_stage]["frac_hbm"], "traffic": traffic, "peak_source": peak_src,
+                "dominant_stage": dom, "share_of_step": stages[dom]["ms_per_step"] / (ms_dev / args.steps),
+                "note": "achieved = algorithmic bytes per step (SURVEY 8d) / CUDA-event time of that stage; the "
+                        "matcher is INT-pipe (xor+popc) bound, see stages.match.popc32_per_s"}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        rate, dt, threads, ok = cpu_reference_rate(args.cpu_pairs)
+        cpu = {"value": rate, "unit": "pairs/s", "cores": threads, "kind": "port",
+               "sample": f"{args.cpu_pairs} synthetic 1280x720 cfg3 pairs in {dt:.1f}s, cv2 {threads} threads "
+                         f"(same cv2 calls as PoseEstimator.estimate)"}
+
+    out = {"metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "u8/i32 (ORB, match), f32 (Harris/angle/blur), f64 (RANSAC, pose)",
+           "data": "synthetic",
+           "config": {"workload": "cfg3: synthetic 1280x720 pair batch, ORB 5000 features (sf 1.1, 12 levels, FAST 15, "
+                                  "HARRIS), BF-Hamming knn2 + ratio 0.75, max_matches 500, RANSAC 5-pt 2000 iters",
+                      "pairs_per_gpu_per_step": B, "image_bytes_per_step": int(2 * B * H * W),
+                      "l2_policy": "inputs larger than L2 (236 MB of frames + 1.2 GB of pyramids per step)",
+                      "parallelism": f"{world} independent shards, no collective",
+                      "mean_keypoints_per_image": nkp, "ok_fraction": ok_frac},
+           "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": int(2 * B * H * W + 72),
+                   "d2h_bytes_per_step": int(B * (15 * 8 + 3 * 4)), "ms_per_step": ms_e2e / args.steps},
+           "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+           "stages": stages}
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,64 @@
+"""Deterministic synthetic image pairs for BASELINE configs 3-5.
+
+TEST / BENCH INFRASTRUCTURE (input generator; uses cv2 on the host for the texture upsampling
+and the homography warp).  The reference has no synthetic data; this is the generator the
+survey defines so that the CPU baseline and the GPU engine see byte-identical inputs.
+
+Per pair: seed = 1000*cfg + pair_idx.  View 1 = multi-octave noise texture scaled to [40, 200]
+plus floor(W*H/1500) filled axis-aligned rectangles; view 2 = view 1 warped by the homography
+induced by a small random motion (rvec ~ U(-0.03,0.03)^3, t ~ U(-0.1,0.1)^3) of a camera
+looking at the plane z = 5; K = [[0.9W,0,W/2],[0,0.9W,H/2],[0,0,1]].
+"""
+from __future__ import annotations
+
+import cv2
+import numpy as np
+
+
+def synth_K(W: int, H: int) -> np.ndarray:
+    return np.array([[0.9 * W, 0, W / 2.0], [0, 0.9 * W, H / 2.0], [0, 0, 1.0]])
+
+
+def synth_texture(rng: np.random.Generator, W: int, H: int) -> np.ndarray:
+    acc = np.zeros((H, W), np.float32)
+    for o in range(6):
+        h, w = H // (1 << o) + 2, W // (1 << o) + 2
+        layer = rng.standard_normal((h, w)).astype(np.float32)
+        acc += (2.0 ** (0.7 * o)) * cv2.resize(layer, (W, H), interpolation=cv2.INTER_CUBIC)
+    lo, hi = float(acc.min()), float(acc.max())
+    img = (40.0 + (acc - lo) * (160.0 / max(hi - lo, 1e-9))).astype(np.uint8)
+    for _ in range((W * H) // 1500):
+        x, y = int(rng.integers(0, W)), int(rng.integers(0, H))
+        s1, s2 = int(rng.integers(6, 60)), int(rng.integers(6, 60))
+        img[y:y + s2, x:x + s1] = int(rng.integers(0, 256))
+    return img
+
+
+def synth_motion(rng: np.random.Generator):
+    rvec = rng.uniform(-0.03, 0.03, 3)
+    t = rng.uniform(-0.1, 0.1, 3)
+    R, _ = cv2.Rodrigues(rvec)
+    return R, t
+
+
+def synth_pair(cfg: int, pair_idx: int, W: int, H: int):
+    """-> (view1 u8 HxW, view2 u8 HxW, K, R_gt, t_gt_unit)."""
+    rng = np.random.default_rng(1000 * cfg + pair_idx)
+    img1 = synth_texture(rng, W, H)
+    R, t = synth_motion(rng)
+    K = synth_K(W, H)
+    n = np.array([0.0, 0.0, 1.0])
+    Hm = K @ (R + np.outer(t, n) / 5.0) @ np.linalg.inv(K)
+    img2 = cv2.warpPerspective(img1, Hm, (W, H), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
+    return img1, img2, K, R, t / np.linalg.norm(t)
+
+
+def synth_batch(cfg: int, first_pair: int, n_pairs: int, W: int, H: int, out: np.ndarray | None = None):
+    """(2*n_pairs, H, W) uint8, view 1 of pair i at 2i, view 2 at 2i+1."""
+    if out is None:
+        out = np.empty((2 * n_pairs, H, W), np.uint8)
+    for i in range(n_pairs):
+        a, b, _, _, _ = synth_pair(cfg, first_pair + i, W, H)
+        out[2 * i] = a
+        out[2 * i + 1] = b
+    return out
