@@ -97,7 +97,7 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------------------ data
 def make_batch(rank: int, B: int):
-    from oracle.synth import synth_batch, synth_K   # input generator (host), not the checker
+    from rpe_b200.synth import synth_batch, synth_K   # input generator (host), not the checker
     frames = synth_batch(CFG["synth_cfg"], rank * 100000, B, CFG["W"], CFG["H"])
     return frames, synth_K(CFG["W"], CFG["H"])
 
@@ -133,7 +133,7 @@ def cpu_reference_rate(n_pairs: int, first_pair: int = 900000):
     """The reference's CPU path (cv2, all host threads) on a bounded sample of the same workload."""
     import cv2
     from oracle.reference_path import PathConfig, ReferencePath
-    from oracle.synth import synth_K, synth_pair
+    from rpe_b200.synth import synth_K, synth_pair
     cv2.setNumThreads(-1)
     K = synth_K(CFG["W"], CFG["H"])
     ref = ReferencePath(K, PathConfig(nfeatures=CFG["nfeatures"], nlevels=CFG["nlevels"], match_mode=CFG["match_mode"],

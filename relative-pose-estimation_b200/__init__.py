@@ -5,7 +5,8 @@ a hyphen; ``rpe_b200/`` at the repo root is the importable alias of this package
 from .engine import Engine, EngineConfig
 from .pose_estimator import PoseEstimator
 from .geometry import rotation_to_euler, euler_to_rotation, rotation_to_euler_yup, rotation_to_euler_zyx
-from . import _lib
+from .batch_processor import BatchProcessor
+from . import _lib, sharding, synth
 
-__all__ = ["Engine", "EngineConfig", "PoseEstimator", "rotation_to_euler", "euler_to_rotation",
+__all__ = ["Engine", "EngineConfig", "PoseEstimator", "BatchProcessor", "sharding", "rotation_to_euler", "euler_to_rotation",
            "rotation_to_euler_yup", "rotation_to_euler_zyx"]

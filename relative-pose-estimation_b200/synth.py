@@ -1,6 +1,6 @@
 """Deterministic synthetic image pairs for BASELINE configs 3-5.
 
-TEST / BENCH INFRASTRUCTURE (input generator; uses cv2 on the host for the texture upsampling
+BENCH / TEST INPUT GENERATOR (host-side; not on the hot path; uses cv2 on the host for the texture upsampling
 and the homography warp).  The reference has no synthetic data; this is the generator the
 survey defines so that the CPU baseline and the GPU engine see byte-identical inputs.
 

@@ -1,0 +1,123 @@
+"""The per-element arithmetic of the CUDA kernels (csrc/orb_math.cuh, geom_math.cuh), instantiated on
+the host by tests/hostcheck (TEST-ONLY, g++), against the oracle: bit-exact for integer / f32 work,
+tolerance for the FP64 geometry.  Catches arithmetic regressions on a box without a GPU; the GPU
+parity tests (test_gpu_parity.py) are the real gate."""
+import cv2
+import numpy as np
+import pytest
+from conftest import default_K, load_gray
+
+import _hostcheck as hc
+from oracle import geometry as og
+from oracle import matcher as om
+from oracle import orb as oo
+
+
+@pytest.fixture(scope="module")
+def img():
+    return load_gray("sim_000015.png")
+
+
+def test_resize_bit_exact(img):
+    x0, _, _, cx1 = oo.linear_exact_coeffs(640, 582)
+    y0, _, _, cy1 = oo.linear_exact_coeffs(480, 436)
+    got = hc.resize(img, 582, 436, x0, cx1, y0, cy1)
+    assert np.array_equal(got, oo.resize_linear_exact(img, 582, 436))
+
+
+def test_fast_scores_bit_exact(img):
+    assert np.array_equal(hc.fast_scores(img, 15), oo.fast_score_map(img, 15))
+    noise = np.random.default_rng(0).integers(0, 256, (64, 96), dtype=np.uint8)
+    for t in (1, 15, 60):
+        assert np.array_equal(hc.fast_scores(noise, t), oo.fast_score_map(noise, t))
+
+
+def test_harris_angle_bit_exact(img):
+    xs, ys, _ = oo.fast_candidates(img, 15)
+    assert len(xs) > 1000
+    assert np.array_equal(hc.harris(img, xs, ys).view(np.uint32), oo.harris_response(img, xs, ys).view(np.uint32))
+    assert np.array_equal(hc.angle(img, xs, ys).view(np.uint32), oo.ic_angle(img, xs, ys).view(np.uint32))
+    rng = np.random.default_rng(1)
+    y, x = rng.integers(-5000, 5000, 5000).astype(np.float32), rng.integers(-5000, 5000, 5000).astype(np.float32)
+    assert np.array_equal(hc.atan2(y, x), oo.fast_atan2(y, x))
+
+
+def test_blur_and_brief_bit_exact(img):
+    bl = oo.blur7(img)
+    assert np.array_equal(hc.blur(img), bl)
+    xs, ys, _ = oo.fast_candidates(img, 15)
+    ang = oo.ic_angle(img, xs, ys)
+    want = oo.brief_descriptors(bl, xs.astype(np.float32), ys.astype(np.float32), ang, np.float32(1.0))
+    assert np.array_equal(hc.brief(bl, xs, ys, ang), want)
+
+
+def test_rng_and_iteration_update():
+    rng = og.CvRNG()
+    want = [og.draw_subset(rng, 500) for _ in range(64)]
+    assert hc.subsets(500, 64).tolist() == want
+    rng = og.CvRNG()
+    assert hc.subsets(7, 32).tolist() == [og.draw_subset(rng, 7) for _ in range(32)]    # many redraws
+    for ep in (0.0, 0.1, 76 / 500, 0.5, 0.9, 0.999, 1.0):
+        for mx in (12, 1000, 2000):
+            assert hc.update_iters(0.999, ep, 5, mx) == og.ransac_update_num_iters(0.999, ep, 5, mx)
+
+
+def _points():
+    r1 = oo.orb_detect_and_compute(load_gray("sim_000000.png"))
+    r2 = oo.orb_detect_and_compute(load_gray("sim_000015.png"))
+    m = om.sort_and_cut(om.match_crosscheck(r1.desc, r2.desc), 500)
+    p1 = np.stack([r1.x[m[:, 0]], r1.y[m[:, 0]]], 1).astype(np.float32)
+    p2 = np.stack([r2.x[m[:, 1]], r2.y[m[:, 1]]], 1).astype(np.float32)
+    return p1, p2
+
+
+def test_five_point_and_sampson():
+    p1, p2 = _points()
+    K = default_K()
+    x1, x2 = og.normalize_points(p1, K), og.normalize_points(p2, K)
+    rng = og.CvRNG()
+    thr = np.float32((1.0 / ((K[0, 0] + K[1, 1]) / 2)) ** 2)
+    for _ in range(10):
+        s = og.draw_subset(rng, len(x1))
+        mine, want = hc.five_point(x1[s], x2[s]), og.five_point_models(x1[s], x2[s])
+        assert len(mine) == len(want)
+        for E in mine:
+            assert abs(np.linalg.norm(E) - 1) < 1e-9
+            res = np.einsum("ni,ij,nj->n", np.c_[x2[s], np.ones(5)], E, np.c_[x1[s], np.ones(5)])
+            assert np.abs(res).max() < 1e-9
+            T = min(want, key=lambda W: min(np.abs(E - W).max(), np.abs(E + W).max()))
+            c1 = int((hc.sampson(E, x1, x2) <= thr).sum())
+            c2 = int((og.sampson_error_f32(T, x1, x2) <= thr).sum())
+            assert abs(c1 - c2) <= 3
+    E = want[0]
+    assert np.array_equal(hc.sampson(E, x1, x2), og.sampson_error_f32(E, x1, x2))
+
+
+def test_decompose_cheirality_euler():
+    p1, p2 = _points()
+    K = default_K()
+    E, _ = cv2.findEssentialMat(p1, p2, K, method=cv2.RANSAC, prob=0.999, threshold=1.0)
+    R1, R2, t = hc.decompose(E)
+    o1, o2, ot = og.decompose_essential(E)
+    cands = [o1, o2]
+    for R in (R1, R2):
+        assert min(np.abs(R - C).max() for C in cands) < 1e-12 and abs(np.linalg.det(R) - 1) < 1e-12
+    assert min(np.abs(t - ot).max(), np.abs(t + ot).max()) < 1e-12
+    n_cv, R_cv, t_cv, mask_cv = cv2.recoverPose(E, p1, p2, K)
+    x1, x2 = og.normalize_points(p1, K), og.normalize_points(p2, K)
+    ok = hc.cheirality(R_cv, t_cv, x1, x2)
+    assert np.array_equal(ok, mask_cv.ravel() > 0) and int(ok.sum()) == n_cv
+    for conv, name in ((0, "yup"), (1, "zyx")):
+        assert np.allclose(hc.euler(R_cv, conv), og.rotation_to_euler(R_cv, name), atol=1e-12)
+    gimbal = np.array([[1.0, 0, 0], [0, 0, -1], [0, 1, 0]])          # pitch = +90 deg
+    assert np.allclose(hc.euler(gimbal, 0), og.rotation_to_euler_yup(gimbal), atol=1e-12)
+
+
+def test_solve_poly10_against_numpy_roots():
+    rng = np.random.default_rng(5)
+    for _ in range(5):
+        roots = np.concatenate([rng.uniform(-3, 3, 4), (lambda z: np.r_[z, z.conj()])(rng.uniform(-2, 2, 3) + 1j * rng.uniform(0.2, 2, 3))])
+        c = np.real(np.poly(roots))[::-1].copy()                     # c[i] * x^i
+        got = hc.solve_poly10(c)
+        for r in roots:
+            assert np.abs(got - r).min() < 1e-7

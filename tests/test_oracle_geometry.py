@@ -1,0 +1,100 @@
+"""Pins the geometry oracle (oracle/geometry.py): OpenCV's RANSAC driver hypothesis-for-hypothesis,
+the five-point solver, recoverPose and the reference's Euler helpers (golden.json)."""
+import json
+import os
+
+import cv2
+import numpy as np
+from conftest import GOLDEN, load_gray
+
+from oracle import geometry as og
+from oracle import matcher as om
+from oracle import orb as oo
+
+G = json.load(open(os.path.join(GOLDEN, "golden.json")))
+
+
+def _points():
+    r1 = oo.orb_detect_and_compute(load_gray("sim_000000.png"))
+    r2 = oo.orb_detect_and_compute(load_gray("sim_000015.png"))
+    m = om.sort_and_cut(om.match_crosscheck(r1.desc, r2.desc), 500)
+    p1 = np.stack([r1.x[m[:, 0]], r1.y[m[:, 0]]], 1).astype(np.float32)
+    p2 = np.stack([r2.x[m[:, 1]], r2.y[m[:, 1]]], 1).astype(np.float32)
+    return p1, p2, np.array(G["pairs"][0]["K"])
+
+
+def _cv_minimal(x1, x2):
+    """cv2 with exactly 5 points returns every root of its minimal solver stacked."""
+    E, _ = cv2.findEssentialMat(x1.astype(np.float64), x2.astype(np.float64), np.eye(3), method=cv2.RANSAC)
+    return [] if E is None else [E[3 * i:3 * i + 3] for i in range(E.shape[0] // 3)]
+
+
+def test_rng_subsets_known_answer():
+    rng = og.CvRNG()
+    got = [og.draw_subset(rng, 500) for _ in range(8)]
+    assert got == G["known"]["rng_subsets_500"]
+    assert got[:3] == [[105, 4, 440, 173, 331], [12, 301, 280, 73, 110], [485, 494, 46, 149, 418]]
+
+
+def test_update_num_iters():
+    assert og.ransac_update_num_iters(0.999, 0.0, 5, 1000) == 0
+    assert og.ransac_update_num_iters(0.999, 1.0, 5, 1000) == 1000
+    assert og.ransac_update_num_iters(0.999, 76 / 500, 5, 1000) == 12      # the cfg1 golden stop (424 inliers)
+    assert og.ransac_update_num_iters(0.999, 0.5, 5, 1000) == 218
+
+
+def test_ransac_driver_identical_to_cv2_with_cv2_solver():
+    p1, p2, K = _points()
+    E_cv, mask_cv = cv2.findEssentialMat(p1, p2, K, method=cv2.RANSAC, prob=0.999, threshold=1.0)
+    tr = []
+    E, mask = og.find_essential_ransac(p1, p2, K, solver=_cv_minimal, trace=tr)
+    assert np.array_equal(mask, mask_cv.ravel()) and int(mask.sum()) == G["pairs"][0]["canonical"]["ransac_inliers"]
+    assert np.abs(E - E_cv).max() < 1e-9
+    assert np.abs(E_cv - np.array(G["pairs"][0]["canonical"]["E"])).max() < 1e-9
+    assert len(tr) == 12
+
+
+def test_numpy_five_point_and_full_ransac():
+    p1, p2, K = _points()
+    x1, x2 = og.normalize_points(p1, K), og.normalize_points(p2, K)
+    rng = og.CvRNG()
+    for _ in range(6):
+        s = og.draw_subset(rng, len(x1))
+        mine, theirs = og.five_point_models(x1[s], x2[s]), _cv_minimal(x1[s], x2[s])
+        assert len(mine) == len(theirs)
+        for E in mine:
+            assert abs(np.linalg.norm(E) - 1) < 1e-9
+            assert min(min(np.abs(E - T).max(), np.abs(E + T).max()) for T in theirs) < 1e-4   # roots of an ill-conditioned degree-10 polynomial
+            assert np.abs(np.einsum("ni,ij,nj->n", np.c_[x2[s], np.ones(5)], E, np.c_[x1[s], np.ones(5)])).max() < 1e-9
+    E, mask = og.find_essential_ransac(p1, p2, K)
+    _, mask_cv = cv2.findEssentialMat(p1, p2, K, method=cv2.RANSAC, prob=0.999, threshold=1.0)
+    m, c = mask.astype(bool), mask_cv.ravel().astype(bool)
+    assert (m & c).sum() / (m | c).sum() >= 0.95
+
+
+def test_recover_pose_vs_cv2_and_golden():
+    p1, p2, K = _points()
+    g = G["pairs"][0]["canonical"]
+    E = np.array(g["E"])
+    n_cv, R_cv, t_cv, mask_cv = cv2.recoverPose(E, p1, p2, K)
+    n, R, t, mask = og.recover_pose(E, p1, p2, K)
+    assert n == n_cv == g["inliers"] and np.array_equal(mask, mask_cv.ravel())
+    assert np.abs(R - R_cv).max() < 1e-12 and np.abs(t - t_cv).max() < 1e-12
+    assert np.abs(R - np.array(g["R"])).max() < 1e-9 and np.abs(t.ravel() - np.array(g["t"])).max() < 1e-9
+
+
+def test_degenerate_inputs():
+    K = np.array(G["pairs"][0]["K"])
+    pts = np.random.default_rng(0).uniform(0, 400, (4, 2)).astype(np.float32)
+    E, mask = og.find_essential_ransac(pts, pts + 1, K)
+    assert E is None and mask.shape == (4,)
+
+
+def test_euler_equals_reference_helpers():
+    for e in G["known"]["euler"]:
+        got = og.rotation_to_euler(np.array(e["R"]), e["convention"])
+        assert np.allclose(got, e["ypr_out"], atol=1e-10), e
+    for p in G["pairs"]:
+        R = np.array(p["reference"]["R"])
+        assert np.allclose(og.rotation_to_euler_yup(R), p["reference"]["euler_yup"], atol=1e-10)
+        assert np.allclose(og.rotation_to_euler_zyx(R), p["reference"]["euler_zyx"], atol=1e-10)
