@@ -119,7 +119,7 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
   g.nlevels = c.nlevels;
   g.fast_threshold = c.fast_threshold;
   size_t off = 0;
-  int cand_off = 0, kp_off = 0, tile0 = 0, max_kp_cap = 1;
+  int cand_off = 0, kp_off = 0, tile0 = 0, ftile0 = 0, max_kp_cap = 1;
   G.taps.clear();
   for (int l = 0; l < c.nlevels; ++l) {
     LevelGeom& L = g.lv[l];
@@ -133,12 +133,19 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
     max_kp_cap = std::max(max_kp_cap, L.kp_cap);
     L.tiles_x = (L.w + kTileW - 1) / kTileW; L.tiles_y = (L.h + kTileH - 1) / kTileH;
     L.tile0 = tile0; tile0 += L.tiles_x * L.tiles_y;
+    // FAST tiles cover x, y in [kFastOrigin, size - 31): keypoints live in [31, size - 31) and their
+    // NMS neighbours in [30, size - 30); levels narrower than 63 px have no tiles at all
+    const int fw = L.w - 31 - kFastOrigin, fh = L.h - 31 - kFastOrigin;
+    L.ftiles_x = fw > 0 && fh > 0 ? (fw + kFastTW - 1) / kFastTW : 0;
+    L.ftiles_y = fw > 0 && fh > 0 ? (fh + kFastTH - 1) / kFastTH : 0;
+    L.ftile0 = ftile0; ftile0 += L.ftiles_x * L.ftiles_y;
     if (l > 0) {
       L.xtab = (int)G.taps.size(); linear_exact_taps(w[l - 1], w[l], G.taps);
       L.ytab = (int)G.taps.size(); linear_exact_taps(h[l - 1], h[l], G.taps);
     }
   }
   g.total_tiles = tile0;
+  g.total_ftiles = ftile0;
   g.cand_stride = cand_off;
   g.kp_stride = kp_off;
   g.sort_cap = pow2_ge(max_kp_cap);

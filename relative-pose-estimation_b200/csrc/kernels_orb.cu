@@ -50,61 +50,103 @@ __device__ __forceinline__ int find_level(const OrbGeom& g, int tile) {
 }
 
 // ------------------------------------------------------------------ K2: FAST-9 + 3x3 NMS + border
-// One CTA = one 64x32 tile of one level of one image.  The image tile (+4 halo) is staged in
-// shared memory with 32-bit loads; scores for the tile (+1 halo) are kept in shared memory for
-// the NMS; survivors inside the 31-px border are appended to the level's candidate list and
-// counted in its score histogram.
-constexpr int kFastIW = kTileW + 8;   // 72
-constexpr int kFastIH = kTileH + 8;   // 40
-constexpr int kFastSW = kTileW + 4;   // 68 (pitch of the score tile; 66 used)
-constexpr int kFastSH = kTileH + 2;   // 34
+// One CTA = one 128x32 tile of one level of one image, in four phases:
+//  (1) stage the tile (+halo) in shared memory with 32-bit loads;
+//  (2) branch-free packed pre-test, four pixels per thread-step: the two opposite-pair tests
+//      on the compass points of the ring (a 9-arc contains one point of each opposite pair),
+//      done on bytes packed in a word (per-byte unsigned compares through 7-bit adds); the
+//      ~3 % of pixels that pass are compacted into a shared-memory queue;
+//  (3) one thread per queued pixel: exact FAST-9 test + score (fast9_score), score tile in smem;
+//  (4) one thread per scored corner: strict 3x3 NMS on the score tile, 31-px border filter,
+//      append (score<<24 | y<<12 | x) to the level's candidate list + score histogram.
+constexpr int kFastIP = kFastTW + 16;        // image tile pitch in bytes: x0-8 .. x0+135
+constexpr int kFastIH = kFastTH + 8;         // rows y0-4 .. y0+35
+constexpr int kFastSP = kFastTW + 8;         // score tile pitch: x0-4 .. x0+131
+constexpr int kFastSH = kFastTH + 2;         // rows y0-1 .. y0+32
+constexpr int kFastQX = kFastSP / 4;         // quads per score row (34)
 
 __global__ void __launch_bounds__(256)
 k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand_key,
        uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
-  __shared__ __align__(16) uint8_t simg[kFastIH * kFastIW];
-  __shared__ uint8_t ssc[kFastSH * kFastSW];
+  __shared__ __align__(16) uint8_t simg[kFastIH * kFastIP];
+  __shared__ __align__(16) uint8_t ssc[kFastSH * kFastSP];
+  __shared__ uint16_t s_queue[kFastSH * kFastSP];
+  __shared__ uint32_t s_qn;
   const int img = blockIdx.y;
-  const int level = find_level(g, blockIdx.x);
+  int level = 0;
+#pragma unroll 1
+  for (int i = 1; i < g.nlevels; ++i)
+    if ((int)blockIdx.x >= g.lv[i].ftile0) level = i;
   const LevelGeom& L = g.lv[level];
-  const int t = blockIdx.x - L.tile0;
-  const int x0 = (t % L.tiles_x) * kTileW, y0 = (t / L.tiles_x) * kTileH;
+  const int t = blockIdx.x - L.ftile0;
+  const int x0 = kFastOrigin + (t % L.ftiles_x) * kFastTW, y0 = kFastOrigin + (t / L.ftiles_x) * kFastTH;
   const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
   const int tid = threadIdx.x;
+  const int thr = g.fast_threshold;
 
-  // stage (x0-4 .. x0+68) x (y0-4 .. y0+36) as 18 words x 40 rows
-  for (int i = tid; i < kFastIH * (kFastIW / 4); i += 256) {
-    const int r = i / (kFastIW / 4), cw = i % (kFastIW / 4);
-    const int y = y0 - 4 + r, x = x0 - 4 + cw * 4;
+  // (1) stage + clear
+  for (int i = tid; i < kFastIH * (kFastIP / 4); i += 256) {
+    const int r = i / (kFastIP / 4), cw = i % (kFastIP / 4);
+    const int y = y0 - 4 + r, x = x0 - 8 + cw * 4;
     uint32_t v = 0;
-    if (y >= 0 && y < L.h && x >= 0 && x < L.pitch)
-      v = *reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch + x);
-    *reinterpret_cast<uint32_t*>(&simg[r * kFastIW + cw * 4]) = v;
+    if (y >= 0 && y < L.h && x < L.pitch) v = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch + x));
+    reinterpret_cast<uint32_t*>(simg)[i] = v;
+  }
+  for (int i = tid; i < kFastSH * kFastSP / 4; i += 256) reinterpret_cast<uint32_t*>(ssc)[i] = 0;
+  if (tid == 0) s_qn = 0;
+  __syncthreads();
+
+  // (2) packed pre-test.  Scores are only ever needed for x in [30, w-30), y in [30, h-30).
+  const int xlo = max(30, x0 - 1), xhi = min(L.w - 30, x0 + kFastTW + 1);
+  const int ylo = max(30, y0 - 1), yhi = min(L.h - 30, y0 + kFastTH + 1);
+  const uint32_t t4 = (uint32_t)min(thr, 127) * 0x01010101u;
+  const uint32_t* wimg = reinterpret_cast<const uint32_t*>(simg);
+  for (int i = tid; i < kFastSH * kFastQX; i += 256) {
+    const int sr = i / kFastQX, qx = i % kFastQX;
+    const int y = y0 - 1 + sr;
+    if (y < ylo || y >= yhi) continue;
+    const uint32_t* row = wimg + (sr + 3) * (kFastIP / 4) + qx;
+    const uint32_t Lw = row[0], C = row[1], Rw = row[2];
+    const uint32_t U = row[1 - 3 * (kFastIP / 4)], D = row[1 + 3 * (kFastIP / 4)];
+    uint32_t cand = fast_compass4(Lw, C, Rw, U, D, t4);
+    if (cand == 0) continue;
+    const int xq = x0 - 4 + 4 * qx;
+    const int lo = min(max(xlo - xq, 0), 4), hi = min(max(xhi - xq, 0), 4);
+    const uint32_t vmask = (uint32_t)(0x80808080ull << (8 * lo)) & (uint32_t)(0x80808080ull >> (8 * (4 - hi)));
+    cand &= vmask;
+    if (cand == 0) continue;
+    uint32_t pos = atomicAdd(&s_qn, (uint32_t)__popc(cand));
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (cand & (0x80u << (8 * j))) s_queue[pos++] = (uint16_t)((sr << 8) | (4 * qx + j));
   }
   __syncthreads();
-  // scores on (x0-1 .. x0+64) x (y0-1 .. y0+32)
-  for (int i = tid; i < kFastSH * (kTileW + 2); i += 256) {
-    const int sy = i / (kTileW + 2), sx = i % (kTileW + 2);
-    const int x = x0 - 1 + sx, y = y0 - 1 + sy;
-    int sc = 0;
-    if (x >= 3 && x < L.w - 3 && y >= 3 && y < L.h - 3)
-      sc = fast9_score(&simg[(sy + 3) * kFastIW + sx + 3], kFastIW, g.fast_threshold);
-    ssc[sy * kFastSW + sx] = (uint8_t)sc;
+  const int qn = (int)s_qn;
+
+  // (3) exact test + score of the queued pixels
+  for (int i = tid; i < qn; i += 256) {
+    const int e = s_queue[i];
+    const int sr = e >> 8, c = e & 255;
+    const int sc = fast9_score(&simg[(sr + 3) * kFastIP + c + 4], kFastIP, thr);
+    if (sc > 0) ssc[sr * kFastSP + c] = (uint8_t)sc;
   }
   __syncthreads();
-  // NMS + border filter + append
+
+  // (4) NMS + border filter + append
   uint32_t* cnt = cand_cnt + img * g.nlevels + level;
   uint32_t* hst = hist + (size_t)(img * g.nlevels + level) * 256;
   uint32_t* out = cand_key + (size_t)img * g.cand_stride + L.cand_off;
-  for (int i = tid; i < kTileW * kTileH; i += 256) {
-    const int ty = i / kTileW, tx = i % kTileW;
-    const uint8_t* c = &ssc[(ty + 1) * kFastSW + tx + 1];
-    const int s = c[0];
+  for (int i = tid; i < qn; i += 256) {
+    const int e = s_queue[i];
+    const int sr = e >> 8, c = e & 255;
+    if (sr < 1 || sr > kFastTH || c < 4 || c >= 4 + kFastTW) continue;
+    const uint8_t* p = &ssc[sr * kFastSP + c];
+    const int s = p[0];
     if (s == 0) continue;
-    const int x = x0 + tx, y = y0 + ty;
+    const int x = x0 - 4 + c, y = y0 - 1 + sr;
     if (x < 31 || x >= L.w - 31 || y < 31 || y >= L.h - 31) continue;
-    const bool keep = s > c[-kFastSW - 1] && s > c[-kFastSW] && s > c[-kFastSW + 1] && s > c[-1] &&
-                      s > c[1] && s > c[kFastSW - 1] && s > c[kFastSW] && s > c[kFastSW + 1];
+    const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
+                      s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
     if (!keep) continue;
     const uint32_t pos = atomicAdd(cnt, 1u);
     if (pos < (uint32_t)L.cand_cap) out[pos] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
@@ -113,7 +155,8 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint3
 }
 
 void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
-  dim3 grid(g.total_tiles, n_img);
+  if (g.total_ftiles == 0) return;
+  dim3 grid(g.total_ftiles, n_img);
   k_fast<<<grid, 256, 0, s>>>(g, b.pyr, b.cand_key, b.cand_cnt, b.hist);
   ++*launches;
 }

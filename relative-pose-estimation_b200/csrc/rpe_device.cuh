@@ -27,13 +27,15 @@ struct LevelGeom {
   int cand_off, cand_cap;  // slice of the per-image candidate arrays
   int kp_off, kp_cap;      // slice of the per-image per-level keypoint arrays
   int xtab, ytab;          // tap-table offsets for producing this level from the previous one
-  int tile0, tiles_x, tiles_y;
+  int tile0, tiles_x, tiles_y;     // 64 x 32 tiles (blur)
+  int ftile0, ftiles_x, ftiles_y;  // 128 x 32 tiles restricted to the rows/cols FAST needs
 };
 
 struct OrbGeom {
   int nlevels;
   int fast_threshold;
   int total_tiles;
+  int total_ftiles;
   int cand_stride;
   int kp_stride;
   int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)
@@ -43,6 +45,9 @@ struct OrbGeom {
 
 constexpr int kTileW = 64;
 constexpr int kTileH = 32;
+constexpr int kFastTW = 128;
+constexpr int kFastTH = 32;
+constexpr int kFastOrigin = 28;  // FAST tiles start at x = y = 28: only scores in [30, size-30) can matter
 
 struct OrbBuffers {
   uint8_t* pyr;

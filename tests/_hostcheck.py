@@ -50,6 +50,13 @@ def fast_scores(img, t):
     return out
 
 
+def fast_compass(img, t):
+    img = np.ascontiguousarray(img)
+    out = np.zeros(img.shape, np.uint8)
+    lib().hc_fast_compass(_p(img), img.shape[1], img.shape[0], int(t), _p(out))
+    return out
+
+
 def harris(img, xs, ys):
     img = np.ascontiguousarray(img)
     xs = np.ascontiguousarray(xs, np.int32); ys = np.ascontiguousarray(ys, np.int32)

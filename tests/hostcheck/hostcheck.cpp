@@ -19,6 +19,19 @@ void hc_fast_scores(const uint8_t* img, int w, int h, int t, int* out) {
   for (int y = 3; y < h - 3; ++y)
     for (int x = 3; x < w - 3; ++x) out[y * w + x] = fast9_score(img + y * w + x, w, t);
 }
+// packed pre-test on every aligned quad of rows 3..h-4 / cols 4..w-8: out[y*w+x] = 1 if it passes
+void hc_fast_compass(const uint8_t* img, int w, int h, int t, uint8_t* out) {
+  memset(out, 0, (size_t)w * h);
+  const uint32_t t4 = (uint32_t)t * 0x01010101u;
+  for (int y = 3; y < h - 3; ++y)
+    for (int x = 4; x + 8 <= w; x += 4) {
+      uint32_t Lw, C, Rw, U, D;
+      memcpy(&Lw, img + y * w + x - 4, 4); memcpy(&C, img + y * w + x, 4); memcpy(&Rw, img + y * w + x + 4, 4);
+      memcpy(&U, img + (y - 3) * w + x, 4); memcpy(&D, img + (y + 3) * w + x, 4);
+      const uint32_t c = fast_compass4(Lw, C, Rw, U, D, t4);
+      for (int j = 0; j < 4; ++j) out[y * w + x + j] = (c >> (8 * j + 7)) & 1;
+    }
+}
 void hc_harris(const uint8_t* img, int w, const int* xs, const int* ys, int n, float* out) {
   for (int i = 0; i < n; ++i) out[i] = harris_response(img + ys[i] * w + xs[i], w);
 }
