@@ -5,6 +5,7 @@
 // (FAST, blur) cover all pyramid levels in one launch through a flat tile table.
 #include "rpe_device.cuh"
 #include "orb_math.cuh"
+#include "tma.cuh"
 
 namespace rpe {
 
@@ -50,28 +51,30 @@ __device__ __forceinline__ int find_level(const OrbGeom& g, int tile) {
 }
 
 // ------------------------------------------------------------------ K2: FAST-9 + 3x3 NMS + border
-// One CTA = one 128x32 tile of one level of one image, in four phases:
-//  (1) stage the tile (+halo) in shared memory with 32-bit loads;
-//  (2) branch-free packed pre-test, four pixels per thread-step: the two opposite-pair tests
-//      on the compass points of the ring (a 9-arc contains one point of each opposite pair),
-//      done on bytes packed in a word (per-byte unsigned compares through 7-bit adds); the
-//      ~3 % of pixels that pass are compacted into a shared-memory queue;
-//  (3) one thread per queued pixel: exact FAST-9 test + score (fast9_score), score tile in smem;
-//  (4) one thread per scored corner: strict 3x3 NMS on the score tile, 31-px border filter,
+// One CTA (8 warps) = one 120x30 tile of one level of one image; the scored region (tile + 1)
+// is 32 rows x 32 aligned pixel quads, one warp per row, four rows per warp.
+//  (1) TMA: one bulk copy per image row of the tile (+halo) into shared memory (UBLKCP);
+//  (2) branch-free packed pre-test, four pixels per thread (fast_pretest4); the few per cent
+//      of pixels that pass are compacted into a shared-memory queue;
+//  (3a) one thread per queued pixel: exact FAST-9 corner test -> corner queue;
+//  (3b) one thread per corner: score (min/max network) -> score tile in shared memory;
+//  (4) one thread per corner: strict 3x3 NMS on the score tile, 31-px border filter,
 //      append (score<<24 | y<<12 | x) to the level's candidate list + score histogram.
-constexpr int kFastIP = kFastTW + 16;        // image tile pitch in bytes: x0-8 .. x0+135
-constexpr int kFastIH = kFastTH + 8;         // rows y0-4 .. y0+35
-constexpr int kFastSP = kFastTW + 8;         // score tile pitch: x0-4 .. x0+131
-constexpr int kFastSH = kFastTH + 2;         // rows y0-1 .. y0+32
-constexpr int kFastQX = kFastSP / 4;         // quads per score row (34)
+constexpr int kFastIP = 160;                 // staged bytes per image row (16-B aligned start)
+constexpr int kFastIH = kFastTH + 8;         // image rows y0-4 .. y0+TH+3
+constexpr int kFastSP = 128;                 // score tile pitch: x0-4 .. x0+123
+constexpr int kFastSH = kFastTH + 2;         // score rows y0-1 .. y0+TH
+static_assert(kFastSH == 32 && kFastTW + 8 == kFastSP, "one warp per score row, 32 quads per row");
 
 __global__ void __launch_bounds__(256)
 k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand_key,
        uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
-  __shared__ __align__(16) uint8_t simg[kFastIH * kFastIP];
+  __shared__ __align__(128) uint8_t simg[kFastIH * kFastIP];
   __shared__ __align__(16) uint8_t ssc[kFastSH * kFastSP];
-  __shared__ uint16_t s_queue[kFastSH * kFastSP];
-  __shared__ uint32_t s_qn;
+  __shared__ uint16_t s_cand[kFastSH * kFastSP];
+  __shared__ uint16_t s_corner[kFastSH * kFastSP];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ uint32_t s_ncand, s_ncorner;
   const int img = blockIdx.y;
   int level = 0;
 #pragma unroll 1
@@ -80,55 +83,69 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint3
   const LevelGeom& L = g.lv[level];
   const int t = blockIdx.x - L.ftile0;
   const int x0 = kFastOrigin + (t % L.ftiles_x) * kFastTW, y0 = kFastOrigin + (t / L.ftiles_x) * kFastTH;
+  const int astart = (x0 - 8) & ~15;                       // first staged column (16-B aligned)
   const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int thr = g.fast_threshold;
 
-  // (1) stage + clear
-  for (int i = tid; i < kFastIH * (kFastIP / 4); i += 256) {
-    const int r = i / (kFastIP / 4), cw = i % (kFastIP / 4);
-    const int y = y0 - 4 + r, x = x0 - 8 + cw * 4;
-    uint32_t v = 0;
-    if (y >= 0 && y < L.h && x < L.pitch) v = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch + x));
-    reinterpret_cast<uint32_t*>(simg)[i] = v;
+  // (1) stage rows y0-4 .. y0+TH+3, columns astart .. astart+159, clipped to the level buffer.
+  // Bytes outside the level are never read for a pixel that can become a candidate.
+  const int row_bytes = min(kFastIP, L.pitch - astart);
+  const int n_rows = min(kFastIH, L.h - (y0 - 4));
+  if (tid == 0) {
+    mbar_init(&s_bar, 1);
+    s_ncand = 0;
+    s_ncorner = 0;
   }
   for (int i = tid; i < kFastSH * kFastSP / 4; i += 256) reinterpret_cast<uint32_t*>(ssc)[i] = 0;
-  if (tid == 0) s_qn = 0;
   __syncthreads();
+  if (tid == 0) mbar_arrive_expect_tx(&s_bar, (uint32_t)(row_bytes * n_rows));
+  if (tid < n_rows)
+    bulk_copy_g2s(&simg[tid * kFastIP], src + (size_t)(y0 - 4 + tid) * L.pitch + astart, (uint32_t)row_bytes, &s_bar);
+  mbar_wait(&s_bar, 0);
 
   // (2) packed pre-test.  Scores are only ever needed for x in [30, w-30), y in [30, h-30).
   const int xlo = max(30, x0 - 1), xhi = min(L.w - 30, x0 + kFastTW + 1);
   const int ylo = max(30, y0 - 1), yhi = min(L.h - 30, y0 + kFastTH + 1);
-  const uint32_t t4 = (uint32_t)min(thr, 127) * 0x01010101u;
-  const uint32_t* wimg = reinterpret_cast<const uint32_t*>(simg);
-  for (int i = tid; i < kFastSH * kFastQX; i += 256) {
-    const int sr = i / kFastQX, qx = i % kFastQX;
-    const int y = y0 - 1 + sr;
-    if (y < ylo || y >= yhi) continue;
-    const uint32_t* row = wimg + (sr + 3) * (kFastIP / 4) + qx;
-    const uint32_t Lw = row[0], C = row[1], Rw = row[2];
-    const uint32_t U = row[1 - 3 * (kFastIP / 4)], D = row[1 + 3 * (kFastIP / 4)];
-    uint32_t cand = fast_compass4(Lw, C, Rw, U, D, t4);
-    if (cand == 0) continue;
-    const int xq = x0 - 4 + 4 * qx;
-    const int lo = min(max(xlo - xq, 0), 4), hi = min(max(xhi - xq, 0), 4);
-    const uint32_t vmask = (uint32_t)(0x80808080ull << (8 * lo)) & (uint32_t)(0x80808080ull >> (8 * (4 - hi)));
-    cand &= vmask;
-    if (cand == 0) continue;
-    uint32_t pos = atomicAdd(&s_qn, (uint32_t)__popc(cand));
+  const uint32_t c4 = (uint32_t)(127 - min(thr, 127)) * 0x01010101u;
+  const int woff = (x0 - 4 - astart) >> 2;                 // smem word of quad 0 within a staged row
+  const int xq = x0 - 4 + 4 * lane;                        // first pixel of this lane's quad
+  const int lo = min(max(xlo - xq, 0), 4), hi = min(max(xhi - xq, 0), 4);
+  const uint32_t vmask = (uint32_t)(0x80808080ull << (8 * lo)) & (uint32_t)(0x80808080ull >> (8 * (4 - hi)));
+  const uint32_t* wimg = reinterpret_cast<const uint32_t*>(simg) + woff + lane;
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
-      if (cand & (0x80u << (8 * j))) s_queue[pos++] = (uint16_t)((sr << 8) | (4 * qx + j));
+  for (int k = 0; k < 4; ++k) {
+    const int sr = warp * 4 + k;
+    const int y = y0 - 1 + sr;
+    if (y < ylo || y >= yhi) continue;                     // warp-uniform
+    const uint32_t* row = wimg + (sr + 3) * (kFastIP / 4);
+    uint32_t cand = fast_pretest4(row[-1], row[0], row[1], row[-3 * (kFastIP / 4)], row[3 * (kFastIP / 4)], c4) & vmask;
+    if (cand == 0) continue;
+    uint32_t pos = atomicAdd(&s_ncand, (uint32_t)__popc(cand));
+    const uint32_t e0 = (uint32_t)((sr << 7) | (4 * lane));
+    while (cand) {
+      const int j = (__ffs(cand) - 1) >> 3;
+      s_cand[pos++] = (uint16_t)(e0 + j);
+      cand &= cand - 1;
+    }
   }
   __syncthreads();
-  const int qn = (int)s_qn;
 
-  // (3) exact test + score of the queued pixels
-  for (int i = tid; i < qn; i += 256) {
-    const int e = s_queue[i];
-    const int sr = e >> 8, c = e & 255;
-    const int sc = fast9_score(&simg[(sr + 3) * kFastIP + c + 4], kFastIP, thr);
-    if (sc > 0) ssc[sr * kFastSP + c] = (uint8_t)sc;
+  // (3a) exact corner test of the queued pixels
+  const int ncand = (int)s_ncand;
+  const int ib = x0 - 4 - astart;                          // smem byte column of score column 0
+  for (int i = tid; i < ncand; i += 256) {
+    const int e = s_cand[i];
+    const int sr = e >> 7, c = e & 127;
+    if (fast9_is_corner(&simg[(sr + 3) * kFastIP + ib + c], kFastIP, thr)) s_corner[atomicAdd(&s_ncorner, 1u)] = (uint16_t)e;
+  }
+  __syncthreads();
+  // (3b) corner scores
+  const int ncorner = (int)s_ncorner;
+  for (int i = tid; i < ncorner; i += 256) {
+    const int e = s_corner[i];
+    const int sr = e >> 7, c = e & 127;
+    ssc[e] = (uint8_t)fast9_corner_score(&simg[(sr + 3) * kFastIP + ib + c], kFastIP);
   }
   __syncthreads();
 
@@ -136,15 +153,14 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint3
   uint32_t* cnt = cand_cnt + img * g.nlevels + level;
   uint32_t* hst = hist + (size_t)(img * g.nlevels + level) * 256;
   uint32_t* out = cand_key + (size_t)img * g.cand_stride + L.cand_off;
-  for (int i = tid; i < qn; i += 256) {
-    const int e = s_queue[i];
-    const int sr = e >> 8, c = e & 255;
+  for (int i = tid; i < ncorner; i += 256) {
+    const int e = s_corner[i];
+    const int sr = e >> 7, c = e & 127;
     if (sr < 1 || sr > kFastTH || c < 4 || c >= 4 + kFastTW) continue;
-    const uint8_t* p = &ssc[sr * kFastSP + c];
-    const int s = p[0];
-    if (s == 0) continue;
     const int x = x0 - 4 + c, y = y0 - 1 + sr;
     if (x < 31 || x >= L.w - 31 || y < 31 || y >= L.h - 31) continue;
+    const uint8_t* p = &ssc[e];
+    const int s = p[0];
     const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
                       s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
     if (!keep) continue;

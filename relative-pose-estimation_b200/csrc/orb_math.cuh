@@ -24,26 +24,16 @@ RPE_HD uint8_t resize_px(const uint8_t* src, int pitch, int sw, int sh, int x0, 
 }
 
 // ------------------------------------------------------------------ A.2 FAST-9/16
-// returns 0 for a non-corner, else score = max(a, b) - 1 (always >= threshold).
-RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
+// Exact corner test: 9 contiguous ring pixels all brighter than v + t or all darker than v - t.
+RPE_HD bool fast9_is_corner(const uint8_t* c, int pitch, int t) {
   const int v = c[0];
   int d[16];
 #define RPE_LD(k, dx, dy) d[k] = v - (int)c[(dy) * pitch + (dx)]
-#define RPE_PAIR(k)                                      \
-  pos = pos && ((d[k] > t) || (d[(k) + 8] > t));         \
-  neg = neg && ((d[k] < -t) || (d[(k) + 8] < -t));       \
-  if (!(pos || neg)) return 0;
-  bool pos = true, neg = true;
-  RPE_LD(0, 0, 3);  RPE_LD(8, 0, -3);   RPE_PAIR(0)
-  RPE_LD(4, 3, 0);  RPE_LD(12, -3, 0);  RPE_PAIR(4)
-  RPE_LD(2, 2, 2);  RPE_LD(10, -2, -2); RPE_PAIR(2)
-  RPE_LD(6, 2, -2); RPE_LD(14, -2, 2);  RPE_PAIR(6)
-  RPE_LD(1, 1, 3);  RPE_LD(9, -1, -3);  RPE_PAIR(1)
-  RPE_LD(3, 3, 1);  RPE_LD(11, -3, -1); RPE_PAIR(3)
-  RPE_LD(5, 3, -1); RPE_LD(13, -3, 1);  RPE_PAIR(5)
-  RPE_LD(7, 1, -3); RPE_LD(15, -1, 3);  RPE_PAIR(7)
+  RPE_LD(0, 0, 3);  RPE_LD(1, 1, 3);   RPE_LD(2, 2, 2);    RPE_LD(3, 3, 1);
+  RPE_LD(4, 3, 0);  RPE_LD(5, 3, -1);  RPE_LD(6, 2, -2);   RPE_LD(7, 1, -3);
+  RPE_LD(8, 0, -3); RPE_LD(9, -1, -3); RPE_LD(10, -2, -2); RPE_LD(11, -3, -1);
+  RPE_LD(12, -3, 0); RPE_LD(13, -3, 1); RPE_LD(14, -2, 2); RPE_LD(15, -1, 3);
 #undef RPE_LD
-#undef RPE_PAIR
   uint32_t mp = 0, mn = 0;
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
@@ -54,8 +44,20 @@ RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
   uint32_t xp = mp | (mp << 16), xn = mn | (mn << 16);
   uint32_t ap = xp & (xp >> 1); ap &= ap >> 2; ap &= ap >> 4; ap &= xp >> 8;
   uint32_t an = xn & (xn >> 1); an &= an >> 2; an &= an >> 4; an &= xn >> 8;
-  if (((ap | an) & 0xffffu) == 0) return 0;
-  // score: a = max over arcs of min(d), b = max over arcs of min(-d) = -min over arcs of max(d)
+  return ((ap | an) & 0xffffu) != 0;
+}
+
+// Score of a pixel KNOWN to be a corner: max(a, b) - 1 with a = max over the 16 arcs of min(d),
+// b = max over arcs of min(-d) = -(min over arcs of max(d)).  Always >= threshold.
+RPE_HD int fast9_corner_score(const uint8_t* c, int pitch) {
+  const int v = c[0];
+  int d[16];
+#define RPE_LD(k, dx, dy) d[k] = v - (int)c[(dy) * pitch + (dx)]
+  RPE_LD(0, 0, 3);  RPE_LD(1, 1, 3);   RPE_LD(2, 2, 2);    RPE_LD(3, 3, 1);
+  RPE_LD(4, 3, 0);  RPE_LD(5, 3, -1);  RPE_LD(6, 2, -2);   RPE_LD(7, 1, -3);
+  RPE_LD(8, 0, -3); RPE_LD(9, -1, -3); RPE_LD(10, -2, -2); RPE_LD(11, -3, -1);
+  RPE_LD(12, -3, 0); RPE_LD(13, -3, 1); RPE_LD(14, -2, 2); RPE_LD(15, -1, 3);
+#undef RPE_LD
   int lo2[16], hi2[16], lo4[16], hi4[16];
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
@@ -78,34 +80,38 @@ RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
   return imax(a, -bmin) - 1;
 }
 
+// returns 0 for a non-corner, else the corner score
+RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
+  return fast9_is_corner(c, pitch, t) ? fast9_corner_score(c, pitch) : 0;
+}
+
 // Packed pre-test on four horizontally adjacent pixels (bytes of C = pixels x .. x+3; Lw / Rw
 // = the words left / right of C on the same row; U / D = the words at x .. x+3 three rows up /
-// down).  Returns 0x80 in byte j iff pixel j passes both opposite-pair tests on the compass
-// points of the ring, (0,+-3) and (+-3,0), for one polarity — a necessary condition for a
-// 9-arc, since an arc of 9 contains at least one point of every opposite pair.  t4 = the
-// threshold replicated in the four bytes (threshold < 128).
-RPE_HD uint32_t sat_add_u8x4(uint32_t v, uint32_t t4) {
-  const uint32_t s = (v & 0x7f7f7f7fu) + t4;               // 7-bit lanes: no carry across bytes
-  const uint32_t ovf = (s & v & 0x80808080u) >> 7;         // 1 in bytes whose sum exceeds 255
-  return (s ^ (v & 0x80808080u)) | (ovf * 0xffu);
+// down).  Returns 0x80 in byte j iff pixel j passes
+//   (|v - p0| > t or |v - p8| > t) and (|v - p4| > t or |v - p12| > t)
+// on the compass points (0,+-3), (+-3,0) of the ring: a necessary condition for a 9-arc, since
+// an arc of 9 contains at least one point of every opposite pair.  c4 = (127 - t) in every
+// byte (t <= 127; a larger threshold is tested with 127, which only weakens the filter).
+RPE_HD uint32_t absdiff_u8x4(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+  return __vabsdiffu4(a, b);                               // VABSDIFF4.U8, one instruction
+#else
+  uint32_t r = 0;
+  for (int j = 0; j < 4; ++j) {
+    const int x = (a >> (8 * j)) & 255, y = (b >> (8 * j)) & 255;
+    r |= (uint32_t)(x > y ? x - y : y - x) << (8 * j);
+  }
+  return r;
+#endif
 }
-RPE_HD uint32_t sat_sub_u8x4(uint32_t v, uint32_t t4) { return ~sat_add_u8x4(~v, t4); }
-// msb of each byte = (a > b) for unsigned bytes; a7 = a & 0x7f7f7f7f, nb7 = ~b & 0x7f7f7f7f
-RPE_HD uint32_t gt_u8x4(uint32_t a, uint32_t b, uint32_t a7, uint32_t nb7) {
-  const uint32_t s = a7 + nb7;                             // bit 7 = (low 7 bits of a) > (low 7 bits of b)
-  return (a & ~b) | (~(a ^ b) & s);
-}
-RPE_HD uint32_t fast_compass4(uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t U, uint32_t D, uint32_t t4) {
+RPE_HD uint32_t fast_pretest4(uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t U, uint32_t D, uint32_t c4) {
   const uint32_t E = (C >> 24) | (Rw << 8);                // pixels x+3 .. x+6
   const uint32_t W = (Lw >> 8) | (C << 24);                // pixels x-3 .. x
-  const uint32_t Vp = sat_add_u8x4(C, t4), Vm = sat_sub_u8x4(C, t4);
-  const uint32_t nVp7 = ~Vp & 0x7f7f7f7fu, Vm7 = Vm & 0x7f7f7f7fu;
-  const uint32_t n0 = D & 0x7f7f7f7fu, n1 = E & 0x7f7f7f7fu, n2 = U & 0x7f7f7f7fu, n3 = W & 0x7f7f7f7fu;
-  const uint32_t b0 = gt_u8x4(D, Vp, n0, nVp7), b1 = gt_u8x4(E, Vp, n1, nVp7);
-  const uint32_t b2 = gt_u8x4(U, Vp, n2, nVp7), b3 = gt_u8x4(W, Vp, n3, nVp7);
-  const uint32_t d0 = gt_u8x4(Vm, D, Vm7, 0x7f7f7f7fu - n0), d1 = gt_u8x4(Vm, E, Vm7, 0x7f7f7f7fu - n1);
-  const uint32_t d2 = gt_u8x4(Vm, U, Vm7, 0x7f7f7f7fu - n2), d3 = gt_u8x4(Vm, W, Vm7, 0x7f7f7f7fu - n3);
-  return (((b0 | b2) & (b1 | b3)) | ((d0 | d2) & (d1 | d3))) & 0x80808080u;
+  const uint32_t a0 = absdiff_u8x4(D, C), a1 = absdiff_u8x4(E, C), a2 = absdiff_u8x4(U, C), a3 = absdiff_u8x4(W, C);
+  // msb = (a > t): bytes >= 128 through the OR, smaller ones through the 7-bit add
+  const uint32_t f0 = ((a0 & 0x7f7f7f7fu) + c4) | a0, f1 = ((a1 & 0x7f7f7f7fu) + c4) | a1;
+  const uint32_t f2 = ((a2 & 0x7f7f7f7fu) + c4) | a2, f3 = ((a3 & 0x7f7f7f7fu) + c4) | a3;
+  return (f0 | f2) & (f1 | f3) & 0x80808080u;
 }
 
 // ------------------------------------------------------------------ A.5 Harris response

@@ -28,7 +28,7 @@ struct LevelGeom {
   int kp_off, kp_cap;      // slice of the per-image per-level keypoint arrays
   int xtab, ytab;          // tap-table offsets for producing this level from the previous one
   int tile0, tiles_x, tiles_y;     // 64 x 32 tiles (blur)
-  int ftile0, ftiles_x, ftiles_y;  // 128 x 32 tiles restricted to the rows/cols FAST needs
+  int ftile0, ftiles_x, ftiles_y;  // 120 x 30 tiles restricted to the rows/cols FAST needs
 };
 
 struct OrbGeom {
@@ -45,9 +45,9 @@ struct OrbGeom {
 
 constexpr int kTileW = 64;
 constexpr int kTileH = 32;
-constexpr int kFastTW = 128;
-constexpr int kFastTH = 32;
-constexpr int kFastOrigin = 28;  // FAST tiles start at x = y = 28: only scores in [30, size-30) can matter
+constexpr int kFastTW = 120;
+constexpr int kFastTH = 30;
+constexpr int kFastOrigin = 24;  // FAST tiles start at x = y = 24 (a multiple of 4): only scores in [30, size-30) can matter
 
 struct OrbBuffers {
   uint8_t* pyr;
