@@ -45,6 +45,8 @@ struct Geometry {
   OrbGeom g;
   std::vector<int2> taps;   // host copy
   int2* d_taps = nullptr;
+  std::vector<uint32_t> ftab;
+  uint32_t* d_ftab = nullptr;
 };
 
 struct rpe_handle {
@@ -121,6 +123,7 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
   size_t off = 0;
   int cand_off = 0, kp_off = 0, tile0 = 0, ftile0 = 0, max_kp_cap = 1;
   G.taps.clear();
+  G.ftab.clear();
   for (int l = 0; l < c.nlevels; ++l) {
     LevelGeom& L = g.lv[l];
     L.w = w[l]; L.h = h[l]; L.pitch = align_up(std::max(w[l], 1), 16);
@@ -139,6 +142,8 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
     L.ftiles_x = fw > 0 && fh > 0 ? (fw + kFastTW - 1) / kFastTW : 0;
     L.ftiles_y = fw > 0 && fh > 0 ? (fh + kFastTH - 1) / kFastTH : 0;
     L.ftile0 = ftile0; ftile0 += L.ftiles_x * L.ftiles_y;
+    for (int ty = 0; ty < L.ftiles_y; ++ty)
+      for (int tx = 0; tx < L.ftiles_x; ++tx) G.ftab.push_back(((uint32_t)l << 24) | ((uint32_t)ty << 12) | (uint32_t)tx);
     if (l > 0) {
       L.xtab = (int)G.taps.size(); linear_exact_taps(w[l - 1], w[l], G.taps);
       L.ytab = (int)G.taps.size(); linear_exact_taps(h[l - 1], h[l], G.taps);
@@ -181,6 +186,8 @@ static int get_geometry(rpe_handle* h, int W, int H, const Geometry** out) {
     G.g.sort_cap = h->sort_cap_orb;
     RPE_CK(cudaMalloc((void**)&G.d_taps, std::max<size_t>(G.taps.size(), 1) * sizeof(int2)));
     RPE_CK(cudaMemcpy(G.d_taps, G.taps.data(), G.taps.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    RPE_CK(cudaMalloc((void**)&G.d_ftab, std::max<size_t>(G.ftab.size(), 1) * sizeof(uint32_t)));
+    RPE_CK(cudaMemcpy(G.d_ftab, G.ftab.data(), G.ftab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     it = h->geoms.emplace(key, std::move(G)).first;
   }
   *out = &it->second;
@@ -291,7 +298,7 @@ void rpe_destroy(rpe_handle* h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
-  for (auto& kv : h->geoms) cudaFree(kv.second.d_taps);
+  for (auto& kv : h->geoms) { cudaFree(kv.second.d_taps); cudaFree(kv.second.d_ftab); }
   if (h->gb.tr_subset) { cudaFree(h->gb.tr_subset); cudaFree(h->gb.tr_nmodels); cudaFree(h->gb.tr_counts); cudaFree(h->gb.tr_models); }
   if (h->h_out_d) cudaFreeHost(h->h_out_d);
   if (h->h_out_i) cudaFreeHost(h->h_out_i);
@@ -345,6 +352,7 @@ static int finish_profile(rpe_handle* h) {
 static int run_orb(rpe_handle* h, const Geometry& G, int n_img, int first_mark) {
   OrbBuffers b = h->ob;
   b.taps = G.d_taps;
+  b.ftab = G.d_ftab;
   const size_t nctr = (size_t)h->NI * h->cfg.nlevels * 257 + h->NI;
   RPE_CK(cudaMemsetAsync(h->ob.cand_cnt, 0, nctr * sizeof(uint32_t), h->stream));
   int* ln = h->launches;

@@ -51,11 +51,11 @@ __device__ __forceinline__ int find_level(const OrbGeom& g, int tile) {
 }
 
 // ------------------------------------------------------------------ K2: FAST-9 + 3x3 NMS + border
-// One CTA (8 warps) = one 120x30 tile of one level of one image; the scored region (tile + 1)
-// is 32 rows x 32 aligned pixel quads, one warp per row, four rows per warp.
+// One CTA (8 warps) = one 120x30 tile of one level of one image (tile table: ftab); the scored
+// region (tile + 1) is 32 rows x 32 aligned pixel quads, one warp per row, four rows per warp.
 //  (1) TMA: one bulk copy per image row of the tile (+halo) into shared memory (UBLKCP);
-//  (2) branch-free packed pre-test, four pixels per thread (fast_pretest4); the few per cent
-//      of pixels that pass are compacted into a shared-memory queue;
+//  (2) branch-free packed pre-test, four pixels per thread (fast_compass4); the ~3 % of pixels
+//      that pass are compacted into a shared-memory queue;
 //  (3a) one thread per queued pixel: exact FAST-9 corner test -> corner queue;
 //  (3b) one thread per corner: score (min/max network) -> score tile in shared memory;
 //  (4) one thread per corner: strict 3x3 NMS on the score tile, 31-px border filter,
@@ -66,114 +66,128 @@ constexpr int kFastSP = 128;                 // score tile pitch: x0-4 .. x0+123
 constexpr int kFastSH = kFastTH + 2;         // score rows y0-1 .. y0+TH
 static_assert(kFastSH == 32 && kFastTW + 8 == kFastSP, "one warp per score row, 32 quads per row");
 
-__global__ void __launch_bounds__(256)
-k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand_key,
-       uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
+struct FastTile {
+  const uint8_t* src;   // level base of this image
+  int level, x0, y0, astart, img;
+};
+
+__device__ __forceinline__ FastTile fast_tile(const OrbGeom& g, const uint8_t* pyr, const uint32_t* ftab, int tile, int img) {
+  FastTile T;
+  T.img = img;
+  const uint32_t e = __ldg(ftab + tile);                  // level<<24 | ty<<12 | tx
+  T.level = e >> 24;
+  T.x0 = kFastOrigin + (int)(e & 0xfff) * kFastTW;
+  T.y0 = kFastOrigin + (int)((e >> 12) & 0xfff) * kFastTH;
+  T.astart = (T.x0 - 8) & ~15;
+  T.src = pyr + (size_t)img * g.pyr_stride + g.lv[T.level].off;
+  return T;
+}
+
+// rows y0-4 .. y0+TH+3, columns astart .. astart+159, clipped to the level buffer.  Bytes
+// outside the level are never read for a pixel that can become a candidate.
+__device__ __forceinline__ void fast_issue(const OrbGeom& g, const FastTile& T, uint8_t* buf, uint64_t* bar, int tid) {
+  const LevelGeom& L = g.lv[T.level];
+  const int row_bytes = min(kFastIP, L.pitch - T.astart);
+  const int n_rows = min(kFastIH, L.h - (T.y0 - 4));
+  if (tid == 0) mbar_arrive_expect_tx(bar, (uint32_t)(row_bytes * n_rows));
+  if (tid < n_rows)
+    bulk_copy_g2s(buf + tid * kFastIP, T.src + (size_t)(T.y0 - 4 + tid) * L.pitch + T.astart, (uint32_t)row_bytes, bar);
+}
+
+__global__ void __launch_bounds__(256, 6)
+k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
+       int n_img, uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
   __shared__ __align__(128) uint8_t simg[kFastIH * kFastIP];
   __shared__ __align__(16) uint8_t ssc[kFastSH * kFastSP];
   __shared__ uint16_t s_cand[kFastSH * kFastSP];
   __shared__ uint16_t s_corner[kFastSH * kFastSP];
   __shared__ __align__(8) uint64_t s_bar;
   __shared__ uint32_t s_ncand, s_ncorner;
-  const int img = blockIdx.y;
-  int level = 0;
-#pragma unroll 1
-  for (int i = 1; i < g.nlevels; ++i)
-    if ((int)blockIdx.x >= g.lv[i].ftile0) level = i;
-  const LevelGeom& L = g.lv[level];
-  const int t = blockIdx.x - L.ftile0;
-  const int x0 = kFastOrigin + (t % L.ftiles_x) * kFastTW, y0 = kFastOrigin + (t / L.ftiles_x) * kFastTH;
-  const int astart = (x0 - 8) & ~15;                       // first staged column (16-B aligned)
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int thr = g.fast_threshold;
-
-  // (1) stage rows y0-4 .. y0+TH+3, columns astart .. astart+159, clipped to the level buffer.
-  // Bytes outside the level are never read for a pixel that can become a candidate.
-  const int row_bytes = min(kFastIP, L.pitch - astart);
-  const int n_rows = min(kFastIH, L.h - (y0 - 4));
+  const uint32_t t4 = (uint32_t)min(thr, 127) * 0x01010101u;
+  const FastTile T = fast_tile(g, pyr, ftab, blockIdx.x, blockIdx.y);
   if (tid == 0) {
     mbar_init(&s_bar, 1);
     s_ncand = 0;
     s_ncorner = 0;
   }
-  for (int i = tid; i < kFastSH * kFastSP / 4; i += 256) reinterpret_cast<uint32_t*>(ssc)[i] = 0;
+  reinterpret_cast<uint4*>(ssc)[tid] = make_uint4(0, 0, 0, 0);
   __syncthreads();
-  if (tid == 0) mbar_arrive_expect_tx(&s_bar, (uint32_t)(row_bytes * n_rows));
-  if (tid < n_rows)
-    bulk_copy_g2s(&simg[tid * kFastIP], src + (size_t)(y0 - 4 + tid) * L.pitch + astart, (uint32_t)row_bytes, &s_bar);
+  fast_issue(g, T, simg, &s_bar, tid);
   mbar_wait(&s_bar, 0);
-
-  // (2) packed pre-test.  Scores are only ever needed for x in [30, w-30), y in [30, h-30).
-  const int xlo = max(30, x0 - 1), xhi = min(L.w - 30, x0 + kFastTW + 1);
-  const int ylo = max(30, y0 - 1), yhi = min(L.h - 30, y0 + kFastTH + 1);
-  const uint32_t c4 = (uint32_t)(127 - min(thr, 127)) * 0x01010101u;
-  const int woff = (x0 - 4 - astart) >> 2;                 // smem word of quad 0 within a staged row
-  const int xq = x0 - 4 + 4 * lane;                        // first pixel of this lane's quad
-  const int lo = min(max(xlo - xq, 0), 4), hi = min(max(xhi - xq, 0), 4);
-  const uint32_t vmask = (uint32_t)(0x80808080ull << (8 * lo)) & (uint32_t)(0x80808080ull >> (8 * (4 - hi)));
-  const uint32_t* wimg = reinterpret_cast<const uint32_t*>(simg) + woff + lane;
+  {
+    const LevelGeom& L = g.lv[T.level];
+    const int x0 = T.x0, y0 = T.y0;
+    // (2) packed pre-test.  Scores are only ever needed for x in [30, w-30), y in [30, h-30).
+    const int xlo = max(30, x0 - 1), xhi = min(L.w - 30, x0 + kFastTW + 1);
+    const int ylo = max(30, y0 - 1), yhi = min(L.h - 30, y0 + kFastTH + 1);
+    const int ib = x0 - 4 - T.astart;                      // smem byte column of score column 0
+    const int xq = x0 - 4 + 4 * lane;                      // first pixel of this lane's quad
+    const int lo = min(max(xlo - xq, 0), 4), hi = min(max(xhi - xq, 0), 4);
+    const uint32_t vmask = (uint32_t)(0x80808080ull << (8 * lo)) & (uint32_t)(0x80808080ull >> (8 * (4 - hi)));
+    const uint32_t* wimg = reinterpret_cast<const uint32_t*>(simg) + (ib >> 2) + lane;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int sr = warp * 4 + k;
-    const int y = y0 - 1 + sr;
-    if (y < ylo || y >= yhi) continue;                     // warp-uniform
-    const uint32_t* row = wimg + (sr + 3) * (kFastIP / 4);
-    uint32_t cand = fast_pretest4(row[-1], row[0], row[1], row[-3 * (kFastIP / 4)], row[3 * (kFastIP / 4)], c4) & vmask;
-    if (cand == 0) continue;
-    uint32_t pos = atomicAdd(&s_ncand, (uint32_t)__popc(cand));
-    const uint32_t e0 = (uint32_t)((sr << 7) | (4 * lane));
-    while (cand) {
-      const int j = (__ffs(cand) - 1) >> 3;
-      s_cand[pos++] = (uint16_t)(e0 + j);
-      cand &= cand - 1;
+    for (int k = 0; k < 4; ++k) {
+      const int sr = warp * 4 + k;
+      const int y = y0 - 1 + sr;
+      if (y < ylo || y >= yhi) continue;                   // warp-uniform
+      const uint32_t* row = wimg + (sr + 3) * (kFastIP / 4);
+      uint32_t cand = fast_compass4(row[-1], row[0], row[1], row[-3 * (kFastIP / 4)], row[3 * (kFastIP / 4)], t4) & vmask;
+      if (cand == 0) continue;
+      uint32_t pos = atomicAdd(&s_ncand, (uint32_t)__popc(cand));
+      const uint32_t e0 = (uint32_t)((sr << 7) | (4 * lane));
+      while (cand) {
+        const int j = (__ffs(cand) - 1) >> 3;
+        s_cand[pos++] = (uint16_t)(e0 + j);
+        cand &= cand - 1;
+      }
     }
-  }
-  __syncthreads();
+    __syncthreads();
 
-  // (3a) exact corner test of the queued pixels
-  const int ncand = (int)s_ncand;
-  const int ib = x0 - 4 - astart;                          // smem byte column of score column 0
-  for (int i = tid; i < ncand; i += 256) {
-    const int e = s_cand[i];
-    const int sr = e >> 7, c = e & 127;
-    if (fast9_is_corner(&simg[(sr + 3) * kFastIP + ib + c], kFastIP, thr)) s_corner[atomicAdd(&s_ncorner, 1u)] = (uint16_t)e;
-  }
-  __syncthreads();
-  // (3b) corner scores
-  const int ncorner = (int)s_ncorner;
-  for (int i = tid; i < ncorner; i += 256) {
-    const int e = s_corner[i];
-    const int sr = e >> 7, c = e & 127;
-    ssc[e] = (uint8_t)fast9_corner_score(&simg[(sr + 3) * kFastIP + ib + c], kFastIP);
-  }
-  __syncthreads();
+    // (3a) exact corner test of the queued pixels
+    const int ncand = (int)s_ncand;
+    for (int i = tid; i < ncand; i += 256) {
+      const int e = s_cand[i];
+      const int sr = e >> 7, c = e & 127;
+      if (fast9_is_corner(&simg[(sr + 3) * kFastIP + ib + c], kFastIP, thr)) s_corner[atomicAdd(&s_ncorner, 1u)] = (uint16_t)e;
+    }
+    __syncthreads();
+    // (3b) corner scores
+    const int ncorner = (int)s_ncorner;
+    for (int i = tid; i < ncorner; i += 256) {
+      const int e = s_corner[i];
+      const int sr = e >> 7, c = e & 127;
+      ssc[e] = (uint8_t)fast9_corner_score(&simg[(sr + 3) * kFastIP + ib + c], kFastIP);
+    }
+    __syncthreads();
 
-  // (4) NMS + border filter + append
-  uint32_t* cnt = cand_cnt + img * g.nlevels + level;
-  uint32_t* hst = hist + (size_t)(img * g.nlevels + level) * 256;
-  uint32_t* out = cand_key + (size_t)img * g.cand_stride + L.cand_off;
-  for (int i = tid; i < ncorner; i += 256) {
-    const int e = s_corner[i];
-    const int sr = e >> 7, c = e & 127;
-    if (sr < 1 || sr > kFastTH || c < 4 || c >= 4 + kFastTW) continue;
-    const int x = x0 - 4 + c, y = y0 - 1 + sr;
-    if (x < 31 || x >= L.w - 31 || y < 31 || y >= L.h - 31) continue;
-    const uint8_t* p = &ssc[e];
-    const int s = p[0];
-    const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
-                      s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
-    if (!keep) continue;
-    const uint32_t pos = atomicAdd(cnt, 1u);
-    if (pos < (uint32_t)L.cand_cap) out[pos] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
-    atomicAdd(&hst[s], 1u);
+    // (4) NMS + border filter + append
+    uint32_t* cnt = cand_cnt + T.img * g.nlevels + T.level;
+    uint32_t* hst = hist + (size_t)(T.img * g.nlevels + T.level) * 256;
+    uint32_t* out = cand_key + (size_t)T.img * g.cand_stride + L.cand_off;
+    for (int i = tid; i < ncorner; i += 256) {
+      const int e = s_corner[i];
+      const int sr = e >> 7, c = e & 127;
+      if (sr < 1 || sr > kFastTH || c < 4 || c >= 4 + kFastTW) continue;
+      const int x = x0 - 4 + c, y = y0 - 1 + sr;
+      if (x < 31 || x >= L.w - 31 || y < 31 || y >= L.h - 31) continue;
+      const uint8_t* p = &ssc[e];
+      const int s = p[0];
+      const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
+                        s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
+      if (!keep) continue;
+      const uint32_t pos = atomicAdd(cnt, 1u);
+      if (pos < (uint32_t)L.cand_cap) out[pos] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+      atomicAdd(&hst[s], 1u);
+    }
   }
 }
 
 void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   if (g.total_ftiles == 0) return;
   dim3 grid(g.total_ftiles, n_img);
-  k_fast<<<grid, 256, 0, s>>>(g, b.pyr, b.cand_key, b.cand_cnt, b.hist);
+  k_fast<<<grid, 256, 0, s>>>(g, b.pyr, b.ftab, n_img, b.cand_key, b.cand_cnt, b.hist);
   ++*launches;
 }
 

@@ -87,31 +87,32 @@ RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
 
 // Packed pre-test on four horizontally adjacent pixels (bytes of C = pixels x .. x+3; Lw / Rw
 // = the words left / right of C on the same row; U / D = the words at x .. x+3 three rows up /
-// down).  Returns 0x80 in byte j iff pixel j passes
-//   (|v - p0| > t or |v - p8| > t) and (|v - p4| > t or |v - p12| > t)
-// on the compass points (0,+-3), (+-3,0) of the ring: a necessary condition for a 9-arc, since
-// an arc of 9 contains at least one point of every opposite pair.  c4 = (127 - t) in every
-// byte (t <= 127; a larger threshold is tested with 127, which only weakens the filter).
-RPE_HD uint32_t absdiff_u8x4(uint32_t a, uint32_t b) {
-#if defined(__CUDA_ARCH__)
-  return __vabsdiffu4(a, b);                               // VABSDIFF4.U8, one instruction
-#else
-  uint32_t r = 0;
-  for (int j = 0; j < 4; ++j) {
-    const int x = (a >> (8 * j)) & 255, y = (b >> (8 * j)) & 255;
-    r |= (uint32_t)(x > y ? x - y : y - x) << (8 * j);
-  }
-  return r;
-#endif
+// down).  Returns 0x80 in byte j iff pixel j passes both opposite-pair tests on the compass
+// points of the ring, (0,+-3) and (+-3,0), for one polarity — a necessary condition for a
+// 9-arc, since an arc of 9 contains at least one point of every opposite pair.  t4 = the
+// threshold replicated in the four bytes (threshold < 128).
+RPE_HD uint32_t sat_add_u8x4(uint32_t v, uint32_t t4) {
+  const uint32_t s = (v & 0x7f7f7f7fu) + t4;               // 7-bit lanes: no carry across bytes
+  const uint32_t ovf = (s & v & 0x80808080u) >> 7;         // 1 in bytes whose sum exceeds 255
+  return (s ^ (v & 0x80808080u)) | (ovf * 0xffu);
 }
-RPE_HD uint32_t fast_pretest4(uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t U, uint32_t D, uint32_t c4) {
+RPE_HD uint32_t sat_sub_u8x4(uint32_t v, uint32_t t4) { return ~sat_add_u8x4(~v, t4); }
+// msb of each byte = (a > b) for unsigned bytes; a7 = a & 0x7f7f7f7f, nb7 = ~b & 0x7f7f7f7f
+RPE_HD uint32_t gt_u8x4(uint32_t a, uint32_t b, uint32_t a7, uint32_t nb7) {
+  const uint32_t s = a7 + nb7;                             // bit 7 = (low 7 bits of a) > (low 7 bits of b)
+  return (a & ~b) | (~(a ^ b) & s);
+}
+RPE_HD uint32_t fast_compass4(uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t U, uint32_t D, uint32_t t4) {
   const uint32_t E = (C >> 24) | (Rw << 8);                // pixels x+3 .. x+6
   const uint32_t W = (Lw >> 8) | (C << 24);                // pixels x-3 .. x
-  const uint32_t a0 = absdiff_u8x4(D, C), a1 = absdiff_u8x4(E, C), a2 = absdiff_u8x4(U, C), a3 = absdiff_u8x4(W, C);
-  // msb = (a > t): bytes >= 128 through the OR, smaller ones through the 7-bit add
-  const uint32_t f0 = ((a0 & 0x7f7f7f7fu) + c4) | a0, f1 = ((a1 & 0x7f7f7f7fu) + c4) | a1;
-  const uint32_t f2 = ((a2 & 0x7f7f7f7fu) + c4) | a2, f3 = ((a3 & 0x7f7f7f7fu) + c4) | a3;
-  return (f0 | f2) & (f1 | f3) & 0x80808080u;
+  const uint32_t Vp = sat_add_u8x4(C, t4), Vm = sat_sub_u8x4(C, t4);
+  const uint32_t nVp7 = ~Vp & 0x7f7f7f7fu, Vm7 = Vm & 0x7f7f7f7fu;
+  const uint32_t n0 = D & 0x7f7f7f7fu, n1 = E & 0x7f7f7f7fu, n2 = U & 0x7f7f7f7fu, n3 = W & 0x7f7f7f7fu;
+  const uint32_t b0 = gt_u8x4(D, Vp, n0, nVp7), b1 = gt_u8x4(E, Vp, n1, nVp7);
+  const uint32_t b2 = gt_u8x4(U, Vp, n2, nVp7), b3 = gt_u8x4(W, Vp, n3, nVp7);
+  const uint32_t d0 = gt_u8x4(Vm, D, Vm7, 0x7f7f7f7fu - n0), d1 = gt_u8x4(Vm, E, Vm7, 0x7f7f7f7fu - n1);
+  const uint32_t d2 = gt_u8x4(Vm, U, Vm7, 0x7f7f7f7fu - n2), d3 = gt_u8x4(Vm, W, Vm7, 0x7f7f7f7fu - n3);
+  return (((b0 | b2) & (b1 | b3)) | ((d0 | d2) & (d1 | d3))) & 0x80808080u;
 }
 
 // ------------------------------------------------------------------ A.5 Harris response

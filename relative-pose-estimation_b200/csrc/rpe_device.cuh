@@ -62,6 +62,7 @@ struct OrbBuffers {
   uint32_t* lvl_cnt;
   uint32_t* img_flags;
   const int2* taps;
+  const uint32_t* ftab;   // FAST tile table: level<<24 | tile_y<<12 | tile_x
   float* kp_x; float* kp_y; float* kp_size; float* kp_angle; float* kp_resp;
   int32_t* kp_oct;
   uint8_t* desc;

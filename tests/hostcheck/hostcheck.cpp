@@ -22,13 +22,13 @@ void hc_fast_scores(const uint8_t* img, int w, int h, int t, int* out) {
 // packed pre-test on every aligned quad of rows 3..h-4 / cols 4..w-8: out[y*w+x] = 1 if it passes
 void hc_fast_compass(const uint8_t* img, int w, int h, int t, uint8_t* out) {
   memset(out, 0, (size_t)w * h);
-  const uint32_t c4 = (uint32_t)(127 - t) * 0x01010101u;
+  const uint32_t t4 = (uint32_t)t * 0x01010101u;
   for (int y = 3; y < h - 3; ++y)
     for (int x = 4; x + 8 <= w; x += 4) {
       uint32_t Lw, C, Rw, U, D;
       memcpy(&Lw, img + y * w + x - 4, 4); memcpy(&C, img + y * w + x, 4); memcpy(&Rw, img + y * w + x + 4, 4);
       memcpy(&U, img + (y - 3) * w + x, 4); memcpy(&D, img + (y + 3) * w + x, 4);
-      const uint32_t c = fast_pretest4(Lw, C, Rw, U, D, c4);
+      const uint32_t c = fast_compass4(Lw, C, Rw, U, D, t4);
       for (int j = 0; j < 4; ++j) out[y * w + x + j] = (c >> (8 * j + 7)) & 1;
     }
 }

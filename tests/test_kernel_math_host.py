@@ -32,9 +32,9 @@ def test_fast_scores_bit_exact(img):
         assert np.array_equal(hc.fast_scores(noise, t), oo.fast_score_map(noise, t))
 
 
-def test_fast_packed_pretest(img):
-    """The 4-pixel packed pre-test of k_fast equals its scalar definition exactly, and no FAST corner
-    fails it (so the compaction never drops a corner)."""
+def test_fast_packed_pretest_is_the_scalar_compass_test(img):
+    """The 4-pixel packed pre-test of k_fast equals the scalar two-pair compass test exactly, and
+    no FAST corner fails it (so compaction never drops a corner)."""
     rng = np.random.default_rng(2)
     hard = rng.integers(0, 256, (96, 128), dtype=np.uint8)
     hard[:, :40] = rng.choice(np.array([0, 1, 14, 15, 16, 17, 127, 128, 129, 239, 240, 241, 254, 255], np.uint8), (96, 40))
@@ -46,7 +46,7 @@ def test_fast_packed_pretest(img):
             c = I[3:h - 3, 4:w - 4]
             d0, d8 = c - I[6:h, 4:w - 4], c - I[0:h - 6, 4:w - 4]
             d4, d12 = c - I[3:h - 3, 7:w - 1], c - I[3:h - 3, 1:w - 7]
-            want = ((abs(d0) > t) | (abs(d8) > t)) & ((abs(d4) > t) | (abs(d12) > t))
+            want = (((d0 > t) | (d8 > t)) & ((d4 > t) | (d12 > t))) | (((d0 < -t) | (d8 < -t)) & ((d4 < -t) | (d12 < -t)))
             x_hi = 4 + ((w - 8) // 4) * 4
             assert np.array_equal(got[3:h - 3, 4:x_hi].astype(bool), want[:, :x_hi - 4]), t
             corners = oo.fast_score_map(im, t)[3:h - 3, 4:x_hi] > 0
