@@ -45,8 +45,9 @@ struct Geometry {
   OrbGeom g;
   std::vector<int2> taps;   // host copy
   int2* d_taps = nullptr;
-  std::vector<uint32_t> ftab;
+  std::vector<uint32_t> ftab, btab;
   uint32_t* d_ftab = nullptr;
+  uint32_t* d_btab = nullptr;
 };
 
 struct rpe_handle {
@@ -124,6 +125,7 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
   int cand_off = 0, kp_off = 0, tile0 = 0, ftile0 = 0, max_kp_cap = 1;
   G.taps.clear();
   G.ftab.clear();
+  G.btab.clear();
   for (int l = 0; l < c.nlevels; ++l) {
     LevelGeom& L = g.lv[l];
     L.w = w[l]; L.h = h[l]; L.pitch = align_up(std::max(w[l], 1), 16);
@@ -144,6 +146,8 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
     L.ftile0 = ftile0; ftile0 += L.ftiles_x * L.ftiles_y;
     for (int ty = 0; ty < L.ftiles_y; ++ty)
       for (int tx = 0; tx < L.ftiles_x; ++tx) G.ftab.push_back(((uint32_t)l << 24) | ((uint32_t)ty << 12) | (uint32_t)tx);
+    for (int sy = 0; sy < (L.h + 63) / 64; ++sy)
+      for (int sx = 0; sx < (L.w + 127) / 128; ++sx) G.btab.push_back(((uint32_t)l << 24) | ((uint32_t)sy << 12) | (uint32_t)sx);
     if (l > 0) {
       L.xtab = (int)G.taps.size(); linear_exact_taps(w[l - 1], w[l], G.taps);
       L.ytab = (int)G.taps.size(); linear_exact_taps(h[l - 1], h[l], G.taps);
@@ -151,6 +155,7 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
   }
   g.total_tiles = tile0;
   g.total_ftiles = ftile0;
+  g.total_bitems = (int)G.btab.size();
   g.cand_stride = cand_off;
   g.kp_stride = kp_off;
   g.sort_cap = pow2_ge(max_kp_cap);
@@ -188,6 +193,8 @@ static int get_geometry(rpe_handle* h, int W, int H, const Geometry** out) {
     RPE_CK(cudaMemcpy(G.d_taps, G.taps.data(), G.taps.size() * sizeof(int2), cudaMemcpyHostToDevice));
     RPE_CK(cudaMalloc((void**)&G.d_ftab, std::max<size_t>(G.ftab.size(), 1) * sizeof(uint32_t)));
     RPE_CK(cudaMemcpy(G.d_ftab, G.ftab.data(), G.ftab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    RPE_CK(cudaMalloc((void**)&G.d_btab, std::max<size_t>(G.btab.size(), 1) * sizeof(uint32_t)));
+    RPE_CK(cudaMemcpy(G.d_btab, G.btab.data(), G.btab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     it = h->geoms.emplace(key, std::move(G)).first;
   }
   *out = &it->second;
@@ -298,7 +305,7 @@ void rpe_destroy(rpe_handle* h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
-  for (auto& kv : h->geoms) { cudaFree(kv.second.d_taps); cudaFree(kv.second.d_ftab); }
+  for (auto& kv : h->geoms) { cudaFree(kv.second.d_taps); cudaFree(kv.second.d_ftab); cudaFree(kv.second.d_btab); }
   if (h->gb.tr_subset) { cudaFree(h->gb.tr_subset); cudaFree(h->gb.tr_nmodels); cudaFree(h->gb.tr_counts); cudaFree(h->gb.tr_models); }
   if (h->h_out_d) cudaFreeHost(h->h_out_d);
   if (h->h_out_i) cudaFreeHost(h->h_out_i);
@@ -353,6 +360,7 @@ static int run_orb(rpe_handle* h, const Geometry& G, int n_img, int first_mark) 
   OrbBuffers b = h->ob;
   b.taps = G.d_taps;
   b.ftab = G.d_ftab;
+  b.btab = G.d_btab;
   const size_t nctr = (size_t)h->NI * h->cfg.nlevels * 257 + h->NI;
   RPE_CK(cudaMemsetAsync(h->ob.cand_cnt, 0, nctr * sizeof(uint32_t), h->stream));
   int* ln = h->launches;

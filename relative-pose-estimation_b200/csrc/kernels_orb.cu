@@ -331,67 +331,88 @@ void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_
 }
 
 // ------------------------------------------------------------------ K6: 7x7 sigma-2 blur (f32 FMA separable)
-constexpr int kBlurIW = kTileW + 8;   // staged columns x0-4 .. x0+67 (only -3..+66 used)
-constexpr int kBlurIH = kTileH + 6;   // rows y0-3 .. y0+34
+// Register sliding window, no shared memory: one thread = 4 adjacent columns (one output
+// word) x a strip of kBlurRows rows; one warp = 128 columns.  Per input row the thread loads
+// three words (columns x-4 .. x+7, L1-shared with its neighbours), converts the ten bytes it
+// needs to f32 with the 2^23 mantissa trick (PRMT + FADD: no I2F), runs the row pass
+// (blur_row7: one FMUL + six FMA, left to right) for its four columns and keeps the last
+// seven row results in registers; the column pass (blur_col7_sum) and the round-to-nearest-
+// even store come out of that window.  Work items (level, strip, segment) come from btab.
+constexpr int kBlurRows = 64;
 
-__global__ void __launch_bounds__(256)
-k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur) {
-  __shared__ __align__(16) uint8_t simg[kBlurIH * kBlurIW];
-  __shared__ float srow[kBlurIH * kTileW];
+__device__ __forceinline__ float u8_to_f32(uint32_t w, uint32_t sel) {
+  // bytes {b, 0, 0, 0x4b} = 2^23 + b exactly; subtracting 2^23 is exact
+  return __fsub_rn(__uint_as_float(__byte_perm(w, 0x4b000000u, sel)), 8388608.0f);
+}
+
+__global__ void __launch_bounds__(128)
+k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
+       const uint32_t* __restrict__ btab) {
   const int img = blockIdx.y;
-  const int level = find_level(g, blockIdx.x);
-  const LevelGeom& L = g.lv[level];
-  const int t = blockIdx.x - L.tile0;
-  const int x0 = (t % L.tiles_x) * kTileW, y0 = (t / L.tiles_x) * kTileH;
+  const int item = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (item >= g.total_bitems) return;
+  const uint32_t e = __ldg(btab + item);                   // level<<24 | strip<<12 | segment
+  const LevelGeom& L = g.lv[e >> 24];
+  const int x = ((int)(e & 0xfff) * 32 + (threadIdx.x & 31)) * 4;
+  const int y0 = (int)((e >> 12) & 0xfff) * kBlurRows;
+  if (x >= L.w) return;
   const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
   uint8_t* dst = blur + (size_t)img * g.pyr_stride + L.off;
-  const int tid = threadIdx.x;
-  const bool interior = x0 >= 4 && x0 + kTileW + 4 <= L.w && y0 >= 3 && y0 + kTileH + 3 <= L.h;
-  if (interior) {
-    for (int i = tid; i < kBlurIH * (kBlurIW / 4); i += 256) {
-      const int r = i / (kBlurIW / 4), cw = i % (kBlurIW / 4);
-      *reinterpret_cast<uint32_t*>(&simg[r * kBlurIW + cw * 4]) =
-          *reinterpret_cast<const uint32_t*>(src + (size_t)(y0 - 3 + r) * L.pitch + x0 - 4 + cw * 4);
-    }
-  } else {
-    for (int i = tid; i < kBlurIH * kBlurIW; i += 256) {
-      const int r = i / kBlurIW, c = i % kBlurIW;
-      const int y = reflect101(min(y0 - 3 + r, L.h + 2), L.h);
-      const int x = reflect101(min(x0 - 4 + c, L.w + 2), L.w);
-      simg[i] = src[(size_t)y * L.pitch + x];
-    }
-  }
-  __syncthreads();
-  for (int i = tid; i < kBlurIH * kTileW; i += 256) {
-    const int r = i / kTileW, c = i % kTileW;
-    const uint8_t* p = &simg[r * kBlurIW + c + 1];   // column x0 + c - 3
-    srow[i] = blur_row7((float)p[0], (float)p[1], (float)p[2], (float)p[3], (float)p[4], (float)p[5],
-                        (float)p[6]);
-  }
-  __syncthreads();
-  // each thread: 4 adjacent columns x 2 rows -> two 32-bit stores
-  {
-    const int cx = (tid % 16) * 4, ry = (tid / 16) * 2;
+  const int w = L.w, h = L.h, pitch = L.pitch;
+  const bool edge = x < 4 || x + 7 > w;                    // some of x-3 .. x+6 fall outside the image
+  int xo[10];
 #pragma unroll
-    for (int rr = 0; rr < 2; ++rr) {
-      const int r = ry + rr;
-      const int y = y0 + r;
-      uint32_t out = 0;
+  for (int k = 0; k < 10; ++k) xo[k] = edge ? reflect101(x - 3 + k, w) : 0;
+  const int n_out = min(kBlurRows, h - y0);
+  float win[7][4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float* q = &srow[r * kTileW + cx + k];
-        out |= (uint32_t)blur_col7(q[0], q[kTileW], q[2 * kTileW], q[3 * kTileW], q[4 * kTileW],
-                                   q[5 * kTileW], q[6 * kTileW]) << (8 * k);
+  for (int i = 0; i < 7; ++i)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) win[i][c] = 0.f;
+
+  for (int base = 0; base < n_out + 6; base += 7) {
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+      const int r = base + i;
+      if (r < n_out + 6) {
+        const uint8_t* row = src + (size_t)reflect101(y0 - 3 + r, h) * pitch;
+        float v[10];
+        if (!edge) {
+          const uint32_t a = __ldg(reinterpret_cast<const uint32_t*>(row + x - 4));
+          const uint32_t b = __ldg(reinterpret_cast<const uint32_t*>(row + x));
+          const uint32_t c = __ldg(reinterpret_cast<const uint32_t*>(row + x + 4));
+          v[0] = u8_to_f32(a, 0x7441); v[1] = u8_to_f32(a, 0x7442); v[2] = u8_to_f32(a, 0x7443);
+          v[3] = u8_to_f32(b, 0x7440); v[4] = u8_to_f32(b, 0x7441); v[5] = u8_to_f32(b, 0x7442);
+          v[6] = u8_to_f32(b, 0x7443);
+          v[7] = u8_to_f32(c, 0x7440); v[8] = u8_to_f32(c, 0x7441); v[9] = u8_to_f32(c, 0x7442);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 10; ++k) v[k] = (float)row[xo[k]];
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          win[i][c] = blur_row7(v[c], v[c + 1], v[c + 2], v[c + 3], v[c + 4], v[c + 5], v[c + 6]);
+        if (r >= 6) {
+          uint32_t o[4];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const float sum = blur_col7_sum(win[(i + 1) % 7][c], win[(i + 2) % 7][c], win[(i + 3) % 7][c],
+                                            win[(i + 4) % 7][c], win[(i + 5) % 7][c], win[(i + 6) % 7][c], win[i][c]);
+            // 0 <= sum <= 255: adding 1.5 * 2^23 leaves rint(sum) (ties to even) in the low byte
+            o[c] = __float_as_uint(__fadd_rn(sum, 12582912.0f));
+          }
+          const uint32_t lo = __byte_perm(o[0], o[1], 0x0040), hi = __byte_perm(o[2], o[3], 0x0040);
+          *reinterpret_cast<uint32_t*>(dst + (size_t)(y0 + r - 6) * pitch + x) = __byte_perm(lo, hi, 0x5410);
+        }
       }
-      if (y < L.h && x0 + cx < L.pitch)
-        *reinterpret_cast<uint32_t*>(dst + (size_t)y * L.pitch + x0 + cx) = out;
     }
   }
 }
 
 void launch_blur(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
-  dim3 grid(g.total_tiles, n_img);
-  k_blur<<<grid, 256, 0, s>>>(g, b.pyr, b.blur);
+  if (g.total_bitems == 0) return;
+  dim3 grid((g.total_bitems + 3) / 4, n_img);
+  k_blur<<<grid, 128, 0, s>>>(g, b.pyr, b.blur, b.btab);
   ++*launches;
 }
 

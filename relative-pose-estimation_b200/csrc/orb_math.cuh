@@ -212,12 +212,15 @@ RPE_HD float blur_row7(float x0, float x1, float x2, float x3, float x4, float x
   return s;
 }
 // column pass on 7 row-pass results r[-3..3]: symmetric pairing, then round + saturate
-RPE_HD uint8_t blur_col7(float r0, float r1, float r2, float r3, float r4, float r5, float r6) {
+RPE_HD float blur_col7_sum(float r0, float r1, float r2, float r3, float r4, float r5, float r6) {
   float s = f32_mul(RPE_BLUR_K3, r3);
   s = f32_fma(RPE_BLUR_K2, f32_add(r2, r4), s);
   s = f32_fma(RPE_BLUR_K1, f32_add(r1, r5), s);
   s = f32_fma(RPE_BLUR_K0, f32_add(r0, r6), s);
-  int v = f32_rint(s);
+  return s;
+}
+RPE_HD uint8_t blur_col7(float r0, float r1, float r2, float r3, float r4, float r5, float r6) {
+  int v = f32_rint(blur_col7_sum(r0, r1, r2, r3, r4, r5, r6));
   return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
 }
 RPE_HD int reflect101(int i, int n) {

@@ -36,6 +36,7 @@ struct OrbGeom {
   int fast_threshold;
   int total_tiles;
   int total_ftiles;
+  int total_bitems;        // blur work items (one warp each): 128 columns x 64 rows
   int cand_stride;
   int kp_stride;
   int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)
@@ -63,6 +64,7 @@ struct OrbBuffers {
   uint32_t* img_flags;
   const int2* taps;
   const uint32_t* ftab;   // FAST tile table: level<<24 | tile_y<<12 | tile_x
+  const uint32_t* btab;   // blur work items: level<<24 | strip<<12 | segment
   float* kp_x; float* kp_y; float* kp_size; float* kp_angle; float* kp_resp;
   int32_t* kp_oct;
   uint8_t* desc;
