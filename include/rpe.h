@@ -79,6 +79,11 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out);
 void rpe_destroy(rpe_handle* h);
 /* run all work of this handle on an existing CUDA stream (cudaStream_t); NULL = own stream */
 int rpe_set_stream(rpe_handle* h, void* cuda_stream);
+/* sub-batch pipeline of the batch calls: pairs are processed in chunks of `chunk_pairs`, round-robin
+ * over `n_streams` (1..4) internal streams forked from / joined into the handle's stream, so the H2D
+ * copy and the latency-bound kernels of one chunk overlap the dense kernels of the next.
+ * Default 32 pairs x 3 streams.  Results do not depend on these settings. */
+int rpe_set_pipeline(rpe_handle* h, int32_t chunk_pairs, int32_t n_streams);
 /* capacities derived from the config: max keypoints per image, max matches per pair */
 int rpe_get_capacity(const rpe_handle* h, int32_t* kp_cap, int32_t* match_cap);
 

@@ -46,6 +46,7 @@ _SIGNATURES = [
     ("rpe_create", C.c_int, [C.POINTER(RpeConfig), C.c_int, C.POINTER(_P)]),
     ("rpe_destroy", None, [_P]),
     ("rpe_set_stream", C.c_int, [_P, _P]),
+    ("rpe_set_pipeline", C.c_int, [_P, C.c_int32, C.c_int32]),
     ("rpe_get_capacity", C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     ("rpe_estimate_batch", C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     ("rpe_estimate_batch_device", C.c_int, [_P, _P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),

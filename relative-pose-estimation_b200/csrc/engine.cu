@@ -55,6 +55,13 @@ struct rpe_handle {
   int device = 0;
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
+  // sub-batch pipeline: chunks of chunk_pairs pairs round-robin over n_workers streams, so that the
+  // H2D copy and the latency-bound tail kernels (select, RANSAC, pose) of one chunk overlap the
+  // dense kernels of the next
+  static constexpr int kMaxWorkers = 4;
+  cudaStream_t wstream[kMaxWorkers] = {};
+  cudaEvent_t ev_fork = nullptr, ev_done[kMaxWorkers] = {};
+  int chunk_pairs = 32, n_workers = 3;
   int NI = 0, NP = 0;
   int kp_stride = 0, cand_stride = 0, mcap = 0, sort_cap_orb = 0, sort_cap_match = 0;
   size_t pyr_stride = 0;
@@ -282,6 +289,12 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out) {
   A(dalloc(h, &h->dK, 9));
   if (rc == RPE_OK && cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaStreamCreate failed");
   h->stream = h->own_stream;
+  for (int i = 0; i < rpe_handle::kMaxWorkers && rc == RPE_OK; ++i) {
+    if (cudaStreamCreateWithFlags(&h->wstream[i], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming) != cudaSuccess)
+      rc = fail(RPE_ERR_CUDA, "worker stream creation failed");
+  }
+  if (rc == RPE_OK && cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
   if (rc == RPE_OK && cudaMallocHost((void**)&h->h_out_d, NP * 15 * sizeof(double)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
   if (rc == RPE_OK && cudaMallocHost((void**)&h->h_out_i, NP * 5 * sizeof(int32_t)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
   if (rc == RPE_OK && cudaMallocHost((void**)&h->h_K, 9 * sizeof(double)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
@@ -312,12 +325,24 @@ void rpe_destroy(rpe_handle* h) {
   if (h->h_K) cudaFreeHost(h->h_K);
   for (int i = 0; i <= RPE_T_COUNT; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  for (int i = 0; i < rpe_handle::kMaxWorkers; ++i) {
+    if (h->wstream[i]) cudaStreamDestroy(h->wstream[i]);
+    if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+  }
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   delete h;
 }
 
 int rpe_set_stream(rpe_handle* h, void* s) {
   if (!h) return fail(RPE_ERR_INVALID, "null handle");
   h->stream = s ? (cudaStream_t)s : h->own_stream;
+  return RPE_OK;
+}
+
+int rpe_set_pipeline(rpe_handle* h, int32_t chunk_pairs, int32_t n_streams) {
+  if (!h || chunk_pairs < 1 || n_streams < 1 || n_streams > rpe_handle::kMaxWorkers) return fail(RPE_ERR_INVALID, "bad pipeline arguments");
+  h->chunk_pairs = chunk_pairs;
+  h->n_workers = n_streams;
   return RPE_OK;
 }
 
@@ -346,8 +371,38 @@ int rpe_get_stage_times(rpe_handle* h, float* ms, int32_t* launches) {
 }  // extern "C"
 
 // ---------------------------------------------------------------------------------------------
-static inline void mark(rpe_handle* h, int i) {
-  if (h->profiling) cudaEventRecord(h->ev[i], h->stream);
+// Slot views: the same buffer structs with every pointer advanced to image slot img0 = 2 * pair0,
+// so the kernels (which index from 0) work on a sub-batch.
+static OrbBuffers orb_view(const rpe_handle* h, int img0) {
+  OrbBuffers b = h->ob;
+  const size_t i = (size_t)img0, L = h->cfg.nlevels, CS = h->cand_stride, KS = h->kp_stride;
+  b.pyr += i * h->pyr_stride; b.blur += i * h->pyr_stride;
+  b.cand_key += i * CS; b.sel_key += i * CS; b.sel_resp += i * CS;
+  b.cand_cnt += i * L; b.hist += i * L * 256; b.lvl_cnt += i * L; b.img_flags += i;
+  b.lvl_key += i * KS; b.lvl_resp += i * KS;
+  b.kp_x += i * KS; b.kp_y += i * KS; b.kp_size += i * KS; b.kp_angle += i * KS; b.kp_resp += i * KS;
+  b.kp_oct += i * KS; b.desc += i * KS * 32; b.kp_n += i;
+  return b;
+}
+static MatchBuffers match_view(const rpe_handle* h, int pair0) {
+  MatchBuffers m = h->mb;
+  const size_t p = (size_t)pair0, KS = h->kp_stride, MC = h->mcap;
+  m.fwd1 += p * KS; m.fwd2 += p * KS; m.bwd1 += p * KS;
+  m.m_q += p * MC; m.m_t += p * MC; m.m_d += p * MC; m.m_n += p;
+  m.pts1 += p * MC * 2; m.pts2 += p * MC * 2;
+  return m;
+}
+static GeomBuffers geom_view(const rpe_handle* h, int pair0) {
+  GeomBuffers g = h->gb;
+  const size_t p = (size_t)pair0, MC = h->mcap;
+  g.npts += p * MC * 4; g.E += p * 9; g.rmask += p * MC; g.pmask += p * MC; g.rinfo += p * 4;
+  g.R += p * 9; g.t += p * 3; g.euler += p * 3; g.pose_cnt += p; g.status += p;
+  g.tr_subset = nullptr;
+  return g;
+}
+
+static inline void mark(rpe_handle* h, int i, bool prof) {
+  if (prof) cudaEventRecord(h->ev[i], h->stream);
 }
 
 static int finish_profile(rpe_handle* h) {
@@ -356,24 +411,29 @@ static int finish_profile(rpe_handle* h) {
   return RPE_OK;
 }
 
-static int run_orb(rpe_handle* h, const Geometry& G, int n_img, int first_mark) {
-  OrbBuffers b = h->ob;
+static int clear_counters(rpe_handle* h, cudaStream_t s) {
+  const size_t nctr = (size_t)h->NI * h->cfg.nlevels * 257 + h->NI;
+  RPE_CK(cudaMemsetAsync(h->ob.cand_cnt, 0, nctr * sizeof(uint32_t), s));
+  return RPE_OK;
+}
+
+// ORB over image slots [img0, img0 + n_img) on stream s (counters already cleared)
+static int run_orb(rpe_handle* h, const Geometry& G, int img0, int n_img, cudaStream_t s, bool prof) {
+  OrbBuffers b = orb_view(h, img0);
   b.taps = G.d_taps;
   b.ftab = G.d_ftab;
   b.btab = G.d_btab;
-  const size_t nctr = (size_t)h->NI * h->cfg.nlevels * 257 + h->NI;
-  RPE_CK(cudaMemsetAsync(h->ob.cand_cnt, 0, nctr * sizeof(uint32_t), h->stream));
   int* ln = h->launches;
-  if (first_mark >= 0) mark(h, RPE_T_PYRAMID);
-  launch_pyramid(G.g, b, n_img, h->stream, &ln[RPE_T_PYRAMID]);
-  if (first_mark >= 0) mark(h, RPE_T_FAST);
-  launch_fast(G.g, b, n_img, h->stream, &ln[RPE_T_FAST]);
-  if (first_mark >= 0) mark(h, RPE_T_SELECT);
-  launch_select(G.g, b, n_img, h->stream, &ln[RPE_T_SELECT]);
-  if (first_mark >= 0) mark(h, RPE_T_BLUR);
-  launch_blur(G.g, b, n_img, h->stream, &ln[RPE_T_BLUR]);
-  if (first_mark >= 0) mark(h, RPE_T_DESCRIBE);
-  launch_describe(G.g, b, n_img, h->stream, &ln[RPE_T_DESCRIBE]);
+  mark(h, RPE_T_PYRAMID, prof);
+  launch_pyramid(G.g, b, n_img, s, &ln[RPE_T_PYRAMID]);
+  mark(h, RPE_T_FAST, prof);
+  launch_fast(G.g, b, n_img, s, &ln[RPE_T_FAST]);
+  mark(h, RPE_T_SELECT, prof);
+  launch_select(G.g, b, n_img, s, &ln[RPE_T_SELECT]);
+  mark(h, RPE_T_BLUR, prof);
+  launch_blur(G.g, b, n_img, s, &ln[RPE_T_BLUR]);
+  mark(h, RPE_T_DESCRIBE, prof);
+  launch_describe(G.g, b, n_img, s, &ln[RPE_T_DESCRIBE]);
   RPE_CK(cudaGetLastError());
   return RPE_OK;
 }
@@ -385,20 +445,22 @@ static RansacParams ransac_params(const rpe_handle* h) {
   return rp;
 }
 
-static int run_pairs(rpe_handle* h, int B) {
+// match -> sort/cut -> RANSAC -> pose over pair slots [pair0, pair0 + nb) on stream s
+static int run_pairs(rpe_handle* h, int pair0, int nb, cudaStream_t s, bool prof) {
   int* ln = h->launches;
-  mark(h, RPE_T_MATCH);
-  launch_match(h->ob, h->mb, h->kp_stride, B, h->cfg.match_mode, h->stream, &ln[RPE_T_MATCH]);
-  mark(h, RPE_T_MATCH_SORT);
-  launch_build_matches(h->ob, h->mb, h->kp_stride, h->mcap, h->sort_cap_match, B, h->cfg.match_mode, h->cfg.ratio,
-                       h->cfg.max_matches, h->stream, &ln[RPE_T_MATCH_SORT]);
-  mark(h, RPE_T_RANSAC);
-  GeomBuffers gb = h->gb;
-  gb.tr_subset = nullptr;
-  launch_normalize(h->mb, gb, h->mcap, B, h->dK, h->stream, &ln[RPE_T_RANSAC]);
-  launch_ransac(h->mb, gb, h->mcap, B, h->dK, ransac_params(h), h->stream, &ln[RPE_T_RANSAC]);
-  mark(h, RPE_T_POSE);
-  launch_pose(h->mb, gb, h->mcap, B, ransac_params(h), h->ob.img_flags, h->ob.kp_n, h->stream, &ln[RPE_T_POSE]);
+  const OrbBuffers ob = orb_view(h, 2 * pair0);
+  const MatchBuffers mb = match_view(h, pair0);
+  const GeomBuffers gb = geom_view(h, pair0);
+  mark(h, RPE_T_MATCH, prof);
+  launch_match(ob, mb, h->kp_stride, nb, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
+  mark(h, RPE_T_MATCH_SORT, prof);
+  launch_build_matches(ob, mb, h->kp_stride, h->mcap, h->sort_cap_match, nb, h->cfg.match_mode, h->cfg.ratio,
+                       h->cfg.max_matches, s, &ln[RPE_T_MATCH_SORT]);
+  mark(h, RPE_T_RANSAC, prof);
+  launch_normalize(mb, gb, h->mcap, nb, h->dK, s, &ln[RPE_T_RANSAC]);
+  launch_ransac(mb, gb, h->mcap, nb, h->dK, ransac_params(h), s, &ln[RPE_T_RANSAC]);
+  mark(h, RPE_T_POSE, prof);
+  launch_pose(mb, gb, h->mcap, nb, ransac_params(h), ob.img_flags, ob.kp_n, s, &ln[RPE_T_POSE]);
   RPE_CK(cudaGetLastError());
   return RPE_OK;
 }
@@ -409,21 +471,26 @@ static int upload_K(rpe_handle* h, const double K[9]) {
   return RPE_OK;
 }
 
-static int download_results(rpe_handle* h, int B, double* R, double* t, double* euler, int32_t* status, int32_t* info) {
-  mark(h, RPE_T_D2H);
+// async D2H of the results of pair slots [pair0, pair0 + nb) into the pinned staging buffers
+static int download_async(rpe_handle* h, int pair0, int nb, bool info, cudaStream_t s) {
   double* hd = h->h_out_d;
   int32_t* hi = h->h_out_i;
-  cudaStream_t s = h->stream;
-  RPE_CK(cudaMemcpyAsync(hd, h->gb.R, (size_t)B * 9 * sizeof(double), cudaMemcpyDeviceToHost, s));
-  RPE_CK(cudaMemcpyAsync(hd + (size_t)h->NP * 9, h->gb.t, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
-  RPE_CK(cudaMemcpyAsync(hd + (size_t)h->NP * 12, h->gb.euler, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
-  RPE_CK(cudaMemcpyAsync(hi, h->gb.status, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  const size_t NP = h->NP, p = pair0, n = nb;
+  RPE_CK(cudaMemcpyAsync(hd + p * 9, h->gb.R + p * 9, n * 9 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hd + NP * 9 + p * 3, h->gb.t + p * 3, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hd + NP * 12 + p * 3, h->gb.euler + p * 3, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hi + p, h->gb.status + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   if (info) {
-    RPE_CK(cudaMemcpyAsync(hi + h->NP, h->mb.m_n, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-    RPE_CK(cudaMemcpyAsync(hi + 2 * h->NP, h->gb.pose_cnt, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    RPE_CK(cudaMemcpyAsync(hi + NP + p, h->mb.m_n + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    RPE_CK(cudaMemcpyAsync(hi + 2 * NP + p, h->gb.pose_cnt + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   }
-  if (h->profiling) cudaEventRecord(h->ev[RPE_T_COUNT], s);
-  RPE_CK(cudaStreamSynchronize(s));
+  return RPE_OK;
+}
+
+static int finish_results(rpe_handle* h, int B, double* R, double* t, double* euler, int32_t* status, int32_t* info) {
+  double* hd = h->h_out_d;
+  int32_t* hi = h->h_out_i;
+  RPE_CK(cudaStreamSynchronize(h->stream));
   if (R) memcpy(R, hd, (size_t)B * 9 * sizeof(double));
   if (t) memcpy(t, hd + (size_t)h->NP * 9, (size_t)B * 3 * sizeof(double));
   if (euler) memcpy(euler, hd + (size_t)h->NP * 12, (size_t)B * 3 * sizeof(double));
@@ -455,6 +522,88 @@ static void reset_profile(rpe_handle* h) {
   for (int i = 0; i < RPE_T_COUNT; ++i) { h->launches[i] = 0; h->ms[i] = 0.f; }
 }
 
+// Source of one batch: host pointer arrays (img1/img2) or one device buffer.
+struct BatchSource {
+  const uint8_t* const* img1 = nullptr;
+  const uint8_t* const* img2 = nullptr;
+  bool host_contiguous = false;   // all 2B host images equally spaced, pair-interleaved, device pitch
+  ptrdiff_t host_stride = 0;
+  const uint8_t* d_images = nullptr;
+  size_t img_stride = 0;
+  size_t pitch = 0;
+};
+
+// copy the images of pair slots [pair0, pair0 + nb) into level 0 of their pyramid slabs
+static int upload_images(rpe_handle* h, const Geometry& G, const BatchSource& src, int pair0, int nb, int H, int W,
+                         cudaStream_t s) {
+  const int p0 = G.g.lv[0].pitch;
+  uint8_t* dst = h->ob.pyr + (size_t)(2 * pair0) * h->pyr_stride;
+  if (src.d_images) {
+    const uint8_t* from = src.d_images + (size_t)(2 * pair0) * src.img_stride;
+    if (src.pitch == (size_t)p0) {
+      RPE_CK(cudaMemcpy2DAsync(dst, h->pyr_stride, from, src.img_stride, src.pitch * H, 2 * nb, cudaMemcpyDeviceToDevice, s));
+    } else {
+      for (int i = 0; i < 2 * nb; ++i)
+        RPE_CK(cudaMemcpy2DAsync(dst + (size_t)i * h->pyr_stride, p0, from + (size_t)i * src.img_stride, src.pitch, W, H,
+                                 cudaMemcpyDeviceToDevice, s));
+    }
+  } else if (src.host_contiguous) {
+    RPE_CK(cudaMemcpy2DAsync(dst, h->pyr_stride, src.img1[pair0], (size_t)src.host_stride, src.pitch * H, 2 * nb,
+                             cudaMemcpyHostToDevice, s));
+  } else {
+    for (int i = 0; i < nb; ++i) {
+      RPE_CK(cudaMemcpy2DAsync(dst + (size_t)(2 * i) * h->pyr_stride, p0, src.img1[pair0 + i], src.pitch, W, H,
+                               cudaMemcpyHostToDevice, s));
+      RPE_CK(cudaMemcpy2DAsync(dst + (size_t)(2 * i + 1) * h->pyr_stride, p0, src.img2[pair0 + i], src.pitch, W, H,
+                               cudaMemcpyHostToDevice, s));
+    }
+  }
+  return RPE_OK;
+}
+
+// The whole hot path over B pairs.  Profiling: one chunk on the handle's stream with an event
+// between stages.  Otherwise: chunks round-robin over the worker streams, forked from and joined
+// back into the handle's stream.
+static int run_batch(rpe_handle* h, const BatchSource& src, int B, int H, int W, const double K[9], double* R,
+                     double* t, double* euler, int32_t* status, int32_t* info) {
+  const Geometry* G;
+  RPE_TRY(get_geometry(h, W, H, &G));
+  reset_profile(h);
+  const bool prof = h->profiling;
+  mark(h, RPE_T_H2D, prof);
+  RPE_TRY(upload_K(h, K));
+  RPE_TRY(clear_counters(h, h->stream));
+  const int chunk = prof ? B : std::min(B, h->chunk_pairs);
+  const int n_chunks = (B + chunk - 1) / chunk;
+  if (n_chunks == 1) {
+    RPE_TRY(upload_images(h, *G, src, 0, B, H, W, h->stream));
+    RPE_TRY(run_orb(h, *G, 0, 2 * B, h->stream, prof));
+    RPE_TRY(run_pairs(h, 0, B, h->stream, prof));
+    mark(h, RPE_T_D2H, prof);
+    RPE_TRY(download_async(h, 0, B, info != nullptr, h->stream));
+    if (prof) cudaEventRecord(h->ev[RPE_T_COUNT], h->stream);
+  } else {
+    const int nw = std::min(h->n_workers, n_chunks);
+    RPE_CK(cudaEventRecord(h->ev_fork, h->stream));
+    for (int w = 0; w < nw; ++w) RPE_CK(cudaStreamWaitEvent(h->wstream[w], h->ev_fork, 0));
+    for (int c = 0; c < n_chunks; ++c) {
+      cudaStream_t s = h->wstream[c % nw];
+      const int pair0 = c * chunk, nb = std::min(chunk, B - pair0);
+      RPE_TRY(upload_images(h, *G, src, pair0, nb, H, W, s));
+      RPE_TRY(run_orb(h, *G, 2 * pair0, 2 * nb, s, false));
+      RPE_TRY(run_pairs(h, pair0, nb, s, false));
+      RPE_TRY(download_async(h, pair0, nb, info != nullptr, s));
+    }
+    for (int w = 0; w < nw; ++w) {
+      RPE_CK(cudaEventRecord(h->ev_done[w], h->wstream[w]));
+      RPE_CK(cudaStreamWaitEvent(h->stream, h->ev_done[w], 0));
+    }
+  }
+  h->last_geom = G;
+  h->last_pairs = B;
+  return finish_results(h, B, R, t, euler, status, info);
+}
+
 extern "C" {
 
 int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* const* img2, int32_t B, int32_t H,
@@ -462,35 +611,19 @@ int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t*
                        int32_t* status, int32_t* info) {
   RPE_TRY(check_batch(h, B, H, W, pitch));
   if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
-  const Geometry* G;
-  RPE_TRY(get_geometry(h, W, H, &G));
-  reset_profile(h);
-  mark(h, RPE_T_H2D);
-  RPE_TRY(upload_K(h, K));
-  const int p0 = G->g.lv[0].pitch;
-  // fast path: all 2B images equally spaced in one host buffer with the device pitch -> one copy
+  BatchSource src;
+  src.img1 = img1; src.img2 = img2; src.pitch = pitch;
+  // fast path: all 2B images equally spaced in one host buffer with the device pitch -> one copy per chunk
+  const int p0 = align_up(W, 16);
   bool contiguous = (pitch == (size_t)p0);
   const ptrdiff_t stride = (const uint8_t*)img2[0] - (const uint8_t*)img1[0];
   if (contiguous && stride >= (ptrdiff_t)(pitch * H)) {
     for (int i = 0; i < B && contiguous; ++i)
       contiguous = (img1[i] == img1[0] + (ptrdiff_t)2 * i * stride) && (img2[i] == img1[i] + stride);
   } else contiguous = false;
-  if (contiguous) {
-    RPE_CK(cudaMemcpy2DAsync(h->ob.pyr, h->pyr_stride, img1[0], (size_t)stride, (size_t)pitch * H, 2 * B,
-                             cudaMemcpyHostToDevice, h->stream));
-  } else {
-    for (int i = 0; i < B; ++i) {
-      RPE_CK(cudaMemcpy2DAsync(h->ob.pyr + (size_t)(2 * i) * h->pyr_stride, p0, img1[i], pitch, W, H,
-                               cudaMemcpyHostToDevice, h->stream));
-      RPE_CK(cudaMemcpy2DAsync(h->ob.pyr + (size_t)(2 * i + 1) * h->pyr_stride, p0, img2[i], pitch, W, H,
-                               cudaMemcpyHostToDevice, h->stream));
-    }
-  }
-  RPE_TRY(run_orb(h, *G, 2 * B, 0));
-  RPE_TRY(run_pairs(h, B));
-  h->last_geom = G;
-  h->last_pairs = B;
-  return download_results(h, B, R, t, euler, status, info);
+  src.host_contiguous = contiguous;
+  src.host_stride = stride;
+  return run_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
 int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img_stride, int32_t B, int32_t H,
@@ -498,25 +631,9 @@ int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img
                               int32_t* status, int32_t* info) {
   RPE_TRY(check_batch(h, B, H, W, pitch));
   if (!d_images || !K || img_stride < pitch * (size_t)H) return fail(RPE_ERR_INVALID, "bad device image arguments");
-  const Geometry* G;
-  RPE_TRY(get_geometry(h, W, H, &G));
-  reset_profile(h);
-  mark(h, RPE_T_H2D);
-  RPE_TRY(upload_K(h, K));
-  const int p0 = G->g.lv[0].pitch;
-  if (pitch == (size_t)p0) {
-    RPE_CK(cudaMemcpy2DAsync(h->ob.pyr, h->pyr_stride, d_images, img_stride, pitch * H, 2 * B,
-                             cudaMemcpyDeviceToDevice, h->stream));
-  } else {
-    for (int i = 0; i < 2 * B; ++i)
-      RPE_CK(cudaMemcpy2DAsync(h->ob.pyr + (size_t)i * h->pyr_stride, p0, d_images + (size_t)i * img_stride, pitch, W,
-                               H, cudaMemcpyDeviceToDevice, h->stream));
-  }
-  RPE_TRY(run_orb(h, *G, 2 * B, 0));
-  RPE_TRY(run_pairs(h, B));
-  h->last_geom = G;
-  h->last_pairs = B;
-  return download_results(h, B, R, t, euler, status, info);
+  BatchSource src;
+  src.d_images = d_images; src.img_stride = img_stride; src.pitch = pitch;
+  return run_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
 int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size_t pitch, float* x, float* y,
@@ -528,7 +645,8 @@ int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size
   RPE_TRY(get_geometry(h, W, H, &G));
   reset_profile(h);
   RPE_CK(cudaMemcpy2DAsync(h->ob.pyr, G->g.lv[0].pitch, img, pitch, W, H, cudaMemcpyHostToDevice, h->stream));
-  RPE_TRY(run_orb(h, *G, 1, -1));
+  RPE_TRY(clear_counters(h, h->stream));
+  RPE_TRY(run_orb(h, *G, 0, 1, h->stream, false));
   h->last_geom = G;
   h->last_pairs = 0;
   int32_t n = 0;

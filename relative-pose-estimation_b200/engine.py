@@ -74,6 +74,10 @@ class Engine:
     def set_stream(self, cuda_stream_ptr: int | None):
         L.check(self._lib.rpe_set_stream(self._h, C.c_void_p(cuda_stream_ptr or 0)), "rpe_set_stream")
 
+    def set_pipeline(self, chunk_pairs: int, n_streams: int):
+        """Sub-batch pipeline of the batch calls (see include/rpe.h: rpe_set_pipeline)."""
+        L.check(self._lib.rpe_set_pipeline(self._h, int(chunk_pairs), int(n_streams)), "rpe_set_pipeline")
+
     def set_profiling(self, on: bool):
         L.check(self._lib.rpe_set_profiling(self._h, int(on)), "rpe_set_profiling")
 

@@ -240,3 +240,30 @@ def test_failure_statuses(engine):
     except RuntimeError:
         ok = False
     assert ok == ref_ok
+
+
+def test_pipeline_chunks_do_not_change_results(engine):
+    """rpe_set_pipeline only changes scheduling (chunks over streams): results must be identical,
+    including with a ragged last chunk and per-pair failures inside a chunk."""
+    a, b, c = load_gray("sim_000000.png"), load_gray("sim_000015.png"), load_gray("sim_000030.png")
+    blank = np.full((480, 640), 128, np.uint8)
+    K = default_K()
+    v1, v2 = [a, b, blank, a], [b, c, a, c]
+    engine.set_pipeline(4, 1)
+    want = engine.estimate_batch(v1, v2, K)
+    try:
+        for chunk, streams in [(1, 3), (3, 2), (2, 4)]:
+            engine.set_pipeline(chunk, streams)
+            got = engine.estimate_batch(v1, v2, K)
+            for k in ("R", "t", "euler", "status", "info"):
+                assert np.array_equal(got[k], want[k]), (chunk, streams, k)
+            for i in range(4):
+                m = engine.get_stage(i, 0, 9, 0, np.int32)
+                engine.set_pipeline(4, 1)
+                engine.estimate_batch(v1, v2, K)
+                assert np.array_equal(m, engine.get_stage(i, 0, 9, 0, np.int32))
+                engine.set_pipeline(chunk, streams)
+                engine.estimate_batch(v1, v2, K)
+    finally:
+        engine.set_pipeline(32, 3)
+    assert want["status"][2] & 0xFF == 1 and (want["status"][[0, 1, 3]] == 0).all()
