@@ -43,8 +43,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=128, help="pairs per GPU per step")
     ap.add_argument("--cpu-pairs", type=int, default=24, help="pairs in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--inflight", type=int, default=2, help="engine handles used alternately (batches in flight)")
     ap.add_argument("--chunk", type=int, default=32, help="pairs per pipeline chunk (rpe_set_pipeline)")
-    ap.add_argument("--streams", type=int, default=3, help="pipeline streams (rpe_set_pipeline)")
+    ap.add_argument("--streams", type=int, default=1, help="pipeline streams per handle (rpe_set_pipeline); 1 = no chunking")
     return ap.parse_args()
 
 
@@ -202,63 +203,87 @@ def run_b200(args):
     frames_np, K = make_batch(rank, B)
     host = torch.from_numpy(frames_np).pin_memory()
     dev = host.cuda(non_blocking=False)
-    eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=W, max_height=H, max_pairs=B, nfeatures=CFG["nfeatures"],
-                                                nlevels=CFG["nlevels"], match_mode=CFG["match_mode"], ratio=CFG["ratio"],
-                                                max_matches=CFG["max_matches"], ransac_max_iters=CFG["ransac_max_iters"]),
-                          device=local)
+    ecfg = rpe_b200.EngineConfig(max_width=W, max_height=H, max_pairs=B, nfeatures=CFG["nfeatures"],
+                                 nlevels=CFG["nlevels"], match_mode=CFG["match_mode"], ratio=CFG["ratio"],
+                                 max_matches=CFG["max_matches"], ransac_max_iters=CFG["ransac_max_iters"])
+    # `inflight` handles used alternately: batch n+1 is submitted before the results of batch n are
+    # waited for, so its upload / kernel heads overlap the tail of batch n (rpe_submit_batch / rpe_wait_batch)
+    engines = [rpe_b200.Engine(ecfg, device=local) for _ in range(max(1, args.inflight))]
+    eng = engines[0]
     stream = torch.cuda.Stream()
-    eng.set_stream(stream.cuda_stream)
-    eng.set_pipeline(args.chunk, args.streams)
+    streams = [stream] + [torch.cuda.Stream() for _ in engines[1:]]
+    for e, st in zip(engines, streams):
+        e.set_stream(st.cuda_stream)
+        e.set_pipeline(args.chunk, args.streams)
+    host_np = host.numpy()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step_device():
-        return eng.estimate_batch_device(dev.data_ptr(), H * W, B, H, W, W, K)
+    def run_steps(n, submit):
+        """n steps over the handles, at most len(engines) batches in flight; returns launches, last result"""
+        launches, out, q = 0, None, []
+        for i in range(n):
+            e = engines[i % len(engines)]
+            if len(q) == len(engines):
+                d = q.pop(0)
+                out = d.wait()
+                launches += sum(d.stage_times()[1].values())
+            submit(e)
+            q.append(e)
+        for d in q:
+            out = d.wait()
+            launches += sum(d.stage_times()[1].values())
+        return launches, out
 
-    def step_host():
-        return eng.estimate_batch_interleaved(host.numpy(), K)
+    submit_device = lambda e: e.submit_device(dev.data_ptr(), H * W, B, H, W, W, K)
+    submit_host = lambda e: e.submit_interleaved(host_np, K)
 
-    for _ in range(max(args.warmup, 1)):
-        out = step_device()
+    _, out = run_steps(max(args.warmup, len(engines)), submit_device)
     nkp = float(np.mean([eng.keypoints(i, v)["x"].shape[0] for i in range(min(B, 4)) for v in (0, 1)]))
     ok_frac = float((out["status"] & 0xFF == 0).mean())
 
-    def timed(fn, profile):
-        eng.set_profiling(profile)
-        acc = {k: 0.0 for k in L.RPE_T_NAMES}
-        launches = 0
+    def timed(submit):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with torch.cuda.stream(stream):
-            e0.record(stream)
-            for _ in range(args.steps):
-                fn()
-                ms, ln = eng.stage_times()
-                launches += sum(ln.values())
-                if profile:
-                    for k in acc:
-                        acc[k] += ms[k]
-            e1.record(stream)
+        e0.record(stream)
+        launches, _ = run_steps(args.steps, submit)
+        torch.cuda.synchronize()
+        e1.record(stream)
         barrier()
         ms_total = e0.elapsed_time(e1)
         if world > 1:
             tt = torch.tensor([ms_total], device="cuda")
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             ms_total = float(tt.item())
+        return ms_total, launches
+
+    def profiled():
+        """per-stage CUDA events: one handle, one chunk, stages serial (rpe_set_profiling)"""
+        eng.set_profiling(True)
+        acc = {k: 0.0 for k in L.RPE_T_NAMES}
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            eng.estimate_batch_device(dev.data_ptr(), H * W, B, H, W, W, K)
+            ms, _ = eng.stage_times()
+            for k in acc:
+                acc[k] += ms[k]
+        e1.record(stream)
+        barrier()
         eng.set_profiling(False)
-        return ms_total, acc, launches
+        return e0.elapsed_time(e1), acc
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms_dev, _, launches = timed(step_device, False)          # headline: pipelined, no per-stage events
-    for _ in range(2):
-        step_host()
-    ms_e2e, _, _ = timed(step_host, False)
-    ms_prof, stage_ms, _ = timed(step_device, True)           # per-stage CUDA events: one chunk, serial stages
+    ms_dev, launches = timed(submit_device)                   # headline: frames resident in HBM
+    run_steps(max(2, len(engines)), submit_host)
+    ms_e2e, _ = timed(submit_host)                            # pinned host frames -> results on host
+    ms_prof, stage_ms = profiled()
     clocks = sampler.stop() if rank == 0 else None
 
     if rank != 0:
@@ -328,7 +353,8 @@ def run_b200(args):
                       "pairs_per_gpu_per_step": B, "image_bytes_per_step": int(2 * B * H * W),
                       "l2_policy": "inputs larger than L2 (236 MB of frames + 1.2 GB of pyramids per step)",
                       "parallelism": f"{world} independent shards, no collective",
-                      "pipeline": {"chunk_pairs": args.chunk, "streams": args.streams},
+                      "pipeline": {"handles_in_flight": len(engines), "chunk_pairs": args.chunk,
+                                   "streams": args.streams},
                       "mean_keypoints_per_image": nkp, "ok_fraction": ok_frac},
            "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": int(2 * B * H * W + 72),
                    "d2h_bytes_per_step": int(B * (15 * 8 + 3 * 4)), "ms_per_step": ms_e2e / args.steps},

@@ -79,10 +79,13 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out);
 void rpe_destroy(rpe_handle* h);
 /* run all work of this handle on an existing CUDA stream (cudaStream_t); NULL = own stream */
 int rpe_set_stream(rpe_handle* h, void* cuda_stream);
-/* sub-batch pipeline of the batch calls: pairs are processed in chunks of `chunk_pairs`, round-robin
- * over `n_streams` (1..4) internal streams forked from / joined into the handle's stream, so the H2D
- * copy and the latency-bound kernels of one chunk overlap the dense kernels of the next.
- * Default 32 pairs x 3 streams.  Results do not depend on these settings. */
+/* sub-batch pipeline of the HOST-buffer batch calls: pairs are processed in chunks of `chunk_pairs`
+ * over internal streams forked from / joined into the handle's stream.  n_streams = 1: no pipeline
+ * (one chunk on the handle's stream); n >= 2: one copy stream + (n - 1) compute streams used
+ * round-robin, so the image upload of chunk c+1 and the kernel tails of chunk c overlap.  Default:
+ * 32 pairs x 4 streams (best for one blocking call at a time; measured 6995 vs 6392 pairs/s).  With
+ * two handles in flight (rpe_submit_batch) use n_streams = 1: batches already overlap each other.
+ * Device-resident inputs are never chunked.  Results do not depend on these settings. */
 int rpe_set_pipeline(rpe_handle* h, int32_t chunk_pairs, int32_t n_streams);
 /* capacities derived from the config: max keypoints per image, max matches per pair */
 int rpe_get_capacity(const rpe_handle* h, int32_t* kp_cap, int32_t* match_cap);
@@ -96,6 +99,20 @@ int rpe_get_capacity(const rpe_handle* h, int32_t* kp_cap, int32_t* match_cap);
 int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* const* img2,
                        int32_t B, int32_t H, int32_t W, size_t pitch, const double K[9],
                        double* R, double* t, double* euler, int32_t* status, int32_t* info);
+
+/* asynchronous form of rpe_estimate_batch: rpe_submit_batch enqueues the uploads and kernels and
+ * returns without waiting; rpe_wait_batch blocks until the results of the submitted batch are in the
+ * output pointers given at submit time.  The images and the output arrays must stay valid until
+ * rpe_wait_batch returns; one batch may be pending per handle (other calls on the handle fail with
+ * RPE_ERR_INVALID meanwhile).  Two handles used alternately overlap the upload of one batch with the
+ * kernels of the other (see bench.py e2e). */
+int rpe_submit_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* const* img2,
+                     int32_t B, int32_t H, int32_t W, size_t pitch, const double K[9],
+                     double* R, double* t, double* euler, int32_t* status, int32_t* info);
+int rpe_submit_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img_stride,
+                            int32_t B, int32_t H, int32_t W, size_t pitch, const double K[9],
+                            double* R, double* t, double* euler, int32_t* status, int32_t* info);
+int rpe_wait_batch(rpe_handle* h);
 
 /* same, inputs already resident in device memory: d_images holds 2*B images, image 2*i is
  * view 1 of pair i and 2*i+1 is view 2, each H rows of `pitch` bytes, consecutive images

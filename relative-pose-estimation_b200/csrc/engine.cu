@@ -60,8 +60,12 @@ struct rpe_handle {
   // dense kernels of the next
   static constexpr int kMaxWorkers = 4;
   cudaStream_t wstream[kMaxWorkers] = {};
-  cudaEvent_t ev_fork = nullptr, ev_done[kMaxWorkers] = {};
-  int chunk_pairs = 32, n_workers = 3;
+  // outputs of a submitted, not yet waited-for batch (rpe_submit_batch / rpe_wait_batch)
+  struct Pending { bool active = false; int B = 0; double* R = nullptr; double* t = nullptr; double* euler = nullptr;
+                   int32_t* status = nullptr; int32_t* info = nullptr; } pending;
+  static constexpr int kChunkEvents = 64;
+  cudaEvent_t ev_fork = nullptr, ev_done[kMaxWorkers] = {}, ev_chunk[kChunkEvents] = {};
+  int chunk_pairs = 32, n_workers = 4;
   int NI = 0, NP = 0;
   int kp_stride = 0, cand_stride = 0, mcap = 0, sort_cap_orb = 0, sort_cap_match = 0;
   size_t pyr_stride = 0;
@@ -295,6 +299,8 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out) {
       rc = fail(RPE_ERR_CUDA, "worker stream creation failed");
   }
   if (rc == RPE_OK && cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
+  for (int i = 0; i < rpe_handle::kChunkEvents && rc == RPE_OK; ++i)
+    if (cudaEventCreateWithFlags(&h->ev_chunk[i], cudaEventDisableTiming) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
   if (rc == RPE_OK && cudaMallocHost((void**)&h->h_out_d, NP * 15 * sizeof(double)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
   if (rc == RPE_OK && cudaMallocHost((void**)&h->h_out_i, NP * 5 * sizeof(int32_t)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
   if (rc == RPE_OK && cudaMallocHost((void**)&h->h_K, 9 * sizeof(double)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
@@ -330,6 +336,7 @@ void rpe_destroy(rpe_handle* h) {
     if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
   }
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  for (int i = 0; i < rpe_handle::kChunkEvents; ++i) if (h->ev_chunk[i]) cudaEventDestroy(h->ev_chunk[i]);
   delete h;
 }
 
@@ -445,17 +452,26 @@ static RansacParams ransac_params(const rpe_handle* h) {
   return rp;
 }
 
-// match -> sort/cut -> RANSAC -> pose over pair slots [pair0, pair0 + nb) on stream s
-static int run_pairs(rpe_handle* h, int pair0, int nb, cudaStream_t s, bool prof) {
+// match -> sort/cut over pair slots [pair0, pair0 + nb) on stream s (dense, XU-pipe bound)
+static int run_match(rpe_handle* h, int pair0, int nb, cudaStream_t s, bool prof) {
   int* ln = h->launches;
   const OrbBuffers ob = orb_view(h, 2 * pair0);
   const MatchBuffers mb = match_view(h, pair0);
-  const GeomBuffers gb = geom_view(h, pair0);
   mark(h, RPE_T_MATCH, prof);
   launch_match(ob, mb, h->kp_stride, nb, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
   mark(h, RPE_T_MATCH_SORT, prof);
   launch_build_matches(ob, mb, h->kp_stride, h->mcap, h->sort_cap_match, nb, h->cfg.match_mode, h->cfg.ratio,
                        h->cfg.max_matches, s, &ln[RPE_T_MATCH_SORT]);
+  RPE_CK(cudaGetLastError());
+  return RPE_OK;
+}
+
+// RANSAC -> pose over pair slots [pair0, pair0 + nb) on stream s (one CTA per pair: latency bound)
+static int run_geometry(rpe_handle* h, int pair0, int nb, cudaStream_t s, bool prof) {
+  int* ln = h->launches;
+  const OrbBuffers ob = orb_view(h, 2 * pair0);
+  const MatchBuffers mb = match_view(h, pair0);
+  const GeomBuffers gb = geom_view(h, pair0);
   mark(h, RPE_T_RANSAC, prof);
   launch_normalize(mb, gb, h->mcap, nb, h->dK, s, &ln[RPE_T_RANSAC]);
   launch_ransac(mb, gb, h->mcap, nb, h->dK, ransac_params(h), s, &ln[RPE_T_RANSAC]);
@@ -561,57 +577,8 @@ static int upload_images(rpe_handle* h, const Geometry& G, const BatchSource& sr
   return RPE_OK;
 }
 
-// The whole hot path over B pairs.  Profiling: one chunk on the handle's stream with an event
-// between stages.  Otherwise: chunks round-robin over the worker streams, forked from and joined
-// back into the handle's stream.
-static int run_batch(rpe_handle* h, const BatchSource& src, int B, int H, int W, const double K[9], double* R,
-                     double* t, double* euler, int32_t* status, int32_t* info) {
-  const Geometry* G;
-  RPE_TRY(get_geometry(h, W, H, &G));
-  reset_profile(h);
-  const bool prof = h->profiling;
-  mark(h, RPE_T_H2D, prof);
-  RPE_TRY(upload_K(h, K));
-  RPE_TRY(clear_counters(h, h->stream));
-  const int chunk = prof ? B : std::min(B, h->chunk_pairs);
-  const int n_chunks = (B + chunk - 1) / chunk;
-  if (n_chunks == 1) {
-    RPE_TRY(upload_images(h, *G, src, 0, B, H, W, h->stream));
-    RPE_TRY(run_orb(h, *G, 0, 2 * B, h->stream, prof));
-    RPE_TRY(run_pairs(h, 0, B, h->stream, prof));
-    mark(h, RPE_T_D2H, prof);
-    RPE_TRY(download_async(h, 0, B, info != nullptr, h->stream));
-    if (prof) cudaEventRecord(h->ev[RPE_T_COUNT], h->stream);
-  } else {
-    const int nw = std::min(h->n_workers, n_chunks);
-    RPE_CK(cudaEventRecord(h->ev_fork, h->stream));
-    for (int w = 0; w < nw; ++w) RPE_CK(cudaStreamWaitEvent(h->wstream[w], h->ev_fork, 0));
-    for (int c = 0; c < n_chunks; ++c) {
-      cudaStream_t s = h->wstream[c % nw];
-      const int pair0 = c * chunk, nb = std::min(chunk, B - pair0);
-      RPE_TRY(upload_images(h, *G, src, pair0, nb, H, W, s));
-      RPE_TRY(run_orb(h, *G, 2 * pair0, 2 * nb, s, false));
-      RPE_TRY(run_pairs(h, pair0, nb, s, false));
-      RPE_TRY(download_async(h, pair0, nb, info != nullptr, s));
-    }
-    for (int w = 0; w < nw; ++w) {
-      RPE_CK(cudaEventRecord(h->ev_done[w], h->wstream[w]));
-      RPE_CK(cudaStreamWaitEvent(h->stream, h->ev_done[w], 0));
-    }
-  }
-  h->last_geom = G;
-  h->last_pairs = B;
-  return finish_results(h, B, R, t, euler, status, info);
-}
-
-extern "C" {
-
-int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* const* img2, int32_t B, int32_t H,
-                       int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
-                       int32_t* status, int32_t* info) {
-  RPE_TRY(check_batch(h, B, H, W, pitch));
-  if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
-  BatchSource src;
+static void fill_host_source(BatchSource& src, const uint8_t* const* img1, const uint8_t* const* img2, int B, int H,
+                             int W, size_t pitch) {
   src.img1 = img1; src.img2 = img2; src.pitch = pitch;
   // fast path: all 2B images equally spaced in one host buffer with the device pitch -> one copy per chunk
   const int p0 = align_up(W, 16);
@@ -623,7 +590,120 @@ int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t*
   } else contiguous = false;
   src.host_contiguous = contiguous;
   src.host_stride = stride;
+}
+
+// The whole hot path over B pairs.  Profiling (or n_streams == 1): one chunk on the handle's stream,
+// with an event between stages when profiling.  Otherwise a copy / dense / tail stream pipeline over
+// chunks, forked from and joined back into the handle's stream.
+static int enqueue_batch(rpe_handle* h, const BatchSource& src, int B, int H, int W, const double K[9], double* R,
+                         double* t, double* euler, int32_t* status, int32_t* info) {
+  if (h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is still pending: call rpe_wait_batch first");
+  const Geometry* G;
+  RPE_TRY(get_geometry(h, W, H, &G));
+  reset_profile(h);
+  const bool prof = h->profiling;
+  mark(h, RPE_T_H2D, prof);
+  RPE_TRY(upload_K(h, K));
+  RPE_TRY(clear_counters(h, h->stream));
+  // device-resident inputs have no upload to hide: one chunk (chunking only costs kernel tails)
+  const int chunk = (prof || h->n_workers < 2 || src.d_images) ? B : std::min(B, h->chunk_pairs);
+  const int n_chunks = (B + chunk - 1) / chunk;
+  if (n_chunks == 1) {
+    RPE_TRY(upload_images(h, *G, src, 0, B, H, W, h->stream));
+    RPE_TRY(run_orb(h, *G, 0, 2 * B, h->stream, prof));
+    RPE_TRY(run_match(h, 0, B, h->stream, prof));
+    RPE_TRY(run_geometry(h, 0, B, h->stream, prof));
+    mark(h, RPE_T_D2H, prof);
+    RPE_TRY(download_async(h, 0, B, info != nullptr, h->stream));
+    if (prof) cudaEventRecord(h->ev[RPE_T_COUNT], h->stream);
+  } else {
+    // copy stream + (n_workers - 1) compute streams.  The image upload of chunk c+1 runs under the
+    // kernels of chunk c; chunks alternate between the compute streams so that the tail of one
+    // chunk's kernels (and its latency-bound RANSAC / pose) is filled by the next chunk's kernels.
+    static const int tail_mode = getenv("RPE_PIPE_TAIL") ? atoi(getenv("RPE_PIPE_TAIL")) : 0;   // experiment knob
+    cudaStream_t s_copy = h->wstream[0];
+    const int nc = h->n_workers - 1;
+    RPE_CK(cudaEventRecord(h->ev_fork, h->stream));
+    for (int w = 0; w <= nc; ++w) RPE_CK(cudaStreamWaitEvent(h->wstream[w], h->ev_fork, 0));
+    for (int c = 0; c < n_chunks; ++c) {
+      const int pair0 = c * chunk, nb = std::min(chunk, B - pair0);
+      cudaEvent_t e_up = h->ev_chunk[(2 * c) % rpe_handle::kChunkEvents];
+      cudaEvent_t e_dense = h->ev_chunk[(2 * c + 1) % rpe_handle::kChunkEvents];
+      cudaStream_t s_dense = tail_mode ? h->wstream[1] : h->wstream[1 + c % nc];
+      cudaStream_t s_tail = (tail_mode && nc >= 2) ? h->wstream[2] : s_dense;
+      RPE_TRY(upload_images(h, *G, src, pair0, nb, H, W, s_copy));
+      RPE_CK(cudaEventRecord(e_up, s_copy));
+      RPE_CK(cudaStreamWaitEvent(s_dense, e_up, 0));
+      RPE_TRY(run_orb(h, *G, 2 * pair0, 2 * nb, s_dense, false));
+      RPE_TRY(run_match(h, pair0, nb, s_dense, false));
+      if (s_tail != s_dense) {
+        RPE_CK(cudaEventRecord(e_dense, s_dense));
+        RPE_CK(cudaStreamWaitEvent(s_tail, e_dense, 0));
+      }
+      RPE_TRY(run_geometry(h, pair0, nb, s_tail, false));
+      RPE_TRY(download_async(h, pair0, nb, info != nullptr, s_tail));
+    }
+    for (int w = 0; w <= nc; ++w) {
+      RPE_CK(cudaEventRecord(h->ev_done[w], h->wstream[w]));
+      RPE_CK(cudaStreamWaitEvent(h->stream, h->ev_done[w], 0));
+    }
+  }
+  h->last_geom = G;
+  h->last_pairs = B;
+  h->pending.active = true; h->pending.B = B;
+  h->pending.R = R; h->pending.t = t; h->pending.euler = euler; h->pending.status = status; h->pending.info = info;
+  return RPE_OK;
+}
+
+static int wait_batch(rpe_handle* h) {
+  if (!h->pending.active) return fail(RPE_ERR_INVALID, "no submitted batch to wait for");
+  const rpe_handle::Pending p = h->pending;
+  h->pending.active = false;
+  RPE_CK(cudaSetDevice(h->device));
+  return finish_results(h, p.B, p.R, p.t, p.euler, p.status, p.info);
+}
+
+static int run_batch(rpe_handle* h, const BatchSource& src, int B, int H, int W, const double K[9], double* R,
+                     double* t, double* euler, int32_t* status, int32_t* info) {
+  RPE_TRY(enqueue_batch(h, src, B, H, W, K, R, t, euler, status, info));
+  return wait_batch(h);
+}
+
+extern "C" {
+
+int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* const* img2, int32_t B, int32_t H,
+                       int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
+                       int32_t* status, int32_t* info) {
+  RPE_TRY(check_batch(h, B, H, W, pitch));
+  if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
+  BatchSource src;
+  fill_host_source(src, img1, img2, B, H, W, pitch);
   return run_batch(h, src, B, H, W, K, R, t, euler, status, info);
+}
+
+int rpe_submit_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* const* img2, int32_t B, int32_t H,
+                     int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
+                     int32_t* status, int32_t* info) {
+  RPE_TRY(check_batch(h, B, H, W, pitch));
+  if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
+  BatchSource src;
+  fill_host_source(src, img1, img2, B, H, W, pitch);
+  return enqueue_batch(h, src, B, H, W, K, R, t, euler, status, info);
+}
+
+int rpe_submit_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img_stride, int32_t B, int32_t H,
+                            int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
+                            int32_t* status, int32_t* info) {
+  RPE_TRY(check_batch(h, B, H, W, pitch));
+  if (!d_images || !K || img_stride < pitch * (size_t)H) return fail(RPE_ERR_INVALID, "bad device image arguments");
+  BatchSource src;
+  src.d_images = d_images; src.img_stride = img_stride; src.pitch = pitch;
+  return enqueue_batch(h, src, B, H, W, K, R, t, euler, status, info);
+}
+
+int rpe_wait_batch(rpe_handle* h) {
+  if (!h) return fail(RPE_ERR_INVALID, "null handle");
+  return wait_batch(h);
 }
 
 int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img_stride, int32_t B, int32_t H,
@@ -639,6 +719,7 @@ int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img
 int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size_t pitch, float* x, float* y,
                    float* size, float* angle, float* response, int32_t* octave, uint8_t* desc, int32_t* n_out,
                    int32_t* flags_out) {
+  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   RPE_TRY(check_batch(h, 1, H, W, pitch));
   if (!img || !n_out) return fail(RPE_ERR_INVALID, "null argument");
   const Geometry* G;
@@ -671,6 +752,7 @@ int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size
 
 int rpe_match(rpe_handle* h, const uint8_t* desc1, int32_t n1, const uint8_t* desc2, int32_t n2, int32_t* matches,
               int32_t* m_out) {
+  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   if (!h || !m_out || n1 < 0 || n2 < 0) return fail(RPE_ERR_INVALID, "bad argument");
   if (n1 > h->kp_stride || n2 > h->kp_stride) return fail(RPE_ERR_CAPACITY, "more descriptors than the handle's keypoint capacity");
   RPE_CK(cudaSetDevice(h->device));
@@ -718,6 +800,7 @@ static int upload_points(rpe_handle* h, const float* pts1, const float* pts2, in
 
 int rpe_find_essential(rpe_handle* h, const float* pts1, const float* pts2, int32_t m, const double K[9], double* E,
                        uint8_t* mask, int32_t* info) {
+  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   if (!h || !K || (m > 0 && (!pts1 || !pts2))) return fail(RPE_ERR_INVALID, "bad argument");
   RPE_CK(cudaSetDevice(h->device));
   reset_profile(h);
@@ -757,6 +840,7 @@ int rpe_ransac_trace(rpe_handle* h, int32_t max_hyp, int32_t* subset, int32_t* n
 
 int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const float* pts2, int32_t m,
                      const double K[9], double* R, double* t, double* euler, int32_t* count, uint8_t* mask) {
+  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   if (!h || !E || !K || (m > 0 && (!pts1 || !pts2))) return fail(RPE_ERR_INVALID, "bad argument");
   RPE_CK(cudaSetDevice(h->device));
   reset_profile(h);
@@ -776,6 +860,7 @@ int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const 
 }
 
 int rpe_get_stage(rpe_handle* h, int32_t pair, int32_t view, int32_t stage, int32_t arg, void* out, size_t* n) {
+  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   if (!h || !n || !out) return fail(RPE_ERR_INVALID, "null argument");
   if (pair < 0 || pair >= h->NP || view < 0 || view > 1) return fail(RPE_ERR_INVALID, "bad pair/view");
   RPE_CK(cudaSetDevice(h->device));

@@ -3,11 +3,14 @@
 // max_matches cut (src/core/pose_estimator.py:131, :144-151) and, for BASELINE configs 3-5,
 // knnMatch(k=2) + ratio test.
 //
-// k_hamming: INT-pipe bound (xor + popc), not HBM bound: each thread keeps kQPT query
+// k_hamming: bound by the XU pipe (POPC, 16 lanes/clk/SM), not by HBM; carry-save adders on the
+// ALU pipe (match_math.cuh) cut the POPCs per 256-bit distance from 8 to 5.  Each thread keeps kQPT query
 // descriptors (8 x u32 each) in registers, train descriptors stream through a shared-memory
 // tile read with 128-bit broadcast loads; nearest / second nearest are tracked as packed
 // (dist << 20 | index) keys, which reproduces OpenCV's tie rule (lowest index) for free.
+#include <cstdlib>
 #include "rpe_device.cuh"
+#include "match_math.cuh"
 
 namespace rpe {
 
@@ -16,7 +19,7 @@ constexpr int kQPT = 2;                       // queries per thread
 constexpr int kQPB = kMatchThreads * kQPT;    // queries per block
 constexpr int kTrainTile = 128;               // train descriptors per shared-memory tile
 
-template <bool kTop2>
+template <bool kTop2, bool kCsa4>
 __global__ void __launch_bounds__(kMatchThreads)
 k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride,
           uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
@@ -52,9 +55,7 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
       const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
 #pragma unroll
       for (int k = 0; k < kQPT; ++k) {
-        const uint32_t d = __popc(q[k][0] ^ a.x) + __popc(q[k][1] ^ a.y) + __popc(q[k][2] ^ a.z) +
-                           __popc(q[k][3] ^ a.w) + __popc(q[k][4] ^ b.x) + __popc(q[k][5] ^ b.y) +
-                           __popc(q[k][6] ^ b.z) + __popc(q[k][7] ^ b.w);
+        const uint32_t d = hamming256<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w);
         const uint32_t key = pack_nn(d, (uint32_t)(t0 + j));
         if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
         best1[k] = min(best1[k], key);
@@ -75,13 +76,12 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
 void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int mode,
                   cudaStream_t s, int* launches) {
   const int qblocks = (kp_stride + kQPB - 1) / kQPB;
-  if (mode == RPE_MATCH_RATIO) {
-    dim3 grid(qblocks, n_pairs, 1);
-    k_hamming<true><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, mb.fwd1, mb.fwd2, mb.bwd1);
-  } else {
-    dim3 grid(qblocks, n_pairs, 2);
-    k_hamming<false><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, mb.fwd1, mb.fwd2, mb.bwd1);
-  }
+  static const int variant = getenv("RPE_MATCH_VARIANT") ? atoi(getenv("RPE_MATCH_VARIANT")) : 0;   // tuning knob
+  const bool top2 = mode == RPE_MATCH_RATIO;
+  dim3 grid(qblocks, n_pairs, top2 ? 1 : 2);
+  auto k = top2 ? (variant == 1 ? k_hamming<true, true> : k_hamming<true, false>)
+                : (variant == 1 ? k_hamming<false, true> : k_hamming<false, false>);
+  k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, mb.fwd1, mb.fwd2, mb.bwd1);
   ++*launches;
 }
 

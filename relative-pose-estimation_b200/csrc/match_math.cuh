@@ -1,0 +1,63 @@
+// match_math.cuh — per-element arithmetic of the Hamming matcher (host/device, see rpe_hd.cuh).
+//
+// hamming256: popcount(q xor t) over 256 bits.  On B200 POPC runs on the XU pipe at 16 lanes/clk/SM
+// (a quarter of the ALU rate) and the plain 8 x (XOR, POPC) form is bound by it (ncu:
+// sm__inst_executed_pipe_xu 90 %).  Three carry-save adders (LOP3 0x96 = xor3, 0xE8 = majority) on
+// the ALU pipe fold the eight xor words into two words of weight 1 and three of weight 2, so only
+// five POPCs are issued per distance; with kCsa4 a fourth adder folds the weight-2 words into one
+// of weight 2 and one of weight 4 (four POPCs).  Exact integer arithmetic either way.
+#pragma once
+#include "rpe_hd.cuh"
+
+namespace rpe {
+
+RPE_HD uint32_t popc32(uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  return (uint32_t)__popc(v);
+#else
+  return (uint32_t)__builtin_popcount(v);
+#endif
+}
+RPE_HD uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) {
+#if defined(__CUDA_ARCH__)
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+#else
+  return a ^ b ^ c;
+#endif
+}
+RPE_HD uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) {
+#if defined(__CUDA_ARCH__)
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+#else
+  return (a & b) | (a & c) | (b & c);
+#endif
+}
+
+template <bool kCsa4>
+RPE_HD uint32_t hamming256(const uint32_t q[8], uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, uint32_t t4,
+                           uint32_t t5, uint32_t t6, uint32_t t7) {
+  const uint32_t x0 = q[0] ^ t0, x1 = q[1] ^ t1, x2 = q[2] ^ t2, x3 = q[3] ^ t3;
+  const uint32_t x4 = q[4] ^ t4, x5 = q[5] ^ t5, x6 = q[6] ^ t6, x7 = q[7] ^ t7;
+  const uint32_t s0 = xor3(x0, x1, x2), c0 = maj3(x0, x1, x2);
+  const uint32_t s1 = xor3(x3, x4, x5), c1 = maj3(x3, x4, x5);
+  const uint32_t s2 = xor3(s0, s1, x6), c2 = maj3(s0, s1, x6);
+  const uint32_t ones = popc32(s2) + popc32(x7);
+  if (kCsa4) {
+    const uint32_t s3 = xor3(c0, c1, c2), c3 = maj3(c0, c1, c2);
+    return ones + 2u * popc32(s3) + 4u * popc32(c3);
+  }
+  return ones + 2u * (popc32(c0) + popc32(c1) + popc32(c2));
+}
+
+// reference form (tests): eight independent popcounts
+RPE_HD uint32_t hamming256_plain(const uint32_t q[8], const uint32_t t[8]) {
+  uint32_t d = 0;
+  for (int i = 0; i < 8; ++i) d += popc32(q[i] ^ t[i]);
+  return d;
+}
+
+}  // namespace rpe

@@ -127,6 +127,38 @@ class Engine:
                                              _ptr(e), _ptr(st), _ptr(info)), "rpe_estimate_batch")
         return {"R": R, "t": t, "euler": e, "status": st, "info": info}
 
+    def submit_interleaved(self, frames: np.ndarray, K):
+        """Asynchronous estimate_batch_interleaved (rpe_submit_batch): returns at once; ``wait()``
+        returns the result dict.  ``frames`` must stay alive (and unchanged) until then."""
+        B = frames.shape[0] // 2
+        H, W = frames.shape[1:]
+        base = frames.ctypes.data
+        step = frames.strides[0]
+        p1 = (C.c_void_p * B)(*[base + (2 * i) * step for i in range(B)])
+        p2 = (C.c_void_p * B)(*[base + (2 * i + 1) * step for i in range(B)])
+        K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
+        R, t, e, st, info = self._outputs(B)
+        L.check(self._lib.rpe_submit_batch(self._h, p1, p2, B, H, W, frames.strides[1], _ptr(K), _ptr(R), _ptr(t),
+                                           _ptr(e), _ptr(st), _ptr(info)), "rpe_submit_batch")
+        self._pending = ({"R": R, "t": t, "euler": e, "status": st, "info": info}, frames, K)
+        return self
+
+    def submit_device(self, dev_ptr: int, img_stride: int, B: int, H: int, W: int, pitch: int, K):
+        """Asynchronous estimate_batch_device (rpe_submit_batch_device); ``wait()`` returns the results."""
+        K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
+        R, t, e, st, info = self._outputs(B)
+        L.check(self._lib.rpe_submit_batch_device(self._h, C.c_void_p(dev_ptr), img_stride, B, H, W, pitch, _ptr(K),
+                                                  _ptr(R), _ptr(t), _ptr(e), _ptr(st), _ptr(info)),
+                "rpe_submit_batch_device")
+        self._pending = ({"R": R, "t": t, "euler": e, "status": st, "info": info}, None, K)
+        return self
+
+    def wait(self):
+        """Block until the submitted batch is done (rpe_wait_batch) and return its result dict."""
+        L.check(self._lib.rpe_wait_batch(self._h), "rpe_wait_batch")
+        out, self._pending = self._pending[0], None
+        return out
+
     def estimate_batch_device(self, dev_ptr: int, img_stride: int, B: int, H: int, W: int, pitch: int, K):
         """Inputs resident in device memory (e.g. a torch uint8 CUDA tensor's data_ptr())."""
         K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)

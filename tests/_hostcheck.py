@@ -152,3 +152,14 @@ def solve_poly10(c):
     out = np.zeros((10, 2))
     lib().hc_solve_poly10(_p(c), _p(out))
     return out[:, 0] + 1j * out[:, 1]
+
+
+def hamming(q, t, mode=0):
+    """all-pairs 256-bit Hamming distances through the kernel's carry-save arithmetic (match_math.cuh)"""
+    q = np.ascontiguousarray(q, np.uint8); t = np.ascontiguousarray(t, np.uint8)
+    out = np.zeros((q.shape[0], t.shape[0]), np.int32)
+    f = lib().hc_hamming
+    f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    f.restype = None
+    f(_p(q), q.shape[0], _p(t), t.shape[0], mode, _p(out))
+    return out

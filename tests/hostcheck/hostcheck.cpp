@@ -5,9 +5,22 @@
 #include <cstring>
 #include "orb_math.cuh"
 #include "geom_math.cuh"
+#include "match_math.cuh"
 using namespace rpe;
 
 extern "C" {
+
+// all-pairs Hamming distances with the kernel's carry-save form (mode 0: 3 adders, 1: 4 adders, 2: plain)
+void hc_hamming(const uint32_t* q, int nq, const uint32_t* t, int nt, int mode, int* out) {
+  for (int i = 0; i < nq; ++i)
+    for (int j = 0; j < nt; ++j) {
+      const uint32_t* a = q + 8 * i;
+      const uint32_t* b = t + 8 * j;
+      out[i * nt + j] = mode == 0   ? (int)hamming256<false>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7])
+                        : mode == 1 ? (int)hamming256<true>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7])
+                                    : (int)hamming256_plain(a, b);
+    }
+}
 
 void hc_resize(const uint8_t* src, int sw, int sh, uint8_t* dst, int dw, int dh, const int* xo,
                const int* xc, const int* yo, const int* yc) {
@@ -81,6 +94,7 @@ void hc_cheirality(const double* R, const double* t, const double* x1, const dou
     ok[i] = triangulate_cheirality(R, t, x1[2 * i], x1[2 * i + 1], x2[2 * i], x2[2 * i + 1], dist);
 }
 void hc_euler(const double* R, int conv, double* ypr) { rotation_to_euler(R, conv, ypr); }
+int hc_dk_iters(void) { return g_dk_iters_last; }
 void hc_solve_poly10(const double* c, double* roots_re_im) {
   Cplx r[10];
   solve_poly10(c, r, 300);

@@ -267,3 +267,31 @@ def test_pipeline_chunks_do_not_change_results(engine):
     finally:
         engine.set_pipeline(32, 3)
     assert want["status"][2] & 0xFF == 1 and (want["status"][[0, 1, 3]] == 0).all()
+
+
+def test_submit_wait_equals_blocking_call(engine):
+    """rpe_submit_batch / rpe_wait_batch over two handles in flight == the blocking call; a second
+    submit on a busy handle and stage calls while a batch is pending are refused."""
+    import rpe_b200
+    from rpe_b200._lib import RpeError
+    a, b, c = load_gray("sim_000000.png"), load_gray("sim_000015.png"), load_gray("sim_000030.png")
+    K = default_K()
+    frames1 = np.ascontiguousarray(np.stack([a, b, b, c]))
+    frames2 = np.ascontiguousarray(np.stack([a, c, b, a]))
+    want1 = engine.estimate_batch_interleaved(frames1, K)
+    want2 = engine.estimate_batch_interleaved(frames2, K)
+    other = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=640, max_height=480, max_pairs=2))
+    try:
+        engine.submit_interleaved(frames1, K)
+        other.submit_interleaved(frames2, K)
+        with pytest.raises(RpeError):
+            engine.submit_interleaved(frames2, K)
+        with pytest.raises(RpeError):
+            engine.orb_detect(a)
+        got1, got2 = engine.wait(), other.wait()
+        for k in ("R", "t", "euler", "status", "info"):
+            assert np.array_equal(got1[k], want1[k]) and np.array_equal(got2[k], want2[k]), k
+        with pytest.raises(RpeError):
+            engine.wait()
+    finally:
+        other.close()

@@ -142,3 +142,16 @@ def test_solve_poly10_against_numpy_roots():
         got = hc.solve_poly10(c)
         for r in roots:
             assert np.abs(got - r).min() < 1e-7
+
+
+def test_hamming_carry_save_forms_are_exact():
+    """match_math.cuh: 3- and 4-adder carry-save popcount == 8 plain popcounts == numpy, incl. extremes."""
+    rng = np.random.default_rng(7)
+    q = rng.integers(0, 256, (96, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (80, 32), dtype=np.uint8)
+    q[0] = 0; q[1] = 255; t[0] = 0; t[1] = 255; t[2] = q[5]
+    q[2] = np.unpackbits(np.arange(32, dtype=np.uint8))[:32] * 255     # sparse / dense word mixes
+    want = np.unpackbits(q[:, None, :] ^ t[None, :, :], axis=2).sum(axis=2).astype(np.int32)
+    for mode in (0, 1, 2):
+        assert np.array_equal(hc.hamming(q, t, mode), want), mode
+    assert want[1, 0] == 256 and want[0, 0] == 0 and want[5, 2] == 0
