@@ -164,6 +164,13 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
       L.ytab = (int)G.taps.size(); linear_exact_taps(h[l - 1], h[l], G.taps);
     }
   }
+  // k_resize_strip needs x0[k] - x0[first of its aligned group of 4] <= 6 for every output column
+  g.resize_strip_ok = 1;
+  for (int l = 1; l < c.nlevels; ++l) {
+    const int2* xt = G.taps.data() + g.lv[l].xtab;
+    for (int x = 0; x < w[l]; ++x)
+      if (xt[x].x - xt[x & ~3].x > 6) g.resize_strip_ok = 0;
+  }
   g.total_tiles = tile0;
   g.total_ftiles = ftile0;
   g.total_bitems = (int)G.btab.size();

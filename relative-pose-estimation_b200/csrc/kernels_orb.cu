@@ -32,11 +32,82 @@ k_resize(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int
   *reinterpret_cast<uint32_t*>(dst + (size_t)y * d.pitch + x4) = out;
 }
 
+// Fast path for scale factors <= 4/3 (ORB's 1.1 / 1.2): one thread = 4 adjacent output columns x a
+// strip of kResizeRows output rows.  The 4 x 2 horizontal taps of the thread lie within 8
+// consecutive source bytes, so one source row costs three aligned word loads, two funnel shifts,
+// and per output column one PRMT (pick the two neighbours) + one DP2A (c0 * a + c1 * b in 8.8).
+// Row results are kept in registers while the strip walks down: consecutive output rows share
+// a source row, so ~1.1 horizontal passes per output row instead of 2.  Same integer
+// arithmetic as resize_px (orb_math.cuh), bit for bit.
+constexpr int kResizeRows = 8;
+
+__global__ void __launch_bounds__(256)
+k_resize_strip(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,
+               int level) {
+  const LevelGeom& d = g.lv[level];
+  const LevelGeom& s = g.lv[level - 1];
+  const int img = blockIdx.z;
+  const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int y_first = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
+  if (y_first >= d.h || x4 >= d.pitch) return;
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + s.off;
+  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
+  // horizontal taps of the four columns
+  uint32_t sel[4], wgt[4];
+  int xbase;
+  {
+    const int2 t0 = taps[d.xtab + min(x4, d.w - 1)];
+    xbase = t0.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int2 t = taps[d.xtab + min(x4 + k, d.w - 1)];
+      const uint32_t r = (uint32_t)(t.x - xbase);          // 0 .. 6 (checked on the host)
+      sel[k] = r | ((r + 1u) << 4) | 0x8800u;               // bytes r, r+1 of the window; upper bytes unused
+      wgt[k] = (256u - (uint32_t)t.y) | ((uint32_t)t.y << 16);   // {c0, c1} as two u16
+    }
+  }
+  const int abase = xbase & ~3, sh8 = (xbase & 3) * 8;
+  const int sp = s.pitch, last_row = s.h - 1;
+  auto hrow = [&](int row, uint32_t* h) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (size_t)row * sp + abase);
+    const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+    const uint32_t lo = __funnelshift_r(w0, w1, sh8), hi = __funnelshift_r(w1, w2, sh8);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = __dp2a_lo(wgt[k], __byte_perm(lo, hi, sel[k]), 0u);
+  };
+  uint32_t hA[4], hB[4];
+  int ra = -2;
+  const int y_end = min(y_first + kResizeRows, d.h);
+  for (int y = y_first; y < y_end; ++y) {
+    const int2 ty = taps[d.ytab + y];
+    if (ty.x != ra) {
+      if (ty.x == ra + 1) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) hA[k] = hB[k];
+      } else {
+        hrow(ty.x, hA);
+      }
+      ra = ty.x;
+      hrow(min(ra + 1, last_row), hB);
+    }
+    const uint32_t cy1 = (uint32_t)ty.y, cy0 = 256u - cy1;
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o[k] = min((cy0 * hA[k] + cy1 * hB[k] + 32768u) >> 16, 255u);
+    *reinterpret_cast<uint32_t*>(dst + (size_t)y * d.pitch + x4) = o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
+  }
+}
+
 void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   for (int l = 1; l < g.nlevels; ++l) {
     const LevelGeom& d = g.lv[l];
-    dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 7) / 8, n_img), block(32, 8);
-    k_resize<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
+    if (g.resize_strip_ok) {
+      dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
+      k_resize_strip<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
+    } else {
+      dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 7) / 8, n_img), block(32, 8);
+      k_resize<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
+    }
     ++*launches;
   }
 }
@@ -417,50 +488,118 @@ void launch_blur(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t 
 }
 
 // ------------------------------------------------------------------ K5/K7: orientation + rBRIEF + keypoint fields
+// One CTA (4 warps) = 32 consecutive keypoints of one image; one WARP per keypoint for the two
+// gather-heavy parts, so that every load instruction of a warp stays inside one patch:
+//  (0) threads 0..31: locate keypoint (level, index in level), write x / y / size / response / octave;
+//  (1) warp per keypoint, lane = patch column u = lane - 15: integer moments m10, m01 over the
+//      31 rows of the circular patch (31 coalesced byte loads), warp-reduced, fastAtan2;
+//  (2) threads 0..31: steering coefficients (double cos / sin), one keypoint per thread;
+//  (3) warp per keypoint, lane = descriptor byte: its 8 tests (pattern slice held in registers for
+//      the whole CTA), 16 gathers from the blurred level, one coalesced 32-byte store.
+constexpr int kDescKp = 32;   // keypoints per CTA
+
 __global__ void __launch_bounds__(128)
 k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
            const uint32_t* __restrict__ lvl_key, const float* __restrict__ lvl_resp,
            const uint32_t* __restrict__ lvl_cnt, float* __restrict__ kp_x, float* __restrict__ kp_y,
            float* __restrict__ kp_size, float* __restrict__ kp_angle, float* __restrict__ kp_resp,
            int32_t* __restrict__ kp_oct, uint8_t* __restrict__ desc, int32_t* __restrict__ kp_n) {
-  const int img = blockIdx.y;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  // locate (level, index in level)
-  int level = -1, base = 0, total = 0;
-  for (int l = 0; l < g.nlevels; ++l) {
-    const int c = (int)lvl_cnt[img * g.nlevels + l];
-    if (level < 0 && i < total + c) { level = l; base = total; }
-    total += c;
+  __shared__ int s_level[kDescKp], s_x[kDescKp], s_y[kDescKp], s_cx[kDescKp], s_cy[kDescKp];
+  __shared__ float s_angle[kDescKp], s_a[kDescKp], s_b[kDescKp];
+  __shared__ int s_total;
+  const int img = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int i0 = blockIdx.x * kDescKp;
+  // (0) locate
+  if (tid < kDescKp) {
+    const int i = i0 + tid;
+    int level = -1, base = 0, total = 0;
+    for (int l = 0; l < g.nlevels; ++l) {
+      const int c = (int)lvl_cnt[img * g.nlevels + l];
+      if (level < 0 && i < total + c) { level = l; base = total; }
+      total += c;
+    }
+    if (i == 0) kp_n[img] = total;
+    if (tid == 0) s_total = total;
+    s_level[tid] = level;
+    if (level >= 0) {
+      const LevelGeom& L = g.lv[level];
+      const int j = i - base;
+      const uint32_t key = lvl_key[(size_t)img * g.kp_stride + L.kp_off + j];
+      const int x = key & 0xfff, y = (key >> 12) & 0xfff;
+      s_x[tid] = x; s_y[tid] = y;
+      const float px = f32_mul((float)x, L.scale), py = f32_mul((float)y, L.scale);
+      const size_t o = (size_t)img * g.kp_stride + i;
+      kp_x[o] = px;
+      kp_y[o] = py;
+      kp_size[o] = f32_mul(31.0f, L.scale);
+      kp_resp[o] = lvl_resp[(size_t)img * g.kp_stride + L.kp_off + j];
+      kp_oct[o] = level;
+      // descriptor centre exactly as computeOrbDescriptors: cvRound(pt * (1.f / scale))
+      const float inv = f32_div(1.0f, L.scale);
+      s_cx[tid] = f32_rint(f32_mul(px, inv));
+      s_cy[tid] = f32_rint(f32_mul(py, inv));
+    }
   }
-  if (i == 0) kp_n[img] = total;
-  if (level < 0) return;
-  const LevelGeom& L = g.lv[level];
-  const int j = i - base;
-  const uint32_t key = lvl_key[(size_t)img * g.kp_stride + L.kp_off + j];
-  const int x = key & 0xfff, y = (key >> 12) & 0xfff;
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
-  const uint8_t* bl = blur + (size_t)img * g.pyr_stride + L.off;
-  const float angle = ic_angle(src + (size_t)y * L.pitch + x, L.pitch);
-  const float px = f32_mul((float)x, L.scale), py = f32_mul((float)y, L.scale);
-  const size_t o = (size_t)img * g.kp_stride + i;
-  kp_x[o] = px;
-  kp_y[o] = py;
-  kp_size[o] = f32_mul(31.0f, L.scale);
-  kp_angle[o] = angle;
-  kp_resp[o] = lvl_resp[(size_t)img * g.kp_stride + L.kp_off + j];
-  kp_oct[o] = level;
-  // descriptor centre exactly as computeOrbDescriptors: cvRound(pt * (1.f / scale))
-  const float inv = f32_div(1.0f, L.scale);
-  const int cx = f32_rint(f32_mul(px, inv)), cy = f32_rint(f32_mul(py, inv));
-  uint32_t d[8];
-  brief256(bl + (size_t)cy * L.pitch + cx, L.pitch, angle, d);
-  uint4* dp = reinterpret_cast<uint4*>(desc + o * 32);
-  dp[0] = make_uint4(d[0], d[1], d[2], d[3]);
-  dp[1] = make_uint4(d[4], d[5], d[6], d[7]);
+  __syncthreads();
+  const int nk = min(kDescKp, s_total - i0);
+  if (nk <= 0) return;
+  // this lane's 8 tests (32 bytes of the pattern table)
+  uint32_t pat[8];
+  {
+    const uint4* pp = reinterpret_cast<const uint4*>(kBriefPattern_dev + 32 * lane);
+    const uint4 p0 = pp[0], p1 = pp[1];
+    pat[0] = p0.x; pat[1] = p0.y; pat[2] = p0.z; pat[3] = p0.w;
+    pat[4] = p1.x; pat[5] = p1.y; pat[6] = p1.z; pat[7] = p1.w;
+  }
+  // (1) orientation
+  {
+    const int u = lane - 15;
+    const int au = u < 0 ? -u : u;
+    for (int k = warp; k < nk; k += 4) {
+      const LevelGeom& L = g.lv[s_level[k]];
+      const uint8_t* c = pyr + (size_t)img * g.pyr_stride + L.off + (size_t)s_y[k] * L.pitch + s_x[k];
+      int m10 = 0, m01 = 0;
+      if (lane < 31) {
+#pragma unroll
+        for (int v = -15; v <= 15; ++v) {
+          const int av = v < 0 ? -v : v;
+          if (au <= kUmax_dev[av]) {
+            const int val = c[v * L.pitch + u];
+            m10 += u * val;
+            m01 += v * val;
+          }
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+      }
+      if (lane == 0) {
+        const float ang = fast_atan2_deg((float)m01, (float)m10);
+        s_angle[k] = ang;
+        kp_angle[(size_t)img * g.kp_stride + i0 + k] = ang;
+      }
+    }
+  }
+  __syncthreads();
+  // (2) steering coefficients
+  if (tid < nk) brief_steer(s_angle[tid], &s_a[tid], &s_b[tid]);
+  __syncthreads();
+  // (3) descriptor
+  for (int k = warp; k < nk; k += 4) {
+    const LevelGeom& L = g.lv[s_level[k]];
+    const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];
+    const float a = s_a[k], b = s_b[k];
+    uint32_t byte = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) byte |= brief_test(c, L.pitch, a, b, pat[j]) << j;
+    desc[((size_t)img * g.kp_stride + i0 + k) * 32 + lane] = (uint8_t)byte;
+  }
 }
 
 void launch_describe(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
-  dim3 grid((g.kp_stride + 127) / 128, n_img);
+  dim3 grid((g.kp_stride + kDescKp - 1) / kDescKp, n_img);
   k_describe<<<grid, 128, 0, s>>>(g, b.pyr, b.blur, b.lvl_key, b.lvl_resp, b.lvl_cnt, b.kp_x, b.kp_y, b.kp_size,
                                   b.kp_angle, b.kp_resp, b.kp_oct, b.desc, b.kp_n);
   ++*launches;

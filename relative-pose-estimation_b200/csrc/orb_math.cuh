@@ -239,23 +239,45 @@ static __device__ __constant__ int8_t kBriefPattern_dev[1024] = {
 };
 #endif
 
+// steering coefficients of a keypoint: a = (float)cos(theta), b = (float)sin(theta) with theta the f32
+// angle in radians and cos / sin evaluated in double, as computeOrbDescriptors does
+RPE_HD void brief_steer(float angle_deg, float* a, float* b) {
+  const float theta = f32_mul(angle_deg, 0.017453292519943295f);  // (float)(CV_PI/180)
+  *a = (float)cos((double)theta);
+  *b = (float)sin((double)theta);
+}
+
+// one test; t = (xa, ya, xb, yb) as four int8 packed little-endian; c = blurred level at the keypoint centre
+RPE_HD uint32_t brief_test(const uint8_t* c, int pitch, float a, float b, uint32_t t) {
+  const float xa = (float)(int8_t)(t & 0xff), ya = (float)(int8_t)((t >> 8) & 0xff);
+  const float xb = (float)(int8_t)((t >> 16) & 0xff), yb = (float)(int8_t)(t >> 24);
+  const int ixa = f32_rint(f32_sub(f32_mul(xa, a), f32_mul(ya, b)));
+  const int iya = f32_rint(f32_add(f32_mul(xa, b), f32_mul(ya, a)));
+  const int ixb = f32_rint(f32_sub(f32_mul(xb, a), f32_mul(yb, b)));
+  const int iyb = f32_rint(f32_add(f32_mul(xb, b), f32_mul(yb, a)));
+  const int va = c[iya * pitch + ixa], vb = c[iyb * pitch + ixb];
+  return (uint32_t)(va < vb);
+}
+
+// one descriptor byte = 8 tests; p = 8 x (xa, ya, xb, yb)
+RPE_HD uint32_t brief_byte(const uint8_t* c, int pitch, float a, float b, const int8_t* p) {
+  uint32_t bits = 0;
+  for (int j = 0; j < 8; ++j, p += 4) {
+    const uint32_t t = (uint32_t)(uint8_t)p[0] | ((uint32_t)(uint8_t)p[1] << 8) | ((uint32_t)(uint8_t)p[2] << 16) |
+                       ((uint32_t)(uint8_t)p[3] << 24);
+    bits |= brief_test(c, pitch, a, b, t) << j;
+  }
+  return bits;
+}
+
 // c = blurred level at the keypoint centre; angle in degrees; out = 8 x u32 (32 bytes, LSB first)
 RPE_HD void brief256(const uint8_t* c, int pitch, float angle_deg, uint32_t out[8]) {
-  const float theta = f32_mul(angle_deg, 0.017453292519943295f);  // (float)(CV_PI/180)
-  const float a = (float)cos((double)theta), b = (float)sin((double)theta);
+  float a, b;
+  brief_steer(angle_deg, &a, &b);
   const int8_t* P = RPE_TBL(kBriefPattern);
   for (int w = 0; w < 8; ++w) {
     uint32_t bits = 0;
-    for (int j = 0; j < 32; ++j) {
-      const int8_t* p = P + 4 * (32 * w + j);
-      const float xa = (float)p[0], ya = (float)p[1], xb = (float)p[2], yb = (float)p[3];
-      const int ixa = f32_rint(f32_sub(f32_mul(xa, a), f32_mul(ya, b)));
-      const int iya = f32_rint(f32_add(f32_mul(xa, b), f32_mul(ya, a)));
-      const int ixb = f32_rint(f32_sub(f32_mul(xb, a), f32_mul(yb, b)));
-      const int iyb = f32_rint(f32_add(f32_mul(xb, b), f32_mul(yb, a)));
-      const int va = c[iya * pitch + ixa], vb = c[iyb * pitch + ixb];
-      bits |= (uint32_t)(va < vb) << j;
-    }
+    for (int j = 0; j < 4; ++j) bits |= brief_byte(c, pitch, a, b, P + 32 * (4 * w + j)) << (8 * j);
     out[w] = bits;
   }
 }

@@ -40,6 +40,7 @@ struct OrbGeom {
   int cand_stride;
   int kp_stride;
   int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)
+  int resize_strip_ok;     // every aligned group of 4 output columns taps <= 8 consecutive source bytes
   size_t pyr_stride;
   LevelGeom lv[RPE_MAX_LEVELS];
 };
