@@ -127,8 +127,8 @@ __device__ __forceinline__ int find_level(const OrbGeom& g, int tile) {
 //  (1) TMA: one bulk copy per image row of the tile (+halo) into shared memory (UBLKCP);
 //  (2) branch-free packed pre-test, four pixels per thread (fast_compass4); the ~3 % of pixels
 //      that pass are compacted into a shared-memory queue;
-//  (3a) one thread per queued pixel: exact FAST-9 corner test -> corner queue;
-//  (3b) one thread per corner: score (min/max network) -> score tile in shared memory;
+//  (3) one thread per queued pixel: FAST-9 corner test + score in one packed min/max network
+//      (fast9_score) -> score tile in shared memory + corner queue;
 //  (4) one thread per corner: strict 3x3 NMS on the score tile, 31-px border filter,
 //      append (score<<24 | y<<12 | x) to the level's candidate list + score histogram.
 constexpr int kFastIP = 160;                 // staged bytes per image row (16-B aligned start)
@@ -165,29 +165,41 @@ __device__ __forceinline__ void fast_issue(const OrbGeom& g, const FastTile& T, 
     bulk_copy_g2s(buf + tid * kFastIP, T.src + (size_t)(T.y0 - 4 + tid) * L.pitch + T.astart, (uint32_t)row_bytes, bar);
 }
 
+constexpr int kFastTilesPerCta = 4;   // consecutive tiles of one image per CTA, TMA double-buffered
+
 __global__ void __launch_bounds__(256, 6)
 k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
        int n_img, uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
-  __shared__ __align__(128) uint8_t simg[kFastIH * kFastIP];
+  __shared__ __align__(128) uint8_t simg2[2][kFastIH * kFastIP];
   __shared__ __align__(16) uint8_t ssc[kFastSH * kFastSP];
   __shared__ uint16_t s_cand[kFastSH * kFastSP];
   __shared__ uint16_t s_corner[kFastSH * kFastSP];
-  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ __align__(8) uint64_t s_bar[2];
   __shared__ uint32_t s_ncand, s_ncorner;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int thr = g.fast_threshold;
   const uint32_t t4 = (uint32_t)min(thr, 127) * 0x01010101u;
-  const FastTile T = fast_tile(g, pyr, ftab, blockIdx.x, blockIdx.y);
+  const int tile0 = blockIdx.x * kFastTilesPerCta;
+  const int ntile = min(kFastTilesPerCta, g.total_ftiles - tile0);
   if (tid == 0) {
-    mbar_init(&s_bar, 1);
-    s_ncand = 0;
-    s_ncorner = 0;
+    mbar_init(&s_bar[0], 1);
+    mbar_init(&s_bar[1], 1);
   }
-  reinterpret_cast<uint4*>(ssc)[tid] = make_uint4(0, 0, 0, 0);
   __syncthreads();
-  fast_issue(g, T, simg, &s_bar, tid);
-  mbar_wait(&s_bar, 0);
-  {
+  // the rows of tile j+1 are requested (TMA) before tile j is processed
+  fast_issue(g, fast_tile(g, pyr, ftab, tile0, blockIdx.y), simg2[0], &s_bar[0], tid);
+  for (int j = 0; j < ntile; ++j) {
+    const FastTile T = fast_tile(g, pyr, ftab, tile0 + j, blockIdx.y);
+    const uint8_t* simg = simg2[j & 1];
+    if (j + 1 < ntile)
+      fast_issue(g, fast_tile(g, pyr, ftab, tile0 + j + 1, blockIdx.y), simg2[(j + 1) & 1], &s_bar[(j + 1) & 1], tid);
+    if (tid == 0) {
+      s_ncand = 0;
+      s_ncorner = 0;
+    }
+    reinterpret_cast<uint4*>(ssc)[tid] = make_uint4(0, 0, 0, 0);
+    __syncthreads();
+    mbar_wait(&s_bar[j & 1], (uint32_t)(j >> 1) & 1u);
     const LevelGeom& L = g.lv[T.level];
     const int x0 = T.x0, y0 = T.y0;
     // (2) packed pre-test.  Scores are only ever needed for x in [30, w-30), y in [30, h-30).
@@ -209,29 +221,26 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
       uint32_t pos = atomicAdd(&s_ncand, (uint32_t)__popc(cand));
       const uint32_t e0 = (uint32_t)((sr << 7) | (4 * lane));
       while (cand) {
-        const int j = (__ffs(cand) - 1) >> 3;
-        s_cand[pos++] = (uint16_t)(e0 + j);
+        const int jj = (__ffs(cand) - 1) >> 3;
+        s_cand[pos++] = (uint16_t)(e0 + jj);
         cand &= cand - 1;
       }
     }
     __syncthreads();
 
-    // (3a) exact corner test of the queued pixels
+    // (3) corner test + score of the queued pixels in one pass (fast9_score: both polarities packed)
     const int ncand = (int)s_ncand;
     for (int i = tid; i < ncand; i += 256) {
       const int e = s_cand[i];
       const int sr = e >> 7, c = e & 127;
-      if (fast9_is_corner(&simg[(sr + 3) * kFastIP + ib + c], kFastIP, thr)) s_corner[atomicAdd(&s_ncorner, 1u)] = (uint16_t)e;
+      const int sc = fast9_score(&simg[(sr + 3) * kFastIP + ib + c], kFastIP, thr);
+      if (sc > 0) {
+        ssc[e] = (uint8_t)sc;
+        s_corner[atomicAdd(&s_ncorner, 1u)] = (uint16_t)e;
+      }
     }
     __syncthreads();
-    // (3b) corner scores
     const int ncorner = (int)s_ncorner;
-    for (int i = tid; i < ncorner; i += 256) {
-      const int e = s_corner[i];
-      const int sr = e >> 7, c = e & 127;
-      ssc[e] = (uint8_t)fast9_corner_score(&simg[(sr + 3) * kFastIP + ib + c], kFastIP);
-    }
-    __syncthreads();
 
     // (4) NMS + border filter + append
     uint32_t* cnt = cand_cnt + T.img * g.nlevels + T.level;
@@ -252,12 +261,13 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
       if (pos < (uint32_t)L.cand_cap) out[pos] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
       atomicAdd(&hst[s], 1u);
     }
+    __syncthreads();   // every reader of this tile's buffers is done before they are reused
   }
 }
 
 void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   if (g.total_ftiles == 0) return;
-  dim3 grid(g.total_ftiles, n_img);
+  dim3 grid((g.total_ftiles + kFastTilesPerCta - 1) / kFastTilesPerCta, n_img);
   k_fast<<<grid, 256, 0, s>>>(g, b.pyr, b.ftab, n_img, b.cand_key, b.cand_cnt, b.hist);
   ++*launches;
 }
@@ -402,18 +412,41 @@ void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_
 }
 
 // ------------------------------------------------------------------ K6: 7x7 sigma-2 blur (f32 FMA separable)
-// Register sliding window, no shared memory: one thread = 4 adjacent columns (one output
-// word) x a strip of kBlurRows rows; one warp = 128 columns.  Per input row the thread loads
-// three words (columns x-4 .. x+7, L1-shared with its neighbours), converts the ten bytes it
-// needs to f32 with the 2^23 mantissa trick (PRMT + FADD: no I2F), runs the row pass
-// (blur_row7: one FMUL + six FMA, left to right) for its four columns and keeps the last
-// seven row results in registers; the column pass (blur_col7_sum) and the round-to-nearest-
-// even store come out of that window.  Work items (level, strip, segment) come from btab.
+// Register sliding window, no shared memory.  One thread = 4 adjacent columns (one output word)
+// x TWO row strips of kBlurRows rows that are walked in lockstep, so that every f32 operation
+// is a packed f32x2 instruction (FFMA2 / FADD2 / FMUL2 of sm_100: lane 0 = strip A, lane 1 =
+// strip B; each lane is an IEEE round-to-nearest f32 operation, so the results are those of the
+// scalar blur_row7 / blur_col7_sum in orb_math.cuh bit for bit).  One warp = 128 columns.
+// Per input row and strip the thread loads three words (columns x-4 .. x+7, L1-shared with its
+// neighbours), converts the ten bytes it needs with the 2^23 mantissa trick (PRMT + FADD2: no
+// I2F), runs the row pass for its four columns and keeps the last seven row results in
+// registers; the column pass and the round-to-nearest-even store come out of that window.
+// Work items (level, strip pair, segment) come from btab.
 constexpr int kBlurRows = 64;
 
-__device__ __forceinline__ float u8_to_f32(uint32_t w, uint32_t sel) {
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float2 u8x2_to_f32(uint32_t wa, uint32_t wb, uint32_t sel) {
   // bytes {b, 0, 0, 0x4b} = 2^23 + b exactly; subtracting 2^23 is exact
-  return __fsub_rn(__uint_as_float(__byte_perm(w, 0x4b000000u, sel)), 8388608.0f);
+  return __fadd2_rn(f2(__uint_as_float(__byte_perm(wa, 0x4b000000u, sel)),
+                       __uint_as_float(__byte_perm(wb, 0x4b000000u, sel))), f2(-8388608.0f, -8388608.0f));
+}
+__device__ __forceinline__ float2 blur_row7_x2(const float2* v) {
+  float2 s = __fmul2_rn(f2(RPE_BLUR_K0, RPE_BLUR_K0), v[0]);
+  s = __ffma2_rn(f2(RPE_BLUR_K1, RPE_BLUR_K1), v[1], s);
+  s = __ffma2_rn(f2(RPE_BLUR_K2, RPE_BLUR_K2), v[2], s);
+  s = __ffma2_rn(f2(RPE_BLUR_K3, RPE_BLUR_K3), v[3], s);
+  s = __ffma2_rn(f2(RPE_BLUR_K2, RPE_BLUR_K2), v[4], s);
+  s = __ffma2_rn(f2(RPE_BLUR_K1, RPE_BLUR_K1), v[5], s);
+  s = __ffma2_rn(f2(RPE_BLUR_K0, RPE_BLUR_K0), v[6], s);
+  return s;
+}
+__device__ __forceinline__ float2 blur_col7_x2(float2 r0, float2 r1, float2 r2, float2 r3, float2 r4, float2 r5,
+                                               float2 r6) {
+  float2 s = __fmul2_rn(f2(RPE_BLUR_K3, RPE_BLUR_K3), r3);
+  s = __ffma2_rn(f2(RPE_BLUR_K2, RPE_BLUR_K2), __fadd2_rn(r2, r4), s);
+  s = __ffma2_rn(f2(RPE_BLUR_K1, RPE_BLUR_K1), __fadd2_rn(r1, r5), s);
+  s = __ffma2_rn(f2(RPE_BLUR_K0, RPE_BLUR_K0), __fadd2_rn(r0, r6), s);
+  return s;
 }
 
 __global__ void __launch_bounds__(128)
@@ -422,58 +455,93 @@ k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8
   const int img = blockIdx.y;
   const int item = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (item >= g.total_bitems) return;
-  const uint32_t e = __ldg(btab + item);                   // level<<24 | strip<<12 | segment
+  const uint32_t e = __ldg(btab + item);                   // level<<24 | strip pair<<12 | segment
   const LevelGeom& L = g.lv[e >> 24];
   const int x = ((int)(e & 0xfff) * 32 + (threadIdx.x & 31)) * 4;
-  const int y0 = (int)((e >> 12) & 0xfff) * kBlurRows;
+  const int yA = (int)((e >> 12) & 0xfff) * (2 * kBlurRows), yB = yA + kBlurRows;
   if (x >= L.w) return;
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
-  uint8_t* dst = blur + (size_t)img * g.pyr_stride + L.off;
   const int w = L.w, h = L.h, pitch = L.pitch;
-  const bool edge = x < 4 || x + 7 > w;                    // some of x-3 .. x+6 fall outside the image
-  int xo[10];
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off + x;
+  uint8_t* dst = blur + (size_t)img * g.pyr_stride + L.off + x;
+  // Columns x-3 .. x+6 that fall outside the image are mirrored (reflect-101).  The mirrored pixel
+  // always lies inside the three words a0 a1 a2 = pixels x-4 .. x+7 this thread loads anyway, so an
+  // edge thread only needs per-value (word, byte) selectors: wsel 0..2, bsel = PRMT selector.
+  const bool edge = x < 4 || x + 7 > w;
+  const int left = x >= 4 ? -4 : 0;                         // x == 0: a0 is never selected, keep the load in bounds
+  uint32_t wsel = 0, bsel[10];
 #pragma unroll
-  for (int k = 0; k < 10; ++k) xo[k] = edge ? reflect101(x - 3 + k, w) : 0;
-  const int n_out = min(kBlurRows, h - y0);
-  float win[7][4];
+  for (int k = 0; k < 10; ++k) {
+    const int idx = edge ? reflect101(x - 3 + k, w) - (x - 4) : k + 1;   // 0 .. 11
+    wsel |= (uint32_t)(idx >> 2) << (2 * k);
+    bsel[k] = 0x7440u | (uint32_t)(idx & 3);
+  }
+  const int nA = min(kBlurRows, h - yA), nB = min(kBlurRows, h - yB);   // nB may be <= 0: strip B idle
+  float2 win[7][4];
 #pragma unroll
   for (int i = 0; i < 7; ++i)
 #pragma unroll
-    for (int c = 0; c < 4; ++c) win[i][c] = 0.f;
+    for (int c = 0; c < 4; ++c) win[i][c] = f2(0.f, 0.f);
 
-  for (int base = 0; base < n_out + 6; base += 7) {
+  // the six words of input row r + 2 are requested while row r is processed (the loop is otherwise
+  // bound by load latency: ncu stall_long_sb 53 % without the prefetch)
+  uint32_t pf[2][6];
+  auto fetch = [&](int r, uint32_t* o) {
+    const int rr = min(r, nA + 5);                          // stay on rows this strip pair really needs
+    const uint8_t* rowA = src + (uint32_t)(reflect101(yA - 3 + rr, h) * pitch);
+    const uint8_t* rowB = src + (uint32_t)(min(reflect101(yB - 3 + rr, h), h - 1) * pitch);   // in bounds even when idle
+    o[0] = __ldg(reinterpret_cast<const uint32_t*>(rowA + left));
+    o[1] = __ldg(reinterpret_cast<const uint32_t*>(rowA));
+    o[2] = __ldg(reinterpret_cast<const uint32_t*>(rowA + 4));
+    o[3] = __ldg(reinterpret_cast<const uint32_t*>(rowB + left));
+    o[4] = __ldg(reinterpret_cast<const uint32_t*>(rowB));
+    o[5] = __ldg(reinterpret_cast<const uint32_t*>(rowB + 4));
+  };
+  fetch(0, pf[0]);
+  fetch(1, pf[1]);
+  for (int base = 0; base < nA + 6; base += 7) {
 #pragma unroll
     for (int i = 0; i < 7; ++i) {
       const int r = base + i;
-      if (r < n_out + 6) {
-        const uint8_t* row = src + (size_t)reflect101(y0 - 3 + r, h) * pitch;
-        float v[10];
+      if (r < nA + 6) {
+        float2 v[10];
+        const uint32_t a0 = pf[0][0], a1 = pf[0][1], a2 = pf[0][2], b0 = pf[0][3], b1 = pf[0][4], b2 = pf[0][5];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) pf[0][k] = pf[1][k];
+        fetch(r + 2, pf[1]);
         if (!edge) {
-          const uint32_t a = __ldg(reinterpret_cast<const uint32_t*>(row + x - 4));
-          const uint32_t b = __ldg(reinterpret_cast<const uint32_t*>(row + x));
-          const uint32_t c = __ldg(reinterpret_cast<const uint32_t*>(row + x + 4));
-          v[0] = u8_to_f32(a, 0x7441); v[1] = u8_to_f32(a, 0x7442); v[2] = u8_to_f32(a, 0x7443);
-          v[3] = u8_to_f32(b, 0x7440); v[4] = u8_to_f32(b, 0x7441); v[5] = u8_to_f32(b, 0x7442);
-          v[6] = u8_to_f32(b, 0x7443);
-          v[7] = u8_to_f32(c, 0x7440); v[8] = u8_to_f32(c, 0x7441); v[9] = u8_to_f32(c, 0x7442);
+          v[0] = u8x2_to_f32(a0, b0, 0x7441); v[1] = u8x2_to_f32(a0, b0, 0x7442); v[2] = u8x2_to_f32(a0, b0, 0x7443);
+          v[3] = u8x2_to_f32(a1, b1, 0x7440); v[4] = u8x2_to_f32(a1, b1, 0x7441); v[5] = u8x2_to_f32(a1, b1, 0x7442);
+          v[6] = u8x2_to_f32(a1, b1, 0x7443);
+          v[7] = u8x2_to_f32(a2, b2, 0x7440); v[8] = u8x2_to_f32(a2, b2, 0x7441); v[9] = u8x2_to_f32(a2, b2, 0x7442);
         } else {
 #pragma unroll
-          for (int k = 0; k < 10; ++k) v[k] = (float)row[xo[k]];
+          for (int k = 0; k < 10; ++k) {
+            const uint32_t ws = (wsel >> (2 * k)) & 3u;
+            v[k] = u8x2_to_f32(ws == 0 ? a0 : (ws == 1 ? a1 : a2), ws == 0 ? b0 : (ws == 1 ? b1 : b2), bsel[k]);
+          }
         }
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
-          win[i][c] = blur_row7(v[c], v[c + 1], v[c + 2], v[c + 3], v[c + 4], v[c + 5], v[c + 6]);
+        for (int c = 0; c < 4; ++c) win[i][c] = blur_row7_x2(v + c);
         if (r >= 6) {
-          uint32_t o[4];
+          uint32_t oa[4], ob[4];
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
-            const float sum = blur_col7_sum(win[(i + 1) % 7][c], win[(i + 2) % 7][c], win[(i + 3) % 7][c],
+            const float2 sum = blur_col7_x2(win[(i + 1) % 7][c], win[(i + 2) % 7][c], win[(i + 3) % 7][c],
                                             win[(i + 4) % 7][c], win[(i + 5) % 7][c], win[(i + 6) % 7][c], win[i][c]);
             // 0 <= sum <= 255: adding 1.5 * 2^23 leaves rint(sum) (ties to even) in the low byte
-            o[c] = __float_as_uint(__fadd_rn(sum, 12582912.0f));
+            const float2 o = __fadd2_rn(sum, f2(12582912.0f, 12582912.0f));
+            oa[c] = __float_as_uint(o.x);
+            ob[c] = __float_as_uint(o.y);
           }
-          const uint32_t lo = __byte_perm(o[0], o[1], 0x0040), hi = __byte_perm(o[2], o[3], 0x0040);
-          *reinterpret_cast<uint32_t*>(dst + (size_t)(y0 + r - 6) * pitch + x) = __byte_perm(lo, hi, 0x5410);
+          const uint32_t orow = (uint32_t)((r - 6) * pitch);
+          {
+            const uint32_t lo = __byte_perm(oa[0], oa[1], 0x0040), hi = __byte_perm(oa[2], oa[3], 0x0040);
+            *reinterpret_cast<uint32_t*>(dst + (uint32_t)(yA * pitch) + orow) = __byte_perm(lo, hi, 0x5410);
+          }
+          if (r - 6 < nB) {
+            const uint32_t lo = __byte_perm(ob[0], ob[1], 0x0040), hi = __byte_perm(ob[2], ob[3], 0x0040);
+            *reinterpret_cast<uint32_t*>(dst + (uint32_t)(yB * pitch) + orow) = __byte_perm(lo, hi, 0x5410);
+          }
         }
       }
     }

@@ -80,8 +80,8 @@ RPE_HD int fast9_corner_score(const uint8_t* c, int pitch) {
   return imax(a, -bmin) - 1;
 }
 
-// returns 0 for a non-corner, else the corner score
-RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
+// returns 0 for a non-corner, else the corner score (scalar reference form; tests only)
+RPE_HD int fast9_score_scalar(const uint8_t* c, int pitch, int t) {
   return fast9_is_corner(c, pitch, t) ? fast9_corner_score(c, pitch) : 0;
 }
 
@@ -89,30 +89,102 @@ RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
 // = the words left / right of C on the same row; U / D = the words at x .. x+3 three rows up /
 // down).  Returns 0x80 in byte j iff pixel j passes both opposite-pair tests on the compass
 // points of the ring, (0,+-3) and (+-3,0), for one polarity — a necessary condition for a
-// 9-arc, since an arc of 9 contains at least one point of every opposite pair.  t4 = the
-// threshold replicated in the four bytes (threshold < 128).
-RPE_HD uint32_t sat_add_u8x4(uint32_t v, uint32_t t4) {
-  const uint32_t s = (v & 0x7f7f7f7fu) + t4;               // 7-bit lanes: no carry across bytes
-  const uint32_t ovf = (s & v & 0x80808080u) >> 7;         // 1 in bytes whose sum exceeds 255
-  return (s ^ (v & 0x80808080u)) | (ovf * 0xffu);
+// 9-arc, since an arc of 9 contains at least one point of every opposite pair:
+//   bright: min(max(N,S), max(E,W)) > v + t      dark: max(min(N,S), min(E,W)) < v - t.
+// Two pixels per register as u16 lanes (VIMNMX.U16x2 is native on sm_100; byte-wise min / max /
+// compare are not): the two comparisons become one 32-bit add / subtract each whose lane bit 15
+// is the answer (lanes stay within [0x7e00, 0x80ff]: no carry or borrow crosses lanes).
+// t4 = the threshold replicated in the four bytes (threshold < 128).
+RPE_HD uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+#if defined(__CUDA_ARCH__)
+  return __byte_perm(a, b, sel);
+#else
+  const uint64_t v = ((uint64_t)b << 32) | a;
+  uint32_t r = 0;
+  for (int i = 0; i < 4; ++i) r |= (uint32_t)((v >> (8 * ((sel >> (4 * i)) & 7))) & 0xff) << (8 * i);
+  return r;
+#endif
 }
-RPE_HD uint32_t sat_sub_u8x4(uint32_t v, uint32_t t4) { return ~sat_add_u8x4(~v, t4); }
-// msb of each byte = (a > b) for unsigned bytes; a7 = a & 0x7f7f7f7f, nb7 = ~b & 0x7f7f7f7f
-RPE_HD uint32_t gt_u8x4(uint32_t a, uint32_t b, uint32_t a7, uint32_t nb7) {
-  const uint32_t s = a7 + nb7;                             // bit 7 = (low 7 bits of a) > (low 7 bits of b)
-  return (a & ~b) | (~(a ^ b) & s);
+RPE_HD uint32_t umax16x2(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+  return __vmaxu2(a, b);
+#else
+  const uint32_t lo = (a & 0xffff) > (b & 0xffff) ? (a & 0xffff) : (b & 0xffff);
+  const uint32_t hi = (a >> 16) > (b >> 16) ? (a >> 16) : (b >> 16);
+  return lo | (hi << 16);
+#endif
+}
+RPE_HD uint32_t umin16x2(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+  return __vminu2(a, b);
+#else
+  const uint32_t lo = (a & 0xffff) < (b & 0xffff) ? (a & 0xffff) : (b & 0xffff);
+  const uint32_t hi = (a >> 16) < (b >> 16) ? (a >> 16) : (b >> 16);
+  return lo | (hi << 16);
+#endif
+}
+RPE_HD uint32_t umin3_16x2(uint32_t a, uint32_t b, uint32_t c) {
+#if defined(__CUDA_ARCH__)
+  return __vimin3_u16x2(a, b, c);
+#else
+  return umin16x2(umin16x2(a, b), c);
+#endif
+}
+RPE_HD uint32_t umax3_16x2(uint32_t a, uint32_t b, uint32_t c) {
+#if defined(__CUDA_ARCH__)
+  return __vimax3_u16x2(a, b, c);
+#else
+  return umax16x2(umax16x2(a, b), c);
+#endif
+}
+
+// Corner test + score in one pass, both polarities at once: lane 0 of P[k] = 256 + d_k, lane 1 =
+// 256 - d_k (d_k = v - p_k; one IMAD per ring pixel: p * 0xffff + base).  With
+//   a = max over the 16 arcs of min(d over 9 contiguous k),  b = the same for -d,
+// the pixel is a corner iff max(a, b) > t and its score is max(a, b) - 1.
+// Returns 0 for a non-corner, else the score (>= t >= 1).
+RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
+  const uint32_t v = c[0];
+  const uint32_t base = (256u + v) | ((256u - v) << 16);
+  uint32_t P[16];
+#define RPE_LD(k, dx, dy) P[k] = (uint32_t)c[(dy) * pitch + (dx)] * 0xffffu + base
+  RPE_LD(0, 0, 3);  RPE_LD(1, 1, 3);   RPE_LD(2, 2, 2);    RPE_LD(3, 3, 1);
+  RPE_LD(4, 3, 0);  RPE_LD(5, 3, -1);  RPE_LD(6, 2, -2);   RPE_LD(7, 1, -3);
+  RPE_LD(8, 0, -3); RPE_LD(9, -1, -3); RPE_LD(10, -2, -2); RPE_LD(11, -3, -1);
+  RPE_LD(12, -3, 0); RPE_LD(13, -3, 1); RPE_LD(14, -2, 2); RPE_LD(15, -1, 3);
+#undef RPE_LD
+  uint32_t m2[16], m4[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) m2[k] = umin16x2(P[k], P[(k + 1) & 15]);
+#pragma unroll
+  for (int k = 0; k < 16; ++k) m4[k] = umin16x2(m2[k], m2[(k + 2) & 15]);
+  uint32_t best = 0;
+#pragma unroll
+  for (int k = 0; k < 16; k += 2) {
+    const uint32_t m9a = umin3_16x2(m4[k], m4[(k + 4) & 15], P[(k + 8) & 15]);
+    const uint32_t m9b = umin3_16x2(m4[k + 1], m4[(k + 5) & 15], P[(k + 9) & 15]);
+    best = umax3_16x2(best, m9a, m9b);
+  }
+  const int a = (int)(best & 0xffffu) - 256, b = (int)(best >> 16) - 256;
+  const int s = imax(a, b);
+  return s > t ? s - 1 : 0;
+}
+
+// bit 15 of each lane = the two-pixel pre-test; kt = 0x7fff7fff - (t | t << 16)
+RPE_HD uint32_t fast_compass2(uint32_t c, uint32_t n, uint32_t s, uint32_t e, uint32_t w, uint32_t kt) {
+  const uint32_t bright = umin16x2(umax16x2(n, s), umax16x2(e, w));
+  const uint32_t dark = umax16x2(umin16x2(n, s), umin16x2(e, w));
+  return (bright + (kt - c)) | ((kt + c) - dark);
 }
 RPE_HD uint32_t fast_compass4(uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t U, uint32_t D, uint32_t t4) {
   const uint32_t E = (C >> 24) | (Rw << 8);                // pixels x+3 .. x+6
   const uint32_t W = (Lw >> 8) | (C << 24);                // pixels x-3 .. x
-  const uint32_t Vp = sat_add_u8x4(C, t4), Vm = sat_sub_u8x4(C, t4);
-  const uint32_t nVp7 = ~Vp & 0x7f7f7f7fu, Vm7 = Vm & 0x7f7f7f7fu;
-  const uint32_t n0 = D & 0x7f7f7f7fu, n1 = E & 0x7f7f7f7fu, n2 = U & 0x7f7f7f7fu, n3 = W & 0x7f7f7f7fu;
-  const uint32_t b0 = gt_u8x4(D, Vp, n0, nVp7), b1 = gt_u8x4(E, Vp, n1, nVp7);
-  const uint32_t b2 = gt_u8x4(U, Vp, n2, nVp7), b3 = gt_u8x4(W, Vp, n3, nVp7);
-  const uint32_t d0 = gt_u8x4(Vm, D, Vm7, 0x7f7f7f7fu - n0), d1 = gt_u8x4(Vm, E, Vm7, 0x7f7f7f7fu - n1);
-  const uint32_t d2 = gt_u8x4(Vm, U, Vm7, 0x7f7f7f7fu - n2), d3 = gt_u8x4(Vm, W, Vm7, 0x7f7f7f7fu - n3);
-  return (((b0 | b2) & (b1 | b3)) | ((d0 | d2) & (d1 | d3))) & 0x80808080u;
+  const uint32_t kt = 0x7fff7fffu - (t4 & 0x00ff00ffu);
+  const uint32_t lo = fast_compass2(prmt(C, 0, 0x4140), prmt(U, 0, 0x4140), prmt(D, 0, 0x4140), prmt(E, 0, 0x4140),
+                                    prmt(W, 0, 0x4140), kt);
+  const uint32_t hi = fast_compass2(prmt(C, 0, 0x4342), prmt(U, 0, 0x4342), prmt(D, 0, 0x4342), prmt(E, 0, 0x4342),
+                                    prmt(W, 0, 0x4342), kt);
+  return prmt(lo, hi, 0x7531) & 0x80808080u;
 }
 
 // ------------------------------------------------------------------ A.5 Harris response

@@ -36,7 +36,7 @@ struct OrbGeom {
   int fast_threshold;
   int total_tiles;
   int total_ftiles;
-  int total_bitems;        // blur work items (one warp each): 128 columns x 64 rows
+  int total_bitems;        // blur work items (one warp each): 128 columns x two 64-row strips
   int cand_stride;
   int kp_stride;
   int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)

@@ -32,11 +32,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
-      "RPE_MBAR_WAIT:\n"
+      "RPE_MBAR_WAIT_%=:\n"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra RPE_MBAR_DONE;\n"
-      "bra RPE_MBAR_WAIT;\n"
-      "RPE_MBAR_DONE:\n"
+      "@p bra RPE_MBAR_DONE_%=;\n"
+      "bra RPE_MBAR_WAIT_%=;\n"
+      "RPE_MBAR_DONE_%=:\n"
       "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 

@@ -50,6 +50,13 @@ def fast_scores(img, t):
     return out
 
 
+def fast_scores_scalar(img, t):
+    img = np.ascontiguousarray(img)
+    out = np.zeros(img.shape, np.int32)
+    lib().hc_fast_scores_scalar(_p(img), img.shape[1], img.shape[0], int(t), _p(out))
+    return out
+
+
 def fast_compass(img, t):
     img = np.ascontiguousarray(img)
     out = np.zeros(img.shape, np.uint8)

@@ -33,6 +33,12 @@ void hc_fast_scores(const uint8_t* img, int w, int h, int t, int* out) {
     for (int x = 3; x < w - 3; ++x) out[y * w + x] = fast9_score(img + y * w + x, w, t);
 }
 // packed pre-test on every aligned quad of rows 3..h-4 / cols 4..w-8: out[y*w+x] = 1 if it passes
+// scalar reference form (exact 9-arc test, then min / max network) for the same pixels
+void hc_fast_scores_scalar(const uint8_t* img, int w, int h, int t, int* out) {
+  memset(out, 0, sizeof(int) * w * h);
+  for (int y = 3; y < h - 3; ++y)
+    for (int x = 3; x < w - 3; ++x) out[y * w + x] = fast9_score_scalar(img + y * w + x, w, t);
+}
 void hc_fast_compass(const uint8_t* img, int w, int h, int t, uint8_t* out) {
   memset(out, 0, (size_t)w * h);
   const uint32_t t4 = (uint32_t)t * 0x01010101u;

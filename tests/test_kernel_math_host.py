@@ -30,6 +30,13 @@ def test_fast_scores_bit_exact(img):
     noise = np.random.default_rng(0).integers(0, 256, (64, 96), dtype=np.uint8)
     for t in (1, 15, 60):
         assert np.array_equal(hc.fast_scores(noise, t), oo.fast_score_map(noise, t))
+        assert np.array_equal(hc.fast_scores_scalar(noise, t), oo.fast_score_map(noise, t))
+    # extremes of the packed form: saturated rings around dark / bright centres
+    ext = np.zeros((16, 16), np.uint8); ext[8, 8] = 255
+    ext2 = np.full((16, 16), 255, np.uint8); ext2[8, 8] = 0
+    for im in (ext, ext2):
+        for t in (1, 127, 254):
+            assert np.array_equal(hc.fast_scores(im, t), oo.fast_score_map(im, t))
 
 
 def test_fast_packed_pretest_is_the_scalar_compass_test(img):
