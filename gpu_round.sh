@@ -15,8 +15,8 @@ timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; ech
 for extra in "$@"; do
   case "$extra" in
     ncu)
-      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --streams 1 --chunk 128 > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-      timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'k_fast|k_blur|k_hamming|k_resize|k_ransac|k_describe|k_pose|k_select|k_build' --launch-skip 20 -c 20 -o gpurun_out/full -f python bench.py --steps 2 --warmup 1 --no-cpu-baseline --batch 32 --streams 1 > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?" ;;
+      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --inflight 1 > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
+      timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'k_fast|k_blur|k_hamming|k_resize|k_ransac|k_describe|k_pose|k_select|k_build' --launch-skip 20 -c 20 -o gpurun_out/full -f python bench.py --steps 2 --warmup 1 --no-cpu-baseline --batch 32 --inflight 1 > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?" ;;
     sweep)
       for cs in "1 128 1" "2 128 1" "3 128 1" "2 64 3" "2 32 4" "1 32 4" "3 64 3"; do set -- $cs
         timeout 300 python bench.py --no-cpu-baseline --inflight $1 --chunk $2 --streams $3 > gpurun_out/b_$1_$2_$3.json 2>gpurun_out/b.err || tail -3 gpurun_out/b.err; echo "inflight $1 chunk $2 streams $3"; show gpurun_out/b_$1_$2_$3.json 2>/dev/null | head -1; done ;;
