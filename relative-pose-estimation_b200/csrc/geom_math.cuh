@@ -157,8 +157,14 @@ RPE_HDN void solve_poly10(const double* c, Cplx* roots, int max_iters) {
 // All real essential matrices through five normalised correspondences (x2' E x1 = 0), each
 // with Frobenius norm 1.  x1, x2: 5 x (x, y).  Eout: up to 10 x 9 (row-major).  Returns count.
 RPE_HDN int five_point_solve(const double* x1, const double* x2, double* Eout) {
-  // --- 1. orthonormal basis of the null space of the 5x9 epipolar system
-  double Rw[5][9];
+  // --- 1. null space of the 5x9 epipolar system, in the SAME basis OpenCV gets from LAPACK.
+  // cv2 (built with LAPACK) calls dgesdd(FULL_UV) on the 5x9 matrix; for that shape dgesdd takes
+  // the "LQ first" path, so rows 5..8 of Vt are rows 5..8 of the full Householder Q of A = L Q.
+  // The essential-matrix parametrisation E = x N0 + y N1 + z N2 + N3 depends on this basis, and
+  // for near-degenerate samples (planar scenes) its conditioning does too: an arbitrary
+  // orthonormal basis moves the models by up to 1e-2, this one reproduces cv2's to ~1e-8
+  // (tests/test_kernel_math_host.py).  Householder reflectors exactly as dgelq2 / dlarfg.
+  double Rw[5][9], tau[5];
   for (int i = 0; i < 5; ++i) {
     const double a = x1[2 * i], b = x1[2 * i + 1], c = x2[2 * i], d = x2[2 * i + 1];
     Rw[i][0] = c * a; Rw[i][1] = c * b; Rw[i][2] = c;
@@ -166,46 +172,38 @@ RPE_HDN int five_point_solve(const double* x1, const double* x2, double* Eout) {
     Rw[i][6] = a;     Rw[i][7] = b;     Rw[i][8] = 1.0;
   }
   for (int i = 0; i < 5; ++i) {
-    for (int pass = 0; pass < 2; ++pass)
-      for (int j = 0; j < i; ++j) {
-        double dot = 0;
-        for (int k = 0; k < 9; ++k) dot += Rw[j][k] * Rw[i][k];
-        for (int k = 0; k < 9; ++k) Rw[i][k] -= dot * Rw[j][k];
-      }
-    double nn = 0;
-    for (int k = 0; k < 9; ++k) nn += Rw[i][k] * Rw[i][k];
-    if (!(nn > 1e-280)) return 0;
-    nn = 1.0 / sqrt(nn);
-    for (int k = 0; k < 9; ++k) Rw[i][k] *= nn;
+    const double alpha = Rw[i][i];
+    double xn = 0;
+    for (int k = i + 1; k < 9; ++k) xn += Rw[i][k] * Rw[i][k];
+    if (!(xn > 0)) { tau[i] = 0; continue; }            // H = I
+    const double nrm = sqrt(alpha * alpha + xn);
+    const double beta = alpha >= 0 ? -nrm : nrm;
+    tau[i] = (beta - alpha) / beta;
+    const double sc = 1.0 / (alpha - beta);
+    for (int k = i + 1; k < 9; ++k) Rw[i][k] *= sc;       // v (v_i = 1 implied)
+    for (int r = i + 1; r < 5; ++r) {                     // apply H_i to the remaining rows
+      double w = Rw[r][i];
+      for (int k = i + 1; k < 9; ++k) w += Rw[r][k] * Rw[i][k];
+      w *= tau[i];
+      Rw[r][i] -= w;
+      for (int k = i + 1; k < 9; ++k) Rw[r][k] -= w * Rw[i][k];
+    }
   }
   double N[4][9];
-  for (int m = 0; m < 4; ++m) {
-    int bj = 0;
-    double bres = -1;
-    for (int j = 0; j < 9; ++j) {
-      double s = 1.0;
-      for (int i = 0; i < 5; ++i) s -= Rw[i][j] * Rw[i][j];
-      for (int i = 0; i < m; ++i) s -= N[i][j] * N[i][j];
-      if (s > bres) { bres = s; bj = j; }
-    }
+  for (int m = 0; m < 4; ++m) {                           // row 5 + m of Q = e' H5 H4 H3 H2 H1
     double v[9];
-    for (int k = 0; k < 9; ++k) v[k] = (k == bj) ? 1.0 : 0.0;
-    for (int pass = 0; pass < 2; ++pass) {
-      for (int i = 0; i < 5; ++i) {
-        double dot = 0;
-        for (int k = 0; k < 9; ++k) dot += Rw[i][k] * v[k];
-        for (int k = 0; k < 9; ++k) v[k] -= dot * Rw[i][k];
-      }
-      for (int i = 0; i < m; ++i) {
-        double dot = 0;
-        for (int k = 0; k < 9; ++k) dot += N[i][k] * v[k];
-        for (int k = 0; k < 9; ++k) v[k] -= dot * N[i][k];
-      }
+    for (int k = 0; k < 9; ++k) v[k] = (k == 5 + m) ? 1.0 : 0.0;
+    for (int i = 4; i >= 0; --i) {
+      if (tau[i] == 0) continue;
+      double w = v[i];
+      for (int k = i + 1; k < 9; ++k) w += v[k] * Rw[i][k];
+      w *= tau[i];
+      v[i] -= w;
+      for (int k = i + 1; k < 9; ++k) v[k] -= w * Rw[i][k];
     }
     double nn = 0;
-    for (int k = 0; k < 9; ++k) nn += v[k] * v[k];
-    nn = 1.0 / sqrt(nn);
-    for (int k = 0; k < 9; ++k) N[m][k] = v[k] * nn;
+    for (int k = 0; k < 9; ++k) { N[m][k] = v[k]; nn += v[k] * v[k]; }
+    if (!(nn > 0.25)) return 0;                           // NaN / inf guard (rows of Q have norm 1)
   }
   // --- 2. constraint matrix A (10 x 20): det(E) = 0 and E E' E - tr(E E')/2 E = 0
   double e[9][4];

@@ -1,0 +1,103 @@
+"""GPU parity at the sizes BASELINE.json's configs name (cfg3: 1280x720 / 5000 features / knn-2 +
+ratio 0.75 / RANSAC 2000; cfg4: 3840x2160 / 20000 features / 8 levels), on the synthetic pairs
+bench.py times, through the C ABI.  ORB and matches are checked bit-exactly against live cv2 on
+the canonically ordered features; the pose against the reference's own cv2 call sequence
+(oracle/reference_path.py) on the same ordered inputs: R within 0.1 deg, t within 0.5 deg."""
+import numpy as np
+import pytest
+
+import cv2
+
+from oracle import geometry as og
+from oracle import orb as oo
+from oracle.reference_path import PathConfig, ReferencePath
+
+pytestmark = pytest.mark.gpu
+
+CFG3 = dict(W=1280, H=720, nfeatures=5000, nlevels=12, synth_cfg=3)
+CFG4 = dict(W=3840, H=2160, nfeatures=20000, nlevels=8, synth_cfg=4)
+
+
+def _engine(c, max_pairs):
+    import rpe_b200
+    return rpe_b200.Engine(rpe_b200.EngineConfig(max_width=c["W"], max_height=c["H"], max_pairs=max_pairs,
+                                                 nfeatures=c["nfeatures"], nlevels=c["nlevels"], match_mode="ratio",
+                                                 ratio=0.75, max_matches=500, ransac_max_iters=2000))
+
+
+def _cv2_canonical(img, c):
+    orb = cv2.ORB_create(nfeatures=c["nfeatures"], scaleFactor=1.1, nlevels=c["nlevels"], fastThreshold=15,
+                         scoreType=cv2.ORB_HARRIS_SCORE)
+    kps, desc = orb.detectAndCompute(img, None)
+    lv = oo.level_geometry(img.shape[1], img.shape[0], oo.OrbParams(c["nfeatures"], 1.1, c["nlevels"]))
+    return oo.canonicalize_cv2(kps, desc, lv)
+
+
+def _check_pair(eng, c, pair_idx, slot, out):
+    from rpe_b200 import _lib as L
+    from rpe_b200.synth import synth_K, synth_pair
+    a, b = synth_pair(c["synth_cfg"], pair_idx, c["W"], c["H"])[:2]
+    K = synth_K(c["W"], c["H"])
+    assert out["status"][slot] == 0, out["status"][slot]          # ok, and no capacity overflow flag
+    refs = []
+    for view, img in enumerate((a, b)):
+        ref = _cv2_canonical(img, c)
+        kp = eng.keypoints(slot, view)
+        assert len(kp["x"]) == len(ref) > 0.9 * c["nfeatures"], (len(kp["x"]), len(ref))
+        for f in ("x", "y", "size", "angle", "response", "octave"):
+            assert np.array_equal(kp[f], getattr(ref, f)), (pair_idx, view, f)
+        assert np.array_equal(kp["desc"], ref.desc), (pair_idx, view, "desc")
+        refs.append(ref)
+    # matches: cv2 knnMatch + ratio + stable sort + cut on the same ordered descriptors
+    rp = ReferencePath(K, PathConfig(nfeatures=c["nfeatures"], nlevels=c["nlevels"], match_mode="ratio", ratio=0.75,
+                                     max_matches=500, ransac_max_iters=2000), canonical=True)
+    want = rp.match(refs[0].desc, refs[1].desc)
+    got = eng.get_stage(slot, 0, L.STAGE_MATCHES, 0, np.int32).reshape(-1, 3)
+    assert np.array_equal(got, want), (pair_idx, got.shape, want.shape)
+    # pose: the reference call sequence on the same points
+    pts1 = np.stack([refs[0].x[want[:, 0]], refs[0].y[want[:, 0]]], axis=1).astype(np.float32)
+    pts2 = np.stack([refs[1].x[want[:, 1]], refs[1].y[want[:, 1]]], axis=1).astype(np.float32)
+    E, mask = rp.essential(pts1, pts2)
+    n, R, t, _ = cv2.recoverPose(E, pts1, pts2, K)
+    rot = og.rotation_angle_deg(out["R"][slot], R)
+    tdir = og.direction_angle_deg(out["t"][slot], t)
+    assert rot < 0.1 and tdir < 0.5, (pair_idx, rot, tdir)
+    rmask = eng.get_stage(slot, 0, L.STAGE_RANSAC_MASK, 0, np.uint8).astype(bool)
+    m = mask.ravel().astype(bool)
+    assert (rmask & m).sum() / max(1, (rmask | m).sum()) >= 0.95
+    assert abs(int(out["info"][slot, 1]) - n) <= 2
+
+
+def test_cfg3_720p_5000_features_ratio_batch():
+    from rpe_b200.synth import synth_K, synth_batch
+    c = CFG3
+    eng = _engine(c, 3)
+    try:
+        frames = synth_batch(c["synth_cfg"], 0, 3, c["W"], c["H"])
+        out = eng.estimate_batch_interleaved(frames, synth_K(c["W"], c["H"]))
+        for i in range(3):
+            _check_pair(eng, c, i, i, out)
+        # size-independent properties at the full size: order of the pairs in the batch is irrelevant,
+        # and a repeated call is bit-identical
+        perm = [2, 0, 1]
+        pf = np.ascontiguousarray(frames.reshape(3, 2, c["H"], c["W"])[perm].reshape(6, c["H"], c["W"]))
+        out2 = eng.estimate_batch_interleaved(pf, synth_K(c["W"], c["H"]))
+        for k in ("R", "t", "euler", "status", "info"):
+            assert np.array_equal(out2[k], out[k][perm]), k
+        out3 = eng.estimate_batch_interleaved(frames, synth_K(c["W"], c["H"]))
+        for k in ("R", "t", "euler", "status", "info"):
+            assert np.array_equal(out3[k], out[k]), k
+    finally:
+        eng.close()
+
+
+def test_cfg4_4k_20000_features_8_levels():
+    from rpe_b200.synth import synth_K, synth_batch
+    c = CFG4
+    eng = _engine(c, 1)
+    try:
+        frames = synth_batch(c["synth_cfg"], 0, 1, c["W"], c["H"])
+        out = eng.estimate_batch_interleaved(frames, synth_K(c["W"], c["H"]))
+        _check_pair(eng, c, 0, 0, out)
+    finally:
+        eng.close()

@@ -162,3 +162,38 @@ def test_hamming_carry_save_forms_are_exact():
     for mode in (0, 1, 2):
         assert np.array_equal(hc.hamming(q, t, mode), want), mode
     assert want[1, 0] == 256 and want[0, 0] == 0 and want[5, 2] == 0
+
+
+def test_five_point_matches_cv2_minimal_solver():
+    """The kernel's five-point solver (LAPACK-path null basis, Gauss-Jordan, Durand-Kerner + Newton)
+    against cv2's OWN minimal solver — cv2.findEssentialMat called with exactly five points returns
+    all its roots stacked — on a generic 3-D scene: same model sets."""
+    import cv2
+    rng = np.random.default_rng(3)
+    K = np.array([[800., 0, 320], [0, 800, 240], [0, 0, 1]])
+    n = 300
+    X = np.c_[rng.uniform(-2, 2, n), rng.uniform(-1.5, 1.5, n), rng.uniform(3, 9, n)]
+    R, _ = cv2.Rodrigues(np.array([0.02, -0.03, 0.01]))
+    t = np.array([0.3, 0.05, 0.1])
+    p1 = X @ K.T
+    p1 = p1[:, :2] / p1[:, 2:]
+    X2 = X @ R.T + t
+    p2 = X2 @ K.T
+    p2 = p2[:, :2] / p2[:, 2:]
+    p1 = (p1 + rng.normal(0, 0.3, p1.shape)).astype(np.float32)
+    p2 = (p2 + rng.normal(0, 0.3, p2.shape)).astype(np.float32)
+    x1, x2 = og.normalize_points(p1, K), og.normalize_points(p2, K)
+    bad = 0
+    for _ in range(120):
+        s = rng.choice(n, 5, replace=False)
+        Es, _ = cv2.findEssentialMat(p1[s].astype(np.float64), p2[s].astype(np.float64), K, method=cv2.RANSAC,
+                                     prob=0.999, threshold=1.0)
+        want = [] if Es is None else [Es[3 * i:3 * i + 3] for i in range(Es.shape[0] // 3)]
+        got = [e.reshape(3, 3) for e in hc.five_point(x1[s], x2[s])]
+        ok = len(want) == len(got) and all(
+            min(min(np.abs(a - b).max(), np.abs(a + b).max()) for b in want) < 1e-5 for a in got)
+        bad += not ok
+        for e in got:                              # every model really is an essential matrix through the sample
+            assert np.abs(2 * e @ e.T @ e - np.trace(e @ e.T) * e).max() < 1e-6
+            assert max(abs(np.r_[x2[i], 1] @ e @ np.r_[x1[i], 1]) for i in s) < 1e-12
+    assert bad <= 3, bad
