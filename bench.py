@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--inflight", type=int, default=2, help="engine handles used alternately (batches in flight)")
     ap.add_argument("--chunk", type=int, default=32, help="pairs per pipeline chunk (rpe_set_pipeline)")
     ap.add_argument("--streams", type=int, default=1, help="pipeline streams per handle (rpe_set_pipeline); 1 = no chunking")
+    ap.add_argument("--no-stream", action="store_true", help="skip the extra consecutive-frame (config 5) pass")
     return ap.parse_args()
 
 
@@ -286,6 +287,30 @@ def run_b200(args):
     ms_prof, stage_ms = profiled()
     clocks = sampler.stop() if rank == 0 else None
 
+    # extra line item (not the headline): BASELINE config 5, a video stream of consecutive frames through the
+    # sequence ABI (rpe_submit_sequence*: ORB once per frame).  One step = B + 1 frames -> B pairs; a caller
+    # chains steps by starting at the previous step's last frame, so the steady-state rate is B pairs / step.
+    stream = None
+    if not args.no_stream:
+        from rpe_b200.synth import synth_stream
+        F = B + 1
+        shost = torch.from_numpy(synth_stream(5, rank * 100000, F, W, H)).pin_memory()
+        sdev = shost.cuda(non_blocking=False)
+        shost_np = shost.numpy()
+        sub_dev = lambda e: e.submit_sequence_device(sdev.data_ptr(), H * W, F, H, W, W, K)
+        sub_host = lambda e: e.submit_sequence(shost_np, K)
+        _, sout = run_steps(max(2, len(engines)), sub_dev)
+        ms_sdev, _ = timed(sub_dev)
+        run_steps(max(2, len(engines)), sub_host)
+        ms_se2e, _ = timed(sub_host)
+        npairs = world * args.steps * (F - 1)
+        stream = {"workload": "cfg5: synthetic 1280x720 video stream, consecutive frame pairs, cfg3 parameters, "
+                              "frame-level feature cache (ORB once per frame)",
+                  "value": npairs / (ms_sdev * 1e-3), "e2e": npairs / (ms_se2e * 1e-3), "unit": "pairs/s",
+                  "frames_per_gpu_per_step": F, "pairs_per_gpu_per_step": F - 1,
+                  "ms_per_step": ms_sdev / args.steps, "e2e_ms_per_step": ms_se2e / args.steps,
+                  "ok_fraction": float((sout["status"] & 0xFF == 0).mean())}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -359,7 +384,7 @@ def run_b200(args):
            "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": int(2 * B * H * W + 72),
                    "d2h_bytes_per_step": int(B * (15 * 8 + 3 * 4)), "ms_per_step": ms_e2e / args.steps},
            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-           "stages": stages}
+           "stages": stages, "stream": stream}
     print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -8,6 +8,7 @@ import json,sys
 d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
 print("value", round(d["value"],1), "e2e", round(d["e2e"]["value"],1), "ms/step", round(d["ms_per_step"],3), "serial", round(d["roofline"]["serial_ms_per_step"],3), "cpu", (d["cpu_baseline"] or {}).get("value"))
 print({k:round(v["ms_per_step"],3) for k,v in d["stages"].items()})
+print("stream", d.get("stream"))
 print("roofline", d["roofline"]["kernel"], round(d["roofline"]["frac"],3), "xu", round(d["roofline"]["xu_pipe"]["frac"],3), d["clocks"])
 PY
 }

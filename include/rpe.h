@@ -121,6 +121,25 @@ int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img
                               int32_t B, int32_t H, int32_t W, size_t pitch, const double K[9],
                               double* R, double* t, double* euler, int32_t* status, int32_t* info);
 
+/* Consecutive-frame form of the batch call (the reference's sequence driver,
+ * src/core/batch_processor.py:71-92, pairs frame k with frame k+1 and runs ORB on BOTH frames of every
+ * pair, src/core/pose_estimator.py:505-506): F frames -> F-1 pairs, pair p = (frames[p], frames[p+1]),
+ * ORB once per frame (frame-level feature cache).  Outputs hold F-1 entries and are bit-identical to
+ * rpe_estimate_batch on the same F-1 pairs.  F <= max_pairs + 1.  To chain calls over a longer
+ * stream, start the next call at the previous call's last frame.  submit/wait as above. */
+int rpe_estimate_sequence(rpe_handle* h, const uint8_t* const* frames, int32_t F, int32_t H, int32_t W,
+                          size_t pitch, const double K[9], double* R, double* t, double* euler,
+                          int32_t* status, int32_t* info);
+int rpe_submit_sequence(rpe_handle* h, const uint8_t* const* frames, int32_t F, int32_t H, int32_t W,
+                        size_t pitch, const double K[9], double* R, double* t, double* euler,
+                        int32_t* status, int32_t* info);
+int rpe_estimate_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t img_stride, int32_t F,
+                                 int32_t H, int32_t W, size_t pitch, const double K[9], double* R,
+                                 double* t, double* euler, int32_t* status, int32_t* info);
+int rpe_submit_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t img_stride, int32_t F,
+                               int32_t H, int32_t W, size_t pitch, const double K[9], double* R,
+                               double* t, double* euler, int32_t* status, int32_t* info);
+
 /* ---- stage entry points (parity harness; same kernels as the batch path) ------------- */
 
 /* replaces ORB.detectAndCompute(image, None) (reference: src/core/pose_estimator.py:98-109).
@@ -154,9 +173,10 @@ int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const 
                      int32_t* count, uint8_t* mask);
 
 /* intermediate results of the LAST batch call, for stage-wise parity:
- * copies up to *n bytes to `out` and stores the byte count in *n. */
+ * copies up to *n bytes to `out` and stores the byte count in *n.  `view` selects frame pair + view of a
+ * sequence call (image slot pair + view) or view 1 / 2 of a pair-batch call (slot 2*pair + view). */
 enum {
-  RPE_STAGE_PYRAMID_LEVEL = 0, /* arg = level; image slot = 2*pair + view; tight w x h u8 */
+  RPE_STAGE_PYRAMID_LEVEL = 0, /* arg = level; tight w x h u8 */
   RPE_STAGE_BLURRED_LEVEL = 1,
   RPE_STAGE_KP_X = 2,          /* float[n]  */
   RPE_STAGE_KP_Y = 3,

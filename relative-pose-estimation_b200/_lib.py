@@ -53,6 +53,10 @@ _SIGNATURES = [
     ("rpe_submit_batch_device", C.c_int, [_P, _P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     ("rpe_wait_batch", C.c_int, [_P]),
     ("rpe_estimate_batch_device", C.c_int, [_P, _P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
+    ("rpe_estimate_sequence", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
+    ("rpe_submit_sequence", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
+    ("rpe_estimate_sequence_device", C.c_int, [_P, _P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
+    ("rpe_submit_sequence_device", C.c_int, [_P, _P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     ("rpe_orb_detect", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     ("rpe_match", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32, _P, _P]),
     ("rpe_find_essential", C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P, _P]),

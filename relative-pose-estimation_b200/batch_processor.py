@@ -2,8 +2,8 @@
 
 Same constructor, same ``process_sequence`` / ``process_at_interval`` / ``get_image_path``
 and the same result dict ``{frames, roll, pitch, yaw, R, t}``; the per-pair Python loop
-(:71-108) becomes ONE ``estimate_batch`` call per chunk of pairs, and every frame is decoded
-once instead of twice (:79).  World-frame composition ``R_prev @ R_rel`` and the Euler
+(:71-108) becomes ONE ``estimate_sequence`` call per chunk of pairs: every frame is decoded once
+instead of twice (:79) and goes through ORB once instead of twice (pose_estimator.py:505-506).  World-frame composition ``R_prev @ R_rel`` and the Euler
 conversion (:88-101) stay on the host (9 doubles per pair).  A pair whose status is not OK
 raises the reference's RuntimeError, so a failing pair aborts the sequence as documented at
 :55-56.  PNG decode stays on the CPU (out of the hot path).
@@ -47,7 +47,7 @@ class BatchProcessor:
         for c0 in range(0, n_pairs, self.chunk_pairs):
             c1 = min(c0 + self.chunk_pairs, n_pairs)
             frames = [load_image(self.get_image_path(f)) for f in frame_indices[c0:c1 + 1]]
-            R_rel, t_rel, status = self.pose_estimator.estimate_batch(frames[:-1], frames[1:])
+            R_rel, t_rel, status = self.pose_estimator.estimate_sequence(frames)
             for k in range(c1 - c0):
                 self.pose_estimator._raise_for(status[k], self.pose_estimator.last["info"][k, 0])
                 gt = self.gt_loader.get_pose(frame_indices[c0 + k])

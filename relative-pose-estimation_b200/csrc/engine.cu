@@ -77,6 +77,7 @@ struct rpe_handle {
   std::map<std::pair<int, int>, Geometry> geoms;
   const Geometry* last_geom = nullptr;
   int last_pairs = 0;
+  int last_pstep = 2;       // image slots of pair p in the last batch: pstep*p, pstep*p + 1
   // pinned host staging for results: R(9) t(3) euler(3) doubles, status + 4 info ints, K
   double* h_out_d = nullptr;
   int32_t* h_out_i = nullptr;
@@ -460,30 +461,30 @@ static RansacParams ransac_params(const rpe_handle* h) {
 }
 
 // match -> sort/cut over pair slots [pair0, pair0 + nb) on stream s (dense, XU-pipe bound)
-static int run_match(rpe_handle* h, int pair0, int nb, cudaStream_t s, bool prof) {
+static int run_match(rpe_handle* h, int pair0, int nb, int pstep, cudaStream_t s, bool prof) {
   int* ln = h->launches;
-  const OrbBuffers ob = orb_view(h, 2 * pair0);
+  const OrbBuffers ob = orb_view(h, pstep * pair0);
   const MatchBuffers mb = match_view(h, pair0);
   mark(h, RPE_T_MATCH, prof);
-  launch_match(ob, mb, h->kp_stride, nb, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
+  launch_match(ob, mb, h->kp_stride, nb, pstep, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
   mark(h, RPE_T_MATCH_SORT, prof);
-  launch_build_matches(ob, mb, h->kp_stride, h->mcap, h->sort_cap_match, nb, h->cfg.match_mode, h->cfg.ratio,
+  launch_build_matches(ob, mb, h->kp_stride, h->mcap, h->sort_cap_match, nb, pstep, h->cfg.match_mode, h->cfg.ratio,
                        h->cfg.max_matches, s, &ln[RPE_T_MATCH_SORT]);
   RPE_CK(cudaGetLastError());
   return RPE_OK;
 }
 
 // RANSAC -> pose over pair slots [pair0, pair0 + nb) on stream s (one CTA per pair: latency bound)
-static int run_geometry(rpe_handle* h, int pair0, int nb, cudaStream_t s, bool prof) {
+static int run_geometry(rpe_handle* h, int pair0, int nb, int pstep, cudaStream_t s, bool prof) {
   int* ln = h->launches;
-  const OrbBuffers ob = orb_view(h, 2 * pair0);
+  const OrbBuffers ob = orb_view(h, pstep * pair0);
   const MatchBuffers mb = match_view(h, pair0);
   const GeomBuffers gb = geom_view(h, pair0);
   mark(h, RPE_T_RANSAC, prof);
   launch_normalize(mb, gb, h->mcap, nb, h->dK, s, &ln[RPE_T_RANSAC]);
   launch_ransac(mb, gb, h->mcap, nb, h->dK, ransac_params(h), s, &ln[RPE_T_RANSAC]);
   mark(h, RPE_T_POSE, prof);
-  launch_pose(mb, gb, h->mcap, nb, ransac_params(h), ob.img_flags, ob.kp_n, s, &ln[RPE_T_POSE]);
+  launch_pose(mb, gb, h->mcap, nb, ransac_params(h), ob.img_flags, ob.kp_n, pstep, s, &ln[RPE_T_POSE]);
   RPE_CK(cudaGetLastError());
   return RPE_OK;
 }
@@ -545,63 +546,64 @@ static void reset_profile(rpe_handle* h) {
   for (int i = 0; i < RPE_T_COUNT; ++i) { h->launches[i] = 0; h->ms[i] = 0.f; }
 }
 
-// Source of one batch: host pointer arrays (img1/img2) or one device buffer.
+// Source of one batch: host pointer arrays or one device buffer.  Pair batch: image slot 2i = img1[i],
+// 2i + 1 = img2[i], B pairs.  Sequence (frame-level feature cache): image slot i = img1[i]
+// (F frames), pair p = frames (p, p + 1), so every interior frame goes through ORB once, not twice.
 struct BatchSource {
   const uint8_t* const* img1 = nullptr;
   const uint8_t* const* img2 = nullptr;
-  bool host_contiguous = false;   // all 2B host images equally spaced, pair-interleaved, device pitch
+  bool sequence = false;
+  bool host_contiguous = false;   // all host images equally spaced in slot order, device pitch
   ptrdiff_t host_stride = 0;
   const uint8_t* d_images = nullptr;
   size_t img_stride = 0;
   size_t pitch = 0;
+  const uint8_t* host_image(int slot) const { return sequence ? img1[slot] : ((slot & 1) ? img2[slot >> 1] : img1[slot >> 1]); }
 };
 
-// copy the images of pair slots [pair0, pair0 + nb) into level 0 of their pyramid slabs
-static int upload_images(rpe_handle* h, const Geometry& G, const BatchSource& src, int pair0, int nb, int H, int W,
+// copy the images of slots [img0, img0 + ni) into level 0 of their pyramid slabs
+static int upload_images(rpe_handle* h, const Geometry& G, const BatchSource& src, int img0, int ni, int H, int W,
                          cudaStream_t s) {
   const int p0 = G.g.lv[0].pitch;
-  uint8_t* dst = h->ob.pyr + (size_t)(2 * pair0) * h->pyr_stride;
+  uint8_t* dst = h->ob.pyr + (size_t)img0 * h->pyr_stride;
   if (src.d_images) {
-    const uint8_t* from = src.d_images + (size_t)(2 * pair0) * src.img_stride;
+    const uint8_t* from = src.d_images + (size_t)img0 * src.img_stride;
     if (src.pitch == (size_t)p0) {
-      RPE_CK(cudaMemcpy2DAsync(dst, h->pyr_stride, from, src.img_stride, src.pitch * H, 2 * nb, cudaMemcpyDeviceToDevice, s));
+      RPE_CK(cudaMemcpy2DAsync(dst, h->pyr_stride, from, src.img_stride, src.pitch * H, ni, cudaMemcpyDeviceToDevice, s));
     } else {
-      for (int i = 0; i < 2 * nb; ++i)
+      for (int i = 0; i < ni; ++i)
         RPE_CK(cudaMemcpy2DAsync(dst + (size_t)i * h->pyr_stride, p0, from + (size_t)i * src.img_stride, src.pitch, W, H,
                                  cudaMemcpyDeviceToDevice, s));
     }
   } else if (src.host_contiguous) {
-    RPE_CK(cudaMemcpy2DAsync(dst, h->pyr_stride, src.img1[pair0], (size_t)src.host_stride, src.pitch * H, 2 * nb,
-                             cudaMemcpyHostToDevice, s));
+    RPE_CK(cudaMemcpy2DAsync(dst, h->pyr_stride, src.host_image(0) + (ptrdiff_t)img0 * src.host_stride,
+                             (size_t)src.host_stride, src.pitch * H, ni, cudaMemcpyHostToDevice, s));
   } else {
-    for (int i = 0; i < nb; ++i) {
-      RPE_CK(cudaMemcpy2DAsync(dst + (size_t)(2 * i) * h->pyr_stride, p0, src.img1[pair0 + i], src.pitch, W, H,
+    for (int i = 0; i < ni; ++i)
+      RPE_CK(cudaMemcpy2DAsync(dst + (size_t)i * h->pyr_stride, p0, src.host_image(img0 + i), src.pitch, W, H,
                                cudaMemcpyHostToDevice, s));
-      RPE_CK(cudaMemcpy2DAsync(dst + (size_t)(2 * i + 1) * h->pyr_stride, p0, src.img2[pair0 + i], src.pitch, W, H,
-                               cudaMemcpyHostToDevice, s));
-    }
   }
   return RPE_OK;
 }
 
-static void fill_host_source(BatchSource& src, const uint8_t* const* img1, const uint8_t* const* img2, int B, int H,
-                             int W, size_t pitch) {
-  src.img1 = img1; src.img2 = img2; src.pitch = pitch;
-  // fast path: all 2B images equally spaced in one host buffer with the device pitch -> one copy per chunk
+static void fill_host_source(BatchSource& src, const uint8_t* const* img1, const uint8_t* const* img2, int n_img, int H,
+                             int W, size_t pitch, bool sequence) {
+  src.img1 = img1; src.img2 = img2; src.pitch = pitch; src.sequence = sequence;
+  // fast path: all images equally spaced in one host buffer with the device pitch -> one copy per chunk
   const int p0 = align_up(W, 16);
-  bool contiguous = (pitch == (size_t)p0);
-  const ptrdiff_t stride = (const uint8_t*)img2[0] - (const uint8_t*)img1[0];
+  bool contiguous = (pitch == (size_t)p0) && n_img >= 2;
+  const ptrdiff_t stride = contiguous ? src.host_image(1) - src.host_image(0) : 0;
   if (contiguous && stride >= (ptrdiff_t)(pitch * H)) {
-    for (int i = 0; i < B && contiguous; ++i)
-      contiguous = (img1[i] == img1[0] + (ptrdiff_t)2 * i * stride) && (img2[i] == img1[i] + stride);
+    for (int i = 0; i < n_img && contiguous; ++i) contiguous = (src.host_image(i) == src.host_image(0) + (ptrdiff_t)i * stride);
   } else contiguous = false;
   src.host_contiguous = contiguous;
   src.host_stride = stride;
 }
 
-// The whole hot path over B pairs.  Profiling (or n_streams == 1): one chunk on the handle's stream,
-// with an event between stages when profiling.  Otherwise a copy / dense / tail stream pipeline over
-// chunks, forked from and joined back into the handle's stream.
+// The whole hot path over B pairs (pair batch: 2B images; sequence: B + 1 frames).  Profiling (or
+// n_streams == 1): one chunk on the handle's stream, with an event between stages when profiling.
+// Otherwise a copy / compute stream pipeline over chunks of images, forked from and joined back into
+// the handle's stream.
 static int enqueue_batch(rpe_handle* h, const BatchSource& src, int B, int H, int W, const double K[9], double* R,
                          double* t, double* euler, int32_t* status, int32_t* info) {
   if (h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is still pending: call rpe_wait_batch first");
@@ -609,17 +611,19 @@ static int enqueue_batch(rpe_handle* h, const BatchSource& src, int B, int H, in
   RPE_TRY(get_geometry(h, W, H, &G));
   reset_profile(h);
   const bool prof = h->profiling;
+  const int pstep = src.sequence ? 1 : 2;
+  const int n_img = src.sequence ? B + 1 : 2 * B;
   mark(h, RPE_T_H2D, prof);
   RPE_TRY(upload_K(h, K));
   RPE_TRY(clear_counters(h, h->stream));
   // device-resident inputs have no upload to hide: one chunk (chunking only costs kernel tails)
-  const int chunk = (prof || h->n_workers < 2 || src.d_images) ? B : std::min(B, h->chunk_pairs);
-  const int n_chunks = (B + chunk - 1) / chunk;
+  const int chunk_img = (prof || h->n_workers < 2 || src.d_images) ? n_img : std::min(n_img, 2 * h->chunk_pairs);
+  const int n_chunks = (n_img + chunk_img - 1) / chunk_img;
   if (n_chunks == 1) {
-    RPE_TRY(upload_images(h, *G, src, 0, B, H, W, h->stream));
-    RPE_TRY(run_orb(h, *G, 0, 2 * B, h->stream, prof));
-    RPE_TRY(run_match(h, 0, B, h->stream, prof));
-    RPE_TRY(run_geometry(h, 0, B, h->stream, prof));
+    RPE_TRY(upload_images(h, *G, src, 0, n_img, H, W, h->stream));
+    RPE_TRY(run_orb(h, *G, 0, n_img, h->stream, prof));
+    RPE_TRY(run_match(h, 0, B, pstep, h->stream, prof));
+    RPE_TRY(run_geometry(h, 0, B, pstep, h->stream, prof));
     mark(h, RPE_T_D2H, prof);
     RPE_TRY(download_async(h, 0, B, info != nullptr, h->stream));
     if (prof) cudaEventRecord(h->ev[RPE_T_COUNT], h->stream);
@@ -627,28 +631,35 @@ static int enqueue_batch(rpe_handle* h, const BatchSource& src, int B, int H, in
     // copy stream + (n_workers - 1) compute streams.  The image upload of chunk c+1 runs under the
     // kernels of chunk c; chunks alternate between the compute streams so that the tail of one
     // chunk's kernels (and its latency-bound RANSAC / pose) is filled by the next chunk's kernels.
-    static const int tail_mode = getenv("RPE_PIPE_TAIL") ? atoi(getenv("RPE_PIPE_TAIL")) : 0;   // experiment knob
+    // Sequence mode: the pair that straddles two chunks needs the features of the previous chunk's
+    // last frame, so a chunk's matcher waits for the previous chunk's ORB (e_orb).
     cudaStream_t s_copy = h->wstream[0];
     const int nc = h->n_workers - 1;
     RPE_CK(cudaEventRecord(h->ev_fork, h->stream));
     for (int w = 0; w <= nc; ++w) RPE_CK(cudaStreamWaitEvent(h->wstream[w], h->ev_fork, 0));
+    cudaEvent_t e_orb_prev = nullptr;
     for (int c = 0; c < n_chunks; ++c) {
-      const int pair0 = c * chunk, nb = std::min(chunk, B - pair0);
+      const int img0 = c * chunk_img, ni = std::min(chunk_img, n_img - img0);
+      // pairs completed by this chunk: [pair0, pair1)
+      const int pair0 = src.sequence ? std::max(img0 - 1, 0) : img0 / 2;
+      const int pair1 = src.sequence ? img0 + ni - 1 : (img0 + ni) / 2;
       cudaEvent_t e_up = h->ev_chunk[(2 * c) % rpe_handle::kChunkEvents];
-      cudaEvent_t e_dense = h->ev_chunk[(2 * c + 1) % rpe_handle::kChunkEvents];
-      cudaStream_t s_dense = tail_mode ? h->wstream[1] : h->wstream[1 + c % nc];
-      cudaStream_t s_tail = (tail_mode && nc >= 2) ? h->wstream[2] : s_dense;
-      RPE_TRY(upload_images(h, *G, src, pair0, nb, H, W, s_copy));
+      cudaEvent_t e_orb = h->ev_chunk[(2 * c + 1) % rpe_handle::kChunkEvents];
+      cudaStream_t s_dense = h->wstream[1 + c % nc];
+      RPE_TRY(upload_images(h, *G, src, img0, ni, H, W, s_copy));
       RPE_CK(cudaEventRecord(e_up, s_copy));
       RPE_CK(cudaStreamWaitEvent(s_dense, e_up, 0));
-      RPE_TRY(run_orb(h, *G, 2 * pair0, 2 * nb, s_dense, false));
-      RPE_TRY(run_match(h, pair0, nb, s_dense, false));
-      if (s_tail != s_dense) {
-        RPE_CK(cudaEventRecord(e_dense, s_dense));
-        RPE_CK(cudaStreamWaitEvent(s_tail, e_dense, 0));
+      RPE_TRY(run_orb(h, *G, img0, ni, s_dense, false));
+      if (src.sequence) {
+        RPE_CK(cudaEventRecord(e_orb, s_dense));
+        if (e_orb_prev) RPE_CK(cudaStreamWaitEvent(s_dense, e_orb_prev, 0));
+        e_orb_prev = e_orb;
       }
-      RPE_TRY(run_geometry(h, pair0, nb, s_tail, false));
-      RPE_TRY(download_async(h, pair0, nb, info != nullptr, s_tail));
+      if (pair1 > pair0) {
+        RPE_TRY(run_match(h, pair0, pair1 - pair0, pstep, s_dense, false));
+        RPE_TRY(run_geometry(h, pair0, pair1 - pair0, pstep, s_dense, false));
+        RPE_TRY(download_async(h, pair0, pair1 - pair0, info != nullptr, s_dense));
+      }
     }
     for (int w = 0; w <= nc; ++w) {
       RPE_CK(cudaEventRecord(h->ev_done[w], h->wstream[w]));
@@ -657,6 +668,7 @@ static int enqueue_batch(rpe_handle* h, const BatchSource& src, int B, int H, in
   }
   h->last_geom = G;
   h->last_pairs = B;
+  h->last_pstep = pstep;
   h->pending.active = true; h->pending.B = B;
   h->pending.R = R; h->pending.t = t; h->pending.euler = euler; h->pending.status = status; h->pending.info = info;
   return RPE_OK;
@@ -684,7 +696,7 @@ int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t*
   RPE_TRY(check_batch(h, B, H, W, pitch));
   if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
   BatchSource src;
-  fill_host_source(src, img1, img2, B, H, W, pitch);
+  fill_host_source(src, img1, img2, 2 * B, H, W, pitch, false);
   return run_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
@@ -694,7 +706,7 @@ int rpe_submit_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* c
   RPE_TRY(check_batch(h, B, H, W, pitch));
   if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
   BatchSource src;
-  fill_host_source(src, img1, img2, B, H, W, pitch);
+  fill_host_source(src, img1, img2, 2 * B, H, W, pitch, false);
   return enqueue_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
@@ -723,6 +735,46 @@ int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img
   return run_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
+// ---- consecutive-frame form ----------------------------------------------------
+static int check_sequence(rpe_handle* h, int F, int H, int W, size_t pitch) {
+  if (!h) return fail(RPE_ERR_INVALID, "null handle");
+  if (F < 2) return fail(RPE_ERR_INVALID, "a sequence needs at least 2 frames");
+  if (F > h->NI) return fail(RPE_ERR_CAPACITY, "more frames than 2 * max_pairs image slots");
+  return check_batch(h, F - 1, H, W, pitch);
+}
+
+int rpe_submit_sequence(rpe_handle* h, const uint8_t* const* frames, int32_t F, int32_t H, int32_t W, size_t pitch,
+                        const double K[9], double* R, double* t, double* euler, int32_t* status, int32_t* info) {
+  RPE_TRY(check_sequence(h, F, H, W, pitch));
+  if (!frames || !K) return fail(RPE_ERR_INVALID, "null argument");
+  BatchSource src;
+  fill_host_source(src, frames, nullptr, F, H, W, pitch, true);
+  return enqueue_batch(h, src, F - 1, H, W, K, R, t, euler, status, info);
+}
+
+int rpe_estimate_sequence(rpe_handle* h, const uint8_t* const* frames, int32_t F, int32_t H, int32_t W, size_t pitch,
+                          const double K[9], double* R, double* t, double* euler, int32_t* status, int32_t* info) {
+  RPE_TRY(rpe_submit_sequence(h, frames, F, H, W, pitch, K, R, t, euler, status, info));
+  return wait_batch(h);
+}
+
+int rpe_submit_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t img_stride, int32_t F, int32_t H,
+                               int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
+                               int32_t* status, int32_t* info) {
+  RPE_TRY(check_sequence(h, F, H, W, pitch));
+  if (!d_frames || !K || img_stride < pitch * (size_t)H) return fail(RPE_ERR_INVALID, "bad device image arguments");
+  BatchSource src;
+  src.d_images = d_frames; src.img_stride = img_stride; src.pitch = pitch; src.sequence = true;
+  return enqueue_batch(h, src, F - 1, H, W, K, R, t, euler, status, info);
+}
+
+int rpe_estimate_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t img_stride, int32_t F, int32_t H,
+                                 int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
+                                 int32_t* status, int32_t* info) {
+  RPE_TRY(rpe_submit_sequence_device(h, d_frames, img_stride, F, H, W, pitch, K, R, t, euler, status, info));
+  return wait_batch(h);
+}
+
 int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size_t pitch, float* x, float* y,
                    float* size, float* angle, float* response, int32_t* octave, uint8_t* desc, int32_t* n_out,
                    int32_t* flags_out) {
@@ -737,6 +789,7 @@ int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size
   RPE_TRY(run_orb(h, *G, 0, 1, h->stream, false));
   h->last_geom = G;
   h->last_pairs = 0;
+  h->last_pstep = 2;
   int32_t n = 0;
   uint32_t fl = 0;
   RPE_CK(cudaMemcpyAsync(&n, h->ob.kp_n, sizeof n, cudaMemcpyDeviceToHost, h->stream));
@@ -772,8 +825,8 @@ int rpe_match(rpe_handle* h, const uint8_t* desc1, int32_t n1, const uint8_t* de
   RPE_CK(cudaMemcpyAsync(h->ob.kp_n, nn, sizeof nn, cudaMemcpyHostToDevice, s));
   RPE_CK(cudaStreamSynchronize(s));   // nn is a stack buffer
   int* ln = h->launches;
-  launch_match(h->ob, h->mb, h->kp_stride, 1, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
-  launch_build_matches(h->ob, h->mb, h->kp_stride, h->mcap, h->sort_cap_match, 1, h->cfg.match_mode, h->cfg.ratio,
+  launch_match(h->ob, h->mb, h->kp_stride, 1, 2, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
+  launch_build_matches(h->ob, h->mb, h->kp_stride, h->mcap, h->sort_cap_match, 1, 2, h->cfg.match_mode, h->cfg.ratio,
                        h->cfg.max_matches, s, &ln[RPE_T_MATCH_SORT]);
   RPE_CK(cudaGetLastError());
   int32_t m = 0;
@@ -855,7 +908,7 @@ int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const 
   RPE_TRY(upload_points(h, pts1, pts2, m, K));
   GeomBuffers gb = h->gb;
   gb.rinfo = nullptr;
-  launch_pose(h->mb, gb, h->mcap, 1, ransac_params(h), nullptr, nullptr, h->stream, &h->launches[RPE_T_POSE]);
+  launch_pose(h->mb, gb, h->mcap, 1, ransac_params(h), nullptr, nullptr, 2, h->stream, &h->launches[RPE_T_POSE]);
   RPE_CK(cudaGetLastError());
   RPE_CK(cudaStreamSynchronize(h->stream));
   if (R) RPE_CK(cudaMemcpy(R, h->gb.R, 9 * sizeof(double), cudaMemcpyDeviceToHost));
@@ -872,7 +925,7 @@ int rpe_get_stage(rpe_handle* h, int32_t pair, int32_t view, int32_t stage, int3
   if (pair < 0 || pair >= h->NP || view < 0 || view > 1) return fail(RPE_ERR_INVALID, "bad pair/view");
   RPE_CK(cudaSetDevice(h->device));
   RPE_CK(cudaStreamSynchronize(h->stream));
-  const size_t img = 2 * (size_t)pair + view, KS = h->kp_stride, MC = h->mcap;
+  const size_t img = (size_t)h->last_pstep * pair + view, KS = h->kp_stride, MC = h->mcap;
   const size_t cap = *n;
   auto copy = [&](const void* src, size_t bytes) -> int {
     const size_t c = std::min(bytes, cap);

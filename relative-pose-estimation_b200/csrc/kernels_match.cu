@@ -21,12 +21,13 @@ constexpr int kTrainTile = 128;               // train descriptors per shared-me
 
 template <bool kTop2, bool kCsa4>
 __global__ void __launch_bounds__(kMatchThreads)
-k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride,
+k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride, int pstep,
           uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
   __shared__ uint4 s_train[kTrainTile * 2];
   const int pair = blockIdx.y;
   const int dir = blockIdx.z;                  // 0: view1 -> view2, 1: view2 -> view1
-  const int qi = 2 * pair + dir, ti = 2 * pair + 1 - dir;
+  // image slots of the two views: pstep = 2 (pair batch: 2p, 2p+1) or 1 (consecutive frames: p, p+1)
+  const int qi = pstep * pair + dir, ti = pstep * pair + 1 - dir;
   const int nq = kp_n[qi], nt = kp_n[ti];
   const int q0 = blockIdx.x * kQPB;
   if (q0 >= nq) return;
@@ -73,7 +74,7 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
   }
 }
 
-void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int mode,
+void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int pstep, int mode,
                   cudaStream_t s, int* launches) {
   const int qblocks = (kp_stride + kQPB - 1) / kQPB;
   static const int variant = getenv("RPE_MATCH_VARIANT") ? atoi(getenv("RPE_MATCH_VARIANT")) : 0;   // tuning knob
@@ -81,7 +82,7 @@ void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, i
   dim3 grid(qblocks, n_pairs, top2 ? 1 : 2);
   auto k = top2 ? (variant == 1 ? k_hamming<true, true> : k_hamming<true, false>)
                 : (variant == 1 ? k_hamming<false, true> : k_hamming<false, false>);
-  k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, mb.fwd1, mb.fwd2, mb.bwd1);
+  k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, mb.fwd1, mb.fwd2, mb.bwd1);
   ++*launches;
 }
 
@@ -110,7 +111,7 @@ __device__ __forceinline__ uint32_t match_key(int q, int mode, double ratio, int
 
 __global__ void __launch_bounds__(kBuildThreads)
 k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, const int32_t* __restrict__ kp_n,
-                int kp_stride, const uint32_t* __restrict__ fwd1, const uint32_t* __restrict__ fwd2,
+                int kp_stride, int pstep, const uint32_t* __restrict__ fwd1, const uint32_t* __restrict__ fwd2,
                 const uint32_t* __restrict__ bwd1, int mode, double ratio, int max_matches, int mcap,
                 int sort_cap, int32_t* __restrict__ m_q, int32_t* __restrict__ m_t, int32_t* __restrict__ m_d,
                 int32_t* __restrict__ m_n, float* __restrict__ pts1, float* __restrict__ pts2) {
@@ -119,7 +120,8 @@ k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, 
   __shared__ uint32_t s_warp[kBuildThreads / 32];
   __shared__ uint32_t s_cut, s_take, s_n, s_running;
   const int pair = blockIdx.x, tid = threadIdx.x;
-  const int n1 = kp_n[2 * pair], n2 = kp_n[2 * pair + 1];
+  const int v1 = pstep * pair, v2 = v1 + 1;   // image slots of the two views
+  const int n1 = kp_n[v1], n2 = kp_n[v2];
   const uint32_t* f1 = fwd1 + (size_t)pair * kp_stride;
   const uint32_t* f2 = fwd2 + (size_t)pair * kp_stride;
   const uint32_t* b1 = bwd1 + (size_t)pair * kp_stride;
@@ -188,10 +190,10 @@ k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, 
       __syncthreads();
     }
   }
-  const float* x1 = kp_x + (size_t)(2 * pair) * kp_stride;
-  const float* y1 = kp_y + (size_t)(2 * pair) * kp_stride;
-  const float* x2 = kp_x + (size_t)(2 * pair + 1) * kp_stride;
-  const float* y2 = kp_y + (size_t)(2 * pair + 1) * kp_stride;
+  const float* x1 = kp_x + (size_t)v1 * kp_stride;
+  const float* y1 = kp_y + (size_t)v1 * kp_stride;
+  const float* x2 = kp_x + (size_t)v2 * kp_stride;
+  const float* y2 = kp_y + (size_t)v2 * kp_stride;
   for (uint32_t i = tid; i < n; i += kBuildThreads) {
     const uint32_t k = s_keys[i];
     const int q = k & 0xfffffu, d = k >> 20;
@@ -205,9 +207,11 @@ k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, 
 }
 
 void launch_build_matches(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int mcap, int sort_cap,
-                          int n_pairs, int mode, double ratio, int max_matches, cudaStream_t s, int* launches) {
+                          int n_pairs, int pstep, int mode, double ratio, int max_matches, cudaStream_t s,
+                          int* launches) {
   k_build_matches<<<n_pairs, kBuildThreads, (size_t)sort_cap * 4, s>>>(
-      ob.kp_x, ob.kp_y, ob.kp_n, kp_stride, mb.fwd1, mb.fwd2, mb.bwd1, mode, ratio, max_matches, mcap, sort_cap,
+      ob.kp_x, ob.kp_y, ob.kp_n, kp_stride, pstep, mb.fwd1, mb.fwd2, mb.bwd1, mode, ratio, max_matches, mcap,
+      sort_cap,
       mb.m_q, mb.m_t, mb.m_d, mb.m_n, mb.pts1, mb.pts2);
   ++*launches;
 }

@@ -107,17 +107,18 @@ void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t 
 void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
 void launch_blur(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
 void launch_describe(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
-void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int mode,
+// pstep: image slots of pair p are pstep*p and pstep*p + 1 (2 = pair batch, 1 = consecutive frames)
+void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int pstep, int mode,
                   cudaStream_t s, int* launches);
 void launch_build_matches(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int mcap,
-                          int sort_cap, int n_pairs, int mode, double ratio, int max_matches,
+                          int sort_cap, int n_pairs, int pstep, int mode, double ratio, int max_matches,
                           cudaStream_t s, int* launches);
 void launch_normalize(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, const double* dK,
                       cudaStream_t s, int* launches);
 void launch_ransac(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, const double* dK,
                    RansacParams rp, cudaStream_t s, int* launches);
 void launch_pose(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, RansacParams rp,
-                 const uint32_t* img_flags, const int32_t* kp_n, cudaStream_t s, int* launches);
+                 const uint32_t* img_flags, const int32_t* kp_n, int pstep, cudaStream_t s, int* launches);
 int setup_orb_attributes(int sort_cap);
 int setup_match_attributes(int sort_cap);
 int setup_geom_attributes();

@@ -168,6 +168,59 @@ class Engine:
                 "rpe_estimate_batch_device")
         return {"R": R, "t": t, "euler": e, "status": st, "info": info}
 
+    # ------------------------------------------------------------------ consecutive frames (feature cache)
+    def _frame_ptrs(self, frames):
+        if isinstance(frames, np.ndarray) and frames.ndim == 3 and frames.dtype == np.uint8 and frames.strides[2] == 1:
+            F, H, W = frames.shape
+            base, step = frames.ctypes.data, frames.strides[0]
+            return (C.c_void_p * F)(*[base + i * step for i in range(F)]), F, H, W, frames.strides[1], frames
+        arrs = [np.ascontiguousarray(f, dtype=np.uint8) for f in frames]
+        if len(arrs) < 2:
+            raise ValueError("a sequence needs at least 2 frames")
+        H, W = arrs[0].shape
+        for a in arrs:
+            if a.shape != (H, W):
+                raise ValueError("all frames of a sequence must be 2-D uint8 of one size")
+        return (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs]), len(arrs), H, W, W, arrs
+
+    def estimate_sequence(self, frames, K):
+        """frames: (F, H, W) uint8 host array or list of F gray images -> results of the F-1 consecutive
+        pairs (k, k+1); ORB runs once per frame (rpe_estimate_sequence).  Same dict as estimate_batch."""
+        ptrs, F, H, W, pitch, keep = self._frame_ptrs(frames)
+        K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
+        R, t, e, st, info = self._outputs(F - 1)
+        L.check(self._lib.rpe_estimate_sequence(self._h, ptrs, F, H, W, pitch, _ptr(K), _ptr(R), _ptr(t), _ptr(e),
+                                                _ptr(st), _ptr(info)), "rpe_estimate_sequence")
+        return {"R": R, "t": t, "euler": e, "status": st, "info": info}
+
+    def submit_sequence(self, frames, K):
+        """Asynchronous estimate_sequence (rpe_submit_sequence); ``wait()`` returns the result dict."""
+        ptrs, F, H, W, pitch, keep = self._frame_ptrs(frames)
+        K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
+        R, t, e, st, info = self._outputs(F - 1)
+        L.check(self._lib.rpe_submit_sequence(self._h, ptrs, F, H, W, pitch, _ptr(K), _ptr(R), _ptr(t), _ptr(e),
+                                              _ptr(st), _ptr(info)), "rpe_submit_sequence")
+        self._pending = ({"R": R, "t": t, "euler": e, "status": st, "info": info}, keep, K)
+        return self
+
+    def submit_sequence_device(self, dev_ptr: int, img_stride: int, F: int, H: int, W: int, pitch: int, K):
+        """Asynchronous sequence call on device-resident frames (rpe_submit_sequence_device)."""
+        K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
+        R, t, e, st, info = self._outputs(F - 1)
+        L.check(self._lib.rpe_submit_sequence_device(self._h, C.c_void_p(dev_ptr), img_stride, F, H, W, pitch,
+                                                     _ptr(K), _ptr(R), _ptr(t), _ptr(e), _ptr(st), _ptr(info)),
+                "rpe_submit_sequence_device")
+        self._pending = ({"R": R, "t": t, "euler": e, "status": st, "info": info}, None, K)
+        return self
+
+    def estimate_sequence_device(self, dev_ptr: int, img_stride: int, F: int, H: int, W: int, pitch: int, K):
+        K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
+        R, t, e, st, info = self._outputs(F - 1)
+        L.check(self._lib.rpe_estimate_sequence_device(self._h, C.c_void_p(dev_ptr), img_stride, F, H, W, pitch,
+                                                       _ptr(K), _ptr(R), _ptr(t), _ptr(e), _ptr(st), _ptr(info)),
+                "rpe_estimate_sequence_device")
+        return {"R": R, "t": t, "euler": e, "status": st, "info": info}
+
     # ------------------------------------------------------------------ stage entry points
     def orb_detect(self, img):
         img = np.ascontiguousarray(img, dtype=np.uint8)

@@ -86,6 +86,17 @@ class PoseEstimator:
         self.last = out
         return out["R"], out["t"], out["status"]
 
+    def estimate_sequence(self, frames):
+        """Consecutive pairs (k, k+1) of a frame sequence, ORB once per frame (the reference runs it on
+        both frames of every pair, src/core/pose_estimator.py:505-506, so interior frames twice);
+        results are bit-identical to ``estimate_batch(frames[:-1], frames[1:])``.
+        -> (R (F-1,3,3), t (F-1,3,1), status (F-1,))."""
+        frames = [self._gray(f) for f in frames]
+        H, W = frames[0].shape
+        out = self._ensure_engine(W, H, len(frames) - 1).estimate_sequence(frames, self.K)
+        self.last = out
+        return out["R"], out["t"], out["status"]
+
     def _raise_for(self, status, num_matches):
         code = int(status) & 0xFF
         if code == L.STATUS_INSUFFICIENT_MATCHES:

@@ -8,6 +8,11 @@ Per pair: seed = 1000*cfg + pair_idx.  View 1 = multi-octave noise texture scale
 plus floor(W*H/1500) filled axis-aligned rectangles; view 2 = view 1 warped by the homography
 induced by a small random motion (rvec ~ U(-0.03,0.03)^3, t ~ U(-0.1,0.1)^3) of a camera
 looking at the plane z = 5; K = [[0.9W,0,W/2],[0,0.9W,H/2],[0,0,1]].
+
+Stream (config 5): ONE base texture per stream (seed = 1000*cfg + stream_idx) seen by a camera whose pose
+is a smooth bounded function of the frame index (three sinusoids per axis, random phase); frame k =
+the base texture warped by the plane homography of pose k, so consecutive frames differ by a small
+motion and any frame can be generated independently (shards need no state).
 """
 from __future__ import annotations
 
@@ -61,4 +66,55 @@ def synth_batch(cfg: int, first_pair: int, n_pairs: int, W: int, H: int, out: np
         a, b, _, _, _ = synth_pair(cfg, first_pair + i, W, H)
         out[2 * i] = a
         out[2 * i + 1] = b
+    return out
+
+
+_STREAM_CACHE: dict = {}
+
+
+def _stream_state(cfg: int, stream_idx: int, W: int, H: int):
+    key = (cfg, stream_idx, W, H)
+    if key not in _STREAM_CACHE:
+        rng = np.random.default_rng(1000 * cfg + stream_idx)
+        base = synth_texture(rng, W, H)
+        # per axis: amplitude, angular frequency (periods of 40 .. 120 frames), phase
+        par = {"r_amp": rng.uniform(0.02, 0.05, 3), "r_w": 2 * np.pi / rng.uniform(40, 120, 3),
+               "r_ph": rng.uniform(0, 2 * np.pi, 3), "t_amp": rng.uniform(0.08, 0.2, 3),
+               "t_w": 2 * np.pi / rng.uniform(40, 120, 3), "t_ph": rng.uniform(0, 2 * np.pi, 3)}
+        _STREAM_CACHE.clear()
+        _STREAM_CACHE[key] = (base, par)
+    return _STREAM_CACHE[key]
+
+
+def stream_pose(cfg: int, stream_idx: int, k: int, W: int, H: int):
+    """Camera pose (R_k, t_k) of frame k relative to the base view."""
+    _, p = _stream_state(cfg, stream_idx, W, H)
+    rvec = p["r_amp"] * np.sin(p["r_w"] * k + p["r_ph"])
+    t = p["t_amp"] * np.sin(p["t_w"] * k + p["t_ph"])
+    R, _ = cv2.Rodrigues(rvec)
+    return R, t
+
+
+def stream_relative_pose(cfg: int, stream_idx: int, k: int, W: int, H: int):
+    """Ground-truth relative pose of the pair (frame k, frame k+1): R_rel, unit t_rel."""
+    R0, t0 = stream_pose(cfg, stream_idx, k, W, H)
+    R1, t1 = stream_pose(cfg, stream_idx, k + 1, W, H)
+    Rr = R1 @ R0.T
+    tr = t1 - Rr @ t0
+    return Rr, tr / max(np.linalg.norm(tr), 1e-300)
+
+
+def synth_stream(cfg: int, first_frame: int, n_frames: int, W: int, H: int, stream_idx: int = 0,
+                 out: np.ndarray | None = None):
+    """(n_frames, H, W) uint8: frames first_frame .. first_frame + n_frames - 1 of stream ``stream_idx``."""
+    base, _ = _stream_state(cfg, stream_idx, W, H)
+    K = synth_K(W, H)
+    Ki = np.linalg.inv(K)
+    n = np.array([0.0, 0.0, 1.0])
+    if out is None:
+        out = np.empty((n_frames, H, W), np.uint8)
+    for i in range(n_frames):
+        R, t = stream_pose(cfg, stream_idx, first_frame + i, W, H)
+        Hm = K @ (R + np.outer(t, n) / 5.0) @ Ki
+        cv2.warpPerspective(base, Hm, (W, H), dst=out[i], flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
     return out

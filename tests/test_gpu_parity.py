@@ -295,3 +295,36 @@ def test_submit_wait_equals_blocking_call(engine):
             engine.wait()
     finally:
         other.close()
+
+
+def test_sequence_equals_pair_batch(engine):
+    """rpe_estimate_sequence (ORB once per frame) == rpe_estimate_batch on the consecutive pairs, bit for bit,
+    for blocking, chunked-pipeline and submit/wait forms; stage accessors address frames by (pair, view)."""
+    from rpe_b200 import _lib as L
+    names = ["sim_000000.png", "sim_000015.png", "sim_000030.png", "sim_000015.png", "sim_000000.png"]
+    frames = [load_gray(n) for n in names]
+    K = default_K()
+    want = engine.estimate_batch(frames[:-1], frames[1:], K)
+    want_kp = [engine.keypoints(i, v) for i in range(4) for v in (0, 1)]
+    want_m = [engine.get_stage(i, 0, L.STAGE_MATCHES, 0, np.int32).copy() for i in range(4)]
+    assert (want["status"] == 0).all()
+    stack = np.ascontiguousarray(np.stack(frames))
+    for chunk, streams, src in [(32, 1, frames), (1, 3, frames), (1, 4, stack), (2, 2, stack)]:
+        engine.set_pipeline(chunk, streams)
+        got = engine.estimate_sequence(src, K)
+        for k in ("R", "t", "euler", "status", "info"):
+            assert np.array_equal(got[k], want[k]), (k, chunk, streams)
+        for i in range(4):
+            assert np.array_equal(engine.get_stage(i, 0, L.STAGE_MATCHES, 0, np.int32), want_m[i])
+            for v in (0, 1):
+                kp = engine.keypoints(i, v)
+                for f, a in want_kp[2 * i + v].items():
+                    assert np.array_equal(kp[f], a), (i, v, f)
+    engine.set_pipeline(32, 4)
+    got = engine.submit_sequence(stack, K).wait()
+    for k in ("R", "t", "euler", "status", "info"):
+        assert np.array_equal(got[k], want[k]), k
+    with pytest.raises(RuntimeError):          # max_pairs = 4 pair slots
+        engine.estimate_sequence([frames[0]] * 6, K)
+    with pytest.raises(Exception):
+        engine.estimate_sequence([frames[0]], K)

@@ -86,7 +86,7 @@ class _FakeGT:
 
 
 class _FakeEstimator:
-    """estimate_batch with a deterministic R_rel per pair; status 2 on request."""
+    """estimate_batch / estimate_sequence with a deterministic R_rel per pair; status 2 on request."""
     def __init__(self, fail_at=None):
         self.fail_at, self.calls = fail_at, 0
 
@@ -99,6 +99,9 @@ class _FakeEstimator:
         self.last = {"info": np.full((B, 4), 3, np.int32)}
         self.calls += 1
         return R, np.tile(np.array([[0.0], [0.0], [1.0]]), (B, 1, 1)), st
+
+    def estimate_sequence(self, frames):
+        return self.estimate_batch(frames[:-1], frames[1:])
 
     def _raise_for(self, status, n):
         if int(status) & 0xFF == 2:
