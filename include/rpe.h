@@ -47,6 +47,10 @@ typedef enum rpe_status {
 
 enum { RPE_MATCH_CROSSCHECK = 0, RPE_MATCH_RATIO = 1 };
 enum { RPE_EULER_YUP = 0, RPE_EULER_ZYX = 1 };
+/* The reference's two colour -> gray paths (they differ by +-1 on about a third of the pixels):
+ * cv2.imread + cv2.cvtColor(BGR2GRAY) (reference: src/utils/image_loader.py:23-28) and
+ * cv2.imread(path, IMREAD_GRAYSCALE) of a colour PNG (reference: src/run_single_pair.py:31-32). */
+enum { RPE_GRAY_CVTCOLOR = 0, RPE_GRAY_IMREAD_PNG = 1 };
 
 /* Mirrors the constructor arguments and hard-coded constants of the reference
  * (reference: src/core/pose_estimator.py:19-32 ctor, :85-91 ORB, :131 matcher, :150 cut,
@@ -87,6 +91,11 @@ int rpe_set_stream(rpe_handle* h, void* cuda_stream);
  * two handles in flight (rpe_submit_batch) use n_streams = 1: batches already overlap each other.
  * Device-resident inputs are never chunked.  Results do not depend on these settings. */
 int rpe_set_pipeline(rpe_handle* h, int32_t chunk_pairs, int32_t n_streams);
+/* pixel format of the images given to the batch / sequence calls (host or device): channels = 1 (default):
+ * H x W uint8 gray; channels = 3: H x W x 3 interleaved BGR as cv2.imread returns it, converted to gray on the
+ * device with the arithmetic of `gray_mode` (RPE_GRAY_*) — replaces load_image's cvtColor
+ * (reference: src/utils/image_loader.py:28).  `pitch` is then the byte pitch of a BGR row (>= 3 W). */
+int rpe_set_input_format(rpe_handle* h, int32_t channels, int32_t gray_mode);
 /* capacities derived from the config: max keypoints per image, max matches per pair */
 int rpe_get_capacity(const rpe_handle* h, int32_t* kp_cap, int32_t* match_cap);
 
@@ -148,6 +157,11 @@ int rpe_submit_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t im
 int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size_t pitch,
                    float* x, float* y, float* size, float* angle, float* response,
                    int32_t* octave, uint8_t* desc, int32_t* n_out, int32_t* flags_out);
+
+/* replaces cv2.cvtColor(img, COLOR_BGR2GRAY) / the decoder-side conversion of IMREAD_GRAYSCALE (see
+ * RPE_GRAY_*): bgr = H x W x 3 host image, gray = H x W tight host output (stage entry for parity). */
+int rpe_bgr_to_gray(rpe_handle* h, const uint8_t* bgr, int32_t H, int32_t W, size_t pitch, int32_t gray_mode,
+                    uint8_t* gray);
 
 /* replaces _match_descriptors (reference: src/core/pose_estimator.py:133-153): matcher in the
  * handle's match_mode, stable sort by distance, max_matches cut.  matches: m_cap*3 int32

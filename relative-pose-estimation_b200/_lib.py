@@ -21,6 +21,7 @@ STATUS_OK, STATUS_NO_DESCRIPTORS, STATUS_INSUFFICIENT_MATCHES, STATUS_E_FAILED =
 STATUS_FLAG_OVERFLOW = 0x100
 MATCH_CROSSCHECK, MATCH_RATIO = 0, 1
 EULER_YUP, EULER_ZYX = 0, 1
+GRAY_CVTCOLOR, GRAY_IMREAD_PNG = 0, 1
 
 (STAGE_PYRAMID_LEVEL, STAGE_BLURRED_LEVEL, STAGE_KP_X, STAGE_KP_Y, STAGE_KP_SIZE, STAGE_KP_ANGLE,
  STAGE_KP_RESPONSE, STAGE_KP_OCTAVE, STAGE_DESCRIPTORS, STAGE_MATCHES, STAGE_PTS1, STAGE_PTS2, STAGE_E,
@@ -47,6 +48,7 @@ _SIGNATURES = [
     ("rpe_destroy", None, [_P]),
     ("rpe_set_stream", C.c_int, [_P, _P]),
     ("rpe_set_pipeline", C.c_int, [_P, C.c_int32, C.c_int32]),
+    ("rpe_set_input_format", C.c_int, [_P, C.c_int32, C.c_int32]),
     ("rpe_get_capacity", C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     ("rpe_estimate_batch", C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     ("rpe_submit_batch", C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
@@ -58,6 +60,7 @@ _SIGNATURES = [
     ("rpe_estimate_sequence_device", C.c_int, [_P, _P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     ("rpe_submit_sequence_device", C.c_int, [_P, _P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     ("rpe_orb_detect", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_size_t, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    ("rpe_bgr_to_gray", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_size_t, C.c_int32, _P]),
     ("rpe_match", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32, _P, _P]),
     ("rpe_find_essential", C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P, _P]),
     ("rpe_ransac_trace", C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P]),

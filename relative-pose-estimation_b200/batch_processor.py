@@ -28,12 +28,15 @@ def load_image(path, to_gray=True):
 
 class BatchProcessor:
     def __init__(self, images_dir, pose_estimator, ground_truth_loader, euler_convention=CONVENTION_YUP,
-                 chunk_pairs=64):
+                 chunk_pairs=64, gpu_gray=True):
         self.images_dir = Path(images_dir)
         self.pose_estimator = pose_estimator
         self.gt_loader = ground_truth_loader
         self.euler_convention = euler_convention
         self.chunk_pairs = int(chunk_pairs)
+        # True: frames go to the GPU as decoded (BGR) and load_image's cvtColor (image_loader.py:28) runs there,
+        # bit-identical (k_bgr2gray); False: cv2.cvtColor on the host
+        self.gpu_gray = bool(gpu_gray)
 
     def get_image_path(self, frame_idx):
         return self.images_dir / f"{frame_idx:06d}.png"
@@ -46,7 +49,7 @@ class BatchProcessor:
         n_pairs = len(frame_indices) - 1
         for c0 in range(0, n_pairs, self.chunk_pairs):
             c1 = min(c0 + self.chunk_pairs, n_pairs)
-            frames = [load_image(self.get_image_path(f)) for f in frame_indices[c0:c1 + 1]]
+            frames = [load_image(self.get_image_path(f), to_gray=not self.gpu_gray) for f in frame_indices[c0:c1 + 1]]
             R_rel, t_rel, status = self.pose_estimator.estimate_sequence(frames)
             for k in range(c1 - c0):
                 self.pose_estimator._raise_for(status[k], self.pose_estimator.last["info"][k, 0])

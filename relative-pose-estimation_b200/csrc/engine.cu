@@ -77,6 +77,10 @@ struct rpe_handle {
   std::map<std::pair<int, int>, Geometry> geoms;
   const Geometry* last_geom = nullptr;
   int last_pairs = 0;
+  // input format of the batch / sequence calls (rpe_set_input_format) + lazily allocated BGR staging
+  int in_channels = 1, gray_mode = RPE_GRAY_CVTCOLOR;
+  uint8_t* bgr_stage = nullptr;
+  size_t bgr_stage_stride = 0, bgr_stage_imgs = 0;
   int last_pstep = 2;       // image slots of pair p in the last batch: pstep*p, pstep*p + 1
   // pinned host staging for results: R(9) t(3) euler(3) doubles, status + 4 info ints, K
   double* h_out_d = nullptr;
@@ -333,6 +337,7 @@ void rpe_destroy(rpe_handle* h) {
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
   for (auto& kv : h->geoms) { cudaFree(kv.second.d_taps); cudaFree(kv.second.d_ftab); cudaFree(kv.second.d_btab); }
+  if (h->bgr_stage) cudaFree(h->bgr_stage);
   if (h->gb.tr_subset) { cudaFree(h->gb.tr_subset); cudaFree(h->gb.tr_nmodels); cudaFree(h->gb.tr_counts); cudaFree(h->gb.tr_models); }
   if (h->h_out_d) cudaFreeHost(h->h_out_d);
   if (h->h_out_i) cudaFreeHost(h->h_out_i);
@@ -358,6 +363,15 @@ int rpe_set_pipeline(rpe_handle* h, int32_t chunk_pairs, int32_t n_streams) {
   if (!h || chunk_pairs < 1 || n_streams < 1 || n_streams > rpe_handle::kMaxWorkers) return fail(RPE_ERR_INVALID, "bad pipeline arguments");
   h->chunk_pairs = chunk_pairs;
   h->n_workers = n_streams;
+  return RPE_OK;
+}
+
+int rpe_set_input_format(rpe_handle* h, int32_t channels, int32_t gray_mode) {
+  if (!h || (channels != 1 && channels != 3) || (gray_mode != RPE_GRAY_CVTCOLOR && gray_mode != RPE_GRAY_IMREAD_PNG))
+    return fail(RPE_ERR_INVALID, "channels must be 1 or 3, gray_mode RPE_GRAY_*");
+  if (h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  h->in_channels = channels;
+  h->gray_mode = gray_mode;
   return RPE_OK;
 }
 
@@ -535,7 +549,7 @@ static int finish_results(rpe_handle* h, int B, double* R, double* t, double* eu
 
 static int check_batch(rpe_handle* h, int B, int H, int W, size_t pitch) {
   if (!h) return fail(RPE_ERR_INVALID, "null handle");
-  if (B < 1 || H < 1 || W < 1 || pitch < (size_t)W) return fail(RPE_ERR_INVALID, "bad batch arguments");
+  if (B < 1 || H < 1 || W < 1) return fail(RPE_ERR_INVALID, "bad batch arguments");
   if (B > h->NP) return fail(RPE_ERR_CAPACITY, "batch larger than max_pairs");
   if (W > RPE_MAX_DIM || H > RPE_MAX_DIM) return fail(RPE_ERR_CAPACITY, "image dimension above 4095");
   RPE_CK(cudaSetDevice(h->device));
@@ -553,6 +567,7 @@ struct BatchSource {
   const uint8_t* const* img1 = nullptr;
   const uint8_t* const* img2 = nullptr;
   bool sequence = false;
+  int channels = 1;               // 1: gray; 3: interleaved BGR, converted on the device (k_bgr2gray)
   bool host_contiguous = false;   // all host images equally spaced in slot order, device pitch
   ptrdiff_t host_stride = 0;
   const uint8_t* d_images = nullptr;
@@ -561,36 +576,64 @@ struct BatchSource {
   const uint8_t* host_image(int slot) const { return sequence ? img1[slot] : ((slot & 1) ? img2[slot >> 1] : img1[slot >> 1]); }
 };
 
-// copy the images of slots [img0, img0 + ni) into level 0 of their pyramid slabs
+// staging buffer for interleaved BGR input: n_img slots of H rows x align16(3 W) bytes
+static int ensure_bgr_stage(rpe_handle* h, int n_img, int H, int W) {
+  const size_t stride = (size_t)align_up(align_up(3 * W, 16) * H, 256);
+  if (h->bgr_stage && h->bgr_stage_stride >= stride && h->bgr_stage_imgs >= (size_t)n_img) return RPE_OK;
+  RPE_CK(cudaDeviceSynchronize());
+  if (h->bgr_stage) cudaFree(h->bgr_stage);
+  h->bgr_stage = nullptr;
+  const size_t imgs = std::max<size_t>(n_img, h->bgr_stage_imgs), st = std::max(stride, h->bgr_stage_stride);
+  RPE_CK(cudaMalloc((void**)&h->bgr_stage, imgs * st + 64));
+  h->bgr_stage_stride = st;
+  h->bgr_stage_imgs = imgs;
+  return RPE_OK;
+}
+
+// copy the images of slots [img0, img0 + ni) into level 0 of their pyramid slabs; BGR input goes
+// through the staging buffer (or straight from an aligned device buffer) and k_bgr2gray
 static int upload_images(rpe_handle* h, const Geometry& G, const BatchSource& src, int img0, int ni, int H, int W,
                          cudaStream_t s) {
-  const int p0 = G.g.lv[0].pitch;
-  uint8_t* dst = h->ob.pyr + (size_t)img0 * h->pyr_stride;
+  const bool bgr = src.channels == 3;
+  const int p0 = G.g.lv[0].pitch;                                    // gray pitch of level 0
+  const int dp = bgr ? align_up(3 * W, 16) : p0;                     // device pitch of the copied rows
+  const size_t row = (size_t)W * src.channels;
+  const size_t dstride = bgr ? h->bgr_stage_stride : h->pyr_stride;
+  uint8_t* pyr0 = h->ob.pyr + (size_t)img0 * h->pyr_stride;
+  uint8_t* dst = bgr ? h->bgr_stage + (size_t)img0 * dstride : pyr0;
+  const uint8_t* conv_src = dst;
+  size_t conv_stride = dstride;
+  int conv_pitch = dp;
   if (src.d_images) {
     const uint8_t* from = src.d_images + (size_t)img0 * src.img_stride;
-    if (src.pitch == (size_t)p0) {
-      RPE_CK(cudaMemcpy2DAsync(dst, h->pyr_stride, from, src.img_stride, src.pitch * H, ni, cudaMemcpyDeviceToDevice, s));
+    if (bgr && W % 4 == 0 && src.pitch % 4 == 0 && src.img_stride % 4 == 0 && ((uintptr_t)src.d_images & 3) == 0) {
+      conv_src = from; conv_stride = src.img_stride; conv_pitch = (int)src.pitch;   // convert in place, no staging copy
+    } else if (src.pitch == (size_t)dp) {
+      RPE_CK(cudaMemcpy2DAsync(dst, dstride, from, src.img_stride, src.pitch * H, ni, cudaMemcpyDeviceToDevice, s));
     } else {
       for (int i = 0; i < ni; ++i)
-        RPE_CK(cudaMemcpy2DAsync(dst + (size_t)i * h->pyr_stride, p0, from + (size_t)i * src.img_stride, src.pitch, W, H,
+        RPE_CK(cudaMemcpy2DAsync(dst + (size_t)i * dstride, dp, from + (size_t)i * src.img_stride, src.pitch, row, H,
                                  cudaMemcpyDeviceToDevice, s));
     }
   } else if (src.host_contiguous) {
-    RPE_CK(cudaMemcpy2DAsync(dst, h->pyr_stride, src.host_image(0) + (ptrdiff_t)img0 * src.host_stride,
+    RPE_CK(cudaMemcpy2DAsync(dst, dstride, src.host_image(0) + (ptrdiff_t)img0 * src.host_stride,
                              (size_t)src.host_stride, src.pitch * H, ni, cudaMemcpyHostToDevice, s));
   } else {
     for (int i = 0; i < ni; ++i)
-      RPE_CK(cudaMemcpy2DAsync(dst + (size_t)i * h->pyr_stride, p0, src.host_image(img0 + i), src.pitch, W, H,
+      RPE_CK(cudaMemcpy2DAsync(dst + (size_t)i * dstride, dp, src.host_image(img0 + i), src.pitch, row, H,
                                cudaMemcpyHostToDevice, s));
   }
+  if (bgr)
+    launch_bgr2gray(conv_src, conv_stride, conv_pitch, pyr0, h->pyr_stride, p0, W, H, ni, h->gray_mode, s,
+                    &h->launches[RPE_T_H2D]);
   return RPE_OK;
 }
 
 static void fill_host_source(BatchSource& src, const uint8_t* const* img1, const uint8_t* const* img2, int n_img, int H,
-                             int W, size_t pitch, bool sequence) {
-  src.img1 = img1; src.img2 = img2; src.pitch = pitch; src.sequence = sequence;
+                             int W, size_t pitch, bool sequence, int channels) {
+  src.img1 = img1; src.img2 = img2; src.pitch = pitch; src.sequence = sequence; src.channels = channels;
   // fast path: all images equally spaced in one host buffer with the device pitch -> one copy per chunk
-  const int p0 = align_up(W, 16);
+  const int p0 = align_up(W * channels, 16);
   bool contiguous = (pitch == (size_t)p0) && n_img >= 2;
   const ptrdiff_t stride = contiguous ? src.host_image(1) - src.host_image(0) : 0;
   if (contiguous && stride >= (ptrdiff_t)(pitch * H)) {
@@ -613,6 +656,9 @@ static int enqueue_batch(rpe_handle* h, const BatchSource& src, int B, int H, in
   const bool prof = h->profiling;
   const int pstep = src.sequence ? 1 : 2;
   const int n_img = src.sequence ? B + 1 : 2 * B;
+  if (src.pitch < (size_t)W * src.channels) return fail(RPE_ERR_INVALID, "pitch smaller than one image row");
+  if (src.d_images && src.img_stride < src.pitch * (size_t)H) return fail(RPE_ERR_INVALID, "img_stride smaller than one image");
+  if (src.channels == 3) RPE_TRY(ensure_bgr_stage(h, h->NI, H, W));
   mark(h, RPE_T_H2D, prof);
   RPE_TRY(upload_K(h, K));
   RPE_TRY(clear_counters(h, h->stream));
@@ -696,7 +742,7 @@ int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t*
   RPE_TRY(check_batch(h, B, H, W, pitch));
   if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
   BatchSource src;
-  fill_host_source(src, img1, img2, 2 * B, H, W, pitch, false);
+  fill_host_source(src, img1, img2, 2 * B, H, W, pitch, false, h->in_channels);
   return run_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
@@ -706,7 +752,7 @@ int rpe_submit_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* c
   RPE_TRY(check_batch(h, B, H, W, pitch));
   if (!img1 || !img2 || !K) return fail(RPE_ERR_INVALID, "null argument");
   BatchSource src;
-  fill_host_source(src, img1, img2, 2 * B, H, W, pitch, false);
+  fill_host_source(src, img1, img2, 2 * B, H, W, pitch, false, h->in_channels);
   return enqueue_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
@@ -716,7 +762,7 @@ int rpe_submit_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img_s
   RPE_TRY(check_batch(h, B, H, W, pitch));
   if (!d_images || !K || img_stride < pitch * (size_t)H) return fail(RPE_ERR_INVALID, "bad device image arguments");
   BatchSource src;
-  src.d_images = d_images; src.img_stride = img_stride; src.pitch = pitch;
+  src.d_images = d_images; src.img_stride = img_stride; src.pitch = pitch; src.channels = h->in_channels;
   return enqueue_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
@@ -731,7 +777,7 @@ int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img
   RPE_TRY(check_batch(h, B, H, W, pitch));
   if (!d_images || !K || img_stride < pitch * (size_t)H) return fail(RPE_ERR_INVALID, "bad device image arguments");
   BatchSource src;
-  src.d_images = d_images; src.img_stride = img_stride; src.pitch = pitch;
+  src.d_images = d_images; src.img_stride = img_stride; src.pitch = pitch; src.channels = h->in_channels;
   return run_batch(h, src, B, H, W, K, R, t, euler, status, info);
 }
 
@@ -748,7 +794,7 @@ int rpe_submit_sequence(rpe_handle* h, const uint8_t* const* frames, int32_t F, 
   RPE_TRY(check_sequence(h, F, H, W, pitch));
   if (!frames || !K) return fail(RPE_ERR_INVALID, "null argument");
   BatchSource src;
-  fill_host_source(src, frames, nullptr, F, H, W, pitch, true);
+  fill_host_source(src, frames, nullptr, F, H, W, pitch, true, h->in_channels);
   return enqueue_batch(h, src, F - 1, H, W, K, R, t, euler, status, info);
 }
 
@@ -764,7 +810,7 @@ int rpe_submit_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t im
   RPE_TRY(check_sequence(h, F, H, W, pitch));
   if (!d_frames || !K || img_stride < pitch * (size_t)H) return fail(RPE_ERR_INVALID, "bad device image arguments");
   BatchSource src;
-  src.d_images = d_frames; src.img_stride = img_stride; src.pitch = pitch; src.sequence = true;
+  src.d_images = d_frames; src.img_stride = img_stride; src.pitch = pitch; src.sequence = true; src.channels = h->in_channels;
   return enqueue_batch(h, src, F - 1, H, W, K, R, t, euler, status, info);
 }
 
@@ -780,7 +826,7 @@ int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size
                    int32_t* flags_out) {
   if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   RPE_TRY(check_batch(h, 1, H, W, pitch));
-  if (!img || !n_out) return fail(RPE_ERR_INVALID, "null argument");
+  if (!img || !n_out || pitch < (size_t)W) return fail(RPE_ERR_INVALID, "null argument / bad pitch");
   const Geometry* G;
   RPE_TRY(get_geometry(h, W, H, &G));
   reset_profile(h);
@@ -807,6 +853,26 @@ int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size
   RPE_CK(get(response, h->ob.kp_resp, n * sizeof(float)));
   RPE_CK(get(octave, h->ob.kp_oct, n * sizeof(int32_t)));
   RPE_CK(get(desc, h->ob.desc, (size_t)n * 32));
+  return RPE_OK;
+}
+
+int rpe_bgr_to_gray(rpe_handle* h, const uint8_t* bgr, int32_t H, int32_t W, size_t pitch, int32_t gray_mode,
+                    uint8_t* gray) {
+  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  RPE_TRY(check_batch(h, 1, H, W, pitch));
+  if (!bgr || !gray || pitch < (size_t)3 * W || (gray_mode != RPE_GRAY_CVTCOLOR && gray_mode != RPE_GRAY_IMREAD_PNG))
+    return fail(RPE_ERR_INVALID, "bad argument");
+  const Geometry* G;
+  RPE_TRY(get_geometry(h, W, H, &G));
+  RPE_TRY(ensure_bgr_stage(h, 1, H, W));
+  reset_profile(h);
+  const int dp = align_up(3 * W, 16), p0 = G->g.lv[0].pitch;
+  RPE_CK(cudaMemcpy2DAsync(h->bgr_stage, dp, bgr, pitch, (size_t)3 * W, H, cudaMemcpyHostToDevice, h->stream));
+  launch_bgr2gray(h->bgr_stage, h->bgr_stage_stride, dp, h->ob.pyr, h->pyr_stride, p0, W, H, 1, gray_mode, h->stream,
+                  &h->launches[RPE_T_H2D]);
+  RPE_CK(cudaGetLastError());
+  RPE_CK(cudaMemcpy2DAsync(gray, W, h->ob.pyr, p0, W, H, cudaMemcpyDeviceToHost, h->stream));
+  RPE_CK(cudaStreamSynchronize(h->stream));
   return RPE_OK;
 }
 

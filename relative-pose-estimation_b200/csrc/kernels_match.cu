@@ -19,7 +19,14 @@ constexpr int kQPT = 2;                       // queries per thread
 constexpr int kQPB = kMatchThreads * kQPT;    // queries per block
 constexpr int kTrainTile = 128;               // train descriptors per shared-memory tile
 
-template <bool kTop2, bool kCsa4>
+__device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("min.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));   // VIMNMX3 on sm_100
+  return d;
+}
+
+// kFma: keys built with multiply-adds (FMA pipe) and two train descriptors folded per top-2 update
+template <bool kTop2, bool kCsa4, bool kFma>
 __global__ void __launch_bounds__(kMatchThreads)
 k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride, int pstep,
           uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
@@ -51,15 +58,46 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
     __syncthreads();
     for (int i = tid; i < tn * 2; i += kMatchThreads) s_train[i] = dt[2 * t0 + i];
     __syncthreads();
-#pragma unroll 4
-    for (int j = 0; j < tn; ++j) {
-      const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
+    if (kFma) {
+      // pairs of train descriptors: with m <= M the two new keys, the two smallest of {best1, best2, m, M}
+      // are min(best1, m) and min(max(best1, m), best2, M): five min / max per two distances instead of six
+      int j = 0;
+#pragma unroll 2
+      for (; j + 1 < tn; j += 2) {
+        const uint4 a0 = s_train[2 * j], b0 = s_train[2 * j + 1], a1 = s_train[2 * j + 2], b1 = s_train[2 * j + 3];
 #pragma unroll
-      for (int k = 0; k < kQPT; ++k) {
-        const uint32_t d = hamming256<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w);
-        const uint32_t key = pack_nn(d, (uint32_t)(t0 + j));
-        if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
-        best1[k] = min(best1[k], key);
+        for (int k = 0; k < kQPT; ++k) {
+          const uint32_t k0 = hamming256_key<kCsa4>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j));
+          const uint32_t k1 = hamming256_key<kCsa4>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1));
+          if (kTop2) {
+            const uint32_t m = min(k0, k1), M = max(k0, k1);
+            best2[k] = umin3(max(best1[k], m), best2[k], M);
+            best1[k] = min(best1[k], m);
+          } else {
+            best1[k] = umin3(best1[k], k0, k1);
+          }
+        }
+      }
+      if (j < tn) {
+        const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
+#pragma unroll
+        for (int k = 0; k < kQPT; ++k) {
+          const uint32_t key = hamming256_key<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j));
+          if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
+          best1[k] = min(best1[k], key);
+        }
+      }
+    } else {
+#pragma unroll 4
+      for (int j = 0; j < tn; ++j) {
+        const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
+#pragma unroll
+        for (int k = 0; k < kQPT; ++k) {
+          const uint32_t d = hamming256<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w);
+          const uint32_t key = pack_nn(d, (uint32_t)(t0 + j));
+          if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
+          best1[k] = min(best1[k], key);
+        }
       }
     }
   }
@@ -80,8 +118,11 @@ void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, i
   static const int variant = getenv("RPE_MATCH_VARIANT") ? atoi(getenv("RPE_MATCH_VARIANT")) : 0;   // tuning knob
   const bool top2 = mode == RPE_MATCH_RATIO;
   dim3 grid(qblocks, n_pairs, top2 ? 1 : 2);
-  auto k = top2 ? (variant == 1 ? k_hamming<true, true> : k_hamming<true, false>)
-                : (variant == 1 ? k_hamming<false, true> : k_hamming<false, false>);
+  // 0: CSA3, 1: CSA4, 2: CSA3 + FMA-pipe keys + paired update, 3: CSA4 + FMA-pipe keys + paired update
+  auto k = top2 ? (variant == 1 ? k_hamming<true, true, false> : variant == 2 ? k_hamming<true, false, true>
+                   : variant == 3 ? k_hamming<true, true, true> : k_hamming<true, false, false>)
+                : (variant == 1 ? k_hamming<false, true, false> : variant == 2 ? k_hamming<false, false, true>
+                   : variant == 3 ? k_hamming<false, true, true> : k_hamming<false, false, false>);
   k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, mb.fwd1, mb.fwd2, mb.bwd1);
   ++*launches;
 }

@@ -9,6 +9,33 @@
 
 namespace rpe {
 
+// ------------------------------------------------------------------ K0: BGR -> gray ingest
+// HBM-bound: 3 bytes in, 1 byte out per pixel.  One thread = 4 pixels = three aligned word loads
+// (12 bytes of interleaved BGR) and one word store into level 0 of the image's pyramid slab.
+__global__ void __launch_bounds__(256)
+k_bgr2gray(const uint8_t* __restrict__ bgr, size_t src_stride, int src_pitch, uint8_t* __restrict__ pyr,
+           size_t pyr_stride, int dst_pitch, int w, int h, int mode) {
+  const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
+  const int y = blockIdx.y * 4 + threadIdx.y;
+  if (y >= h || x4 >= w) return;
+  const uint32_t* p = reinterpret_cast<const uint32_t*>(bgr + blockIdx.z * src_stride + (size_t)y * src_pitch + 3 * x4);
+  const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);   // B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+  const uint32_t o0 = gray_from_bgr(w0 & 0xff, (w0 >> 8) & 0xff, (w0 >> 16) & 0xff, mode);
+  const uint32_t o1 = gray_from_bgr(w0 >> 24, w1 & 0xff, (w1 >> 8) & 0xff, mode);
+  const uint32_t o2 = gray_from_bgr((w1 >> 16) & 0xff, w1 >> 24, w2 & 0xff, mode);
+  const uint32_t o3 = gray_from_bgr((w2 >> 8) & 0xff, (w2 >> 16) & 0xff, w2 >> 24, mode);
+  // columns >= w of the last quad fall into the row padding (pitch = align16(w)): harmless
+  *reinterpret_cast<uint32_t*>(pyr + blockIdx.z * pyr_stride + (size_t)y * dst_pitch + x4) =
+      o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
+}
+
+void launch_bgr2gray(const uint8_t* bgr, size_t src_stride, int src_pitch, uint8_t* pyr, size_t pyr_stride,
+                     int dst_pitch, int w, int h, int n_img, int mode, cudaStream_t s, int* launches) {
+  dim3 grid((w + 255) / 256, (h + 3) / 4, n_img), block(64, 4);
+  k_bgr2gray<<<grid, block, 0, s>>>(bgr, src_stride, src_pitch, pyr, pyr_stride, dst_pitch, w, h, mode);
+  ++*launches;
+}
+
 // ------------------------------------------------------------------ K1: pyramid level l from l-1
 __global__ void __launch_bounds__(256)
 k_resize(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,

@@ -7,6 +7,18 @@
 
 namespace rpe {
 
+// ------------------------------------------------------------------ ingest: BGR -> gray
+// The two gray paths of the reference differ and are matched separately:
+//   mode 0 = cv2.cvtColor(BGR2GRAY) after cv2.imread (src/utils/image_loader.py:23-28):
+//            (3735 B + 19235 G + 9798 R + 2^14) >> 15;
+//   mode 1 = cv2.imread(path, IMREAD_GRAYSCALE) of a colour PNG (src/run_single_pair.py:31-32), where
+//            libpng converts with truncated 15-bit weights: (9797 R + 19234 G + 3737 B) >> 15.
+// Both probed bit-exact against cv2 4.13 (tests/test_oracle_gray.py).
+RPE_HD uint32_t gray_from_bgr(uint32_t b, uint32_t g, uint32_t r, int mode) {
+  return mode == 0 ? (3735u * b + 19235u * g + 9798u * r + 16384u) >> 15
+                   : (3737u * b + 19234u * g + 9797u * r) >> 15;
+}
+
 // ------------------------------------------------------------------ A.1 pyramid (resize)
 // One INTER_LINEAR_EXACT output pixel from host-built per-axis tap tables: ofs = left/top
 // source index, c1 = 8.8 weight of the right/bottom neighbour (c0 = 256 - c1).

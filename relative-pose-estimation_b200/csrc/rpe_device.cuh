@@ -102,6 +102,9 @@ struct RansacParams {
 __host__ __device__ inline uint32_t pack_nn(uint32_t dist, uint32_t idx) { return (dist << 20) | idx; }
 
 // launchers (defined in the kernel .cu files)
+// BGR (interleaved, 4-byte aligned rows) -> level 0 of n_img pyramid slabs; mode: RPE_GRAY_*
+void launch_bgr2gray(const uint8_t* bgr, size_t src_stride, int src_pitch, uint8_t* pyr, size_t pyr_stride,
+                     int dst_pitch, int w, int h, int n_img, int mode, cudaStream_t s, int* launches);
 void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
 void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
 void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);

@@ -58,6 +58,8 @@ class Engine:
         kc, mc = C.c_int32(), C.c_int32()
         L.check(self._lib.rpe_get_capacity(self._h, C.byref(kc), C.byref(mc)), "rpe_get_capacity")
         self.kp_cap, self.match_cap = kc.value, mc.value
+        self._fmt = (1, L.GRAY_CVTCOLOR)
+        self.gray_mode = L.GRAY_CVTCOLOR      # arithmetic used when BGR images are passed (see set_input_format)
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -77,6 +79,38 @@ class Engine:
     def set_pipeline(self, chunk_pairs: int, n_streams: int):
         """Sub-batch pipeline of the batch calls (see include/rpe.h: rpe_set_pipeline)."""
         L.check(self._lib.rpe_set_pipeline(self._h, int(chunk_pairs), int(n_streams)), "rpe_set_pipeline")
+
+    def set_input_format(self, channels: int, gray_mode: int | None = None):
+        """1 = gray images (default); 3 = interleaved BGR as cv2.imread returns it, converted on the GPU with
+        cv2.cvtColor's arithmetic (GRAY_CVTCOLOR) or IMREAD_GRAYSCALE's for PNG (GRAY_IMREAD_PNG)."""
+        fmt = (int(channels), self.gray_mode if gray_mode is None else int(gray_mode))
+        if fmt != self._fmt:
+            L.check(self._lib.rpe_set_input_format(self._h, fmt[0], fmt[1]), "rpe_set_input_format")
+            self._fmt = fmt
+
+    def _prep(self, imgs):
+        """-> (list of C-contiguous uint8 arrays, H, W, channels); sets the input format to match."""
+        arrs = [np.ascontiguousarray(i, dtype=np.uint8) for i in imgs]
+        a0 = arrs[0]
+        if a0.ndim == 3 and a0.shape[2] == 3:
+            ch = 3
+        elif a0.ndim == 2:
+            ch = 1
+        else:
+            raise ValueError("images must be HxW uint8 gray or HxWx3 uint8 BGR")
+        for a in arrs:
+            if a.shape != a0.shape:
+                raise ValueError("all images of a batch must have one size and format")
+        self.set_input_format(ch)
+        return arrs, a0.shape[0], a0.shape[1], ch
+
+    def bgr_to_gray(self, bgr, gray_mode: int = L.GRAY_CVTCOLOR):
+        """Stage entry: the GPU gray conversion alone (rpe_bgr_to_gray)."""
+        bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+        H, W, _ = bgr.shape
+        out = np.zeros((H, W), np.uint8)
+        L.check(self._lib.rpe_bgr_to_gray(self._h, _ptr(bgr), H, W, 3 * W, int(gray_mode), _ptr(out)), "rpe_bgr_to_gray")
+        return out
 
     def set_profiling(self, on: bool):
         L.check(self._lib.rpe_set_profiling(self._h, int(on)), "rpe_set_profiling")
@@ -98,17 +132,13 @@ class Engine:
         B = len(imgs1)
         if B != len(imgs2) or B == 0:
             raise ValueError("imgs1 and imgs2 must be non-empty and of equal length")
-        a1 = [np.ascontiguousarray(i, dtype=np.uint8) for i in imgs1]
-        a2 = [np.ascontiguousarray(i, dtype=np.uint8) for i in imgs2]
-        H, W = a1[0].shape
-        for a in a1 + a2:
-            if a.shape != (H, W):
-                raise ValueError("all images of a batch must be 2-D uint8 of one size")
+        arrs, H, W, ch = self._prep(list(imgs1) + list(imgs2))
+        a1, a2 = arrs[:B], arrs[B:]
         p1 = (C.c_void_p * B)(*[a.ctypes.data for a in a1])
         p2 = (C.c_void_p * B)(*[a.ctypes.data for a in a2])
         K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
         R, t, e, st, info = self._outputs(B)
-        L.check(self._lib.rpe_estimate_batch(self._h, p1, p2, B, H, W, W, _ptr(K), _ptr(R), _ptr(t), _ptr(e),
+        L.check(self._lib.rpe_estimate_batch(self._h, p1, p2, B, H, W, W * ch, _ptr(K), _ptr(R), _ptr(t), _ptr(e),
                                              _ptr(st), _ptr(info)), "rpe_estimate_batch")
         return {"R": R, "t": t, "euler": e, "status": st, "info": info}
 
@@ -116,7 +146,8 @@ class Engine:
         """frames: (2B, H, W) uint8 host array, view 1 of pair i at 2i and view 2 at 2i+1 (one
         H2D copy when the array is contiguous and W is a multiple of 16; pin it for async copies)."""
         B = frames.shape[0] // 2
-        H, W = frames.shape[1:]
+        H, W = frames.shape[1:3]
+        self.set_input_format(3 if frames.ndim == 4 else 1)
         base = frames.ctypes.data
         step = frames.strides[0]
         p1 = (C.c_void_p * B)(*[base + (2 * i) * step for i in range(B)])
@@ -131,7 +162,8 @@ class Engine:
         """Asynchronous estimate_batch_interleaved (rpe_submit_batch): returns at once; ``wait()``
         returns the result dict.  ``frames`` must stay alive (and unchanged) until then."""
         B = frames.shape[0] // 2
-        H, W = frames.shape[1:]
+        H, W = frames.shape[1:3]
+        self.set_input_format(3 if frames.ndim == 4 else 1)
         base = frames.ctypes.data
         step = frames.strides[0]
         p1 = (C.c_void_p * B)(*[base + (2 * i) * step for i in range(B)])
@@ -170,18 +202,16 @@ class Engine:
 
     # ------------------------------------------------------------------ consecutive frames (feature cache)
     def _frame_ptrs(self, frames):
-        if isinstance(frames, np.ndarray) and frames.ndim == 3 and frames.dtype == np.uint8 and frames.strides[2] == 1:
-            F, H, W = frames.shape
+        if (isinstance(frames, np.ndarray) and frames.dtype == np.uint8 and frames.ndim in (3, 4)
+                and frames[0].flags.c_contiguous and (frames.ndim == 3 or frames.shape[3] == 3)):
+            F, H, W = frames.shape[:3]
+            self.set_input_format(3 if frames.ndim == 4 else 1)
             base, step = frames.ctypes.data, frames.strides[0]
             return (C.c_void_p * F)(*[base + i * step for i in range(F)]), F, H, W, frames.strides[1], frames
-        arrs = [np.ascontiguousarray(f, dtype=np.uint8) for f in frames]
-        if len(arrs) < 2:
+        if len(frames) < 2:
             raise ValueError("a sequence needs at least 2 frames")
-        H, W = arrs[0].shape
-        for a in arrs:
-            if a.shape != (H, W):
-                raise ValueError("all frames of a sequence must be 2-D uint8 of one size")
-        return (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs]), len(arrs), H, W, W, arrs
+        arrs, H, W, ch = self._prep(frames)
+        return (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs]), len(arrs), H, W, W * ch, arrs
 
     def estimate_sequence(self, frames, K):
         """frames: (F, H, W) uint8 host array or list of F gray images -> results of the F-1 consecutive

@@ -71,9 +71,11 @@ class PoseEstimator:
 
     @staticmethod
     def _gray(img):
+        """HxW uint8 gray (the reference's input), or HxWx3 uint8 BGR as cv2.imread returns it: the batch and
+        sequence calls then convert on the GPU with cv2.cvtColor's arithmetic (load_image, image_loader.py:28)."""
         a = np.asarray(img)
-        if a.ndim != 2 or a.dtype != np.uint8:
-            raise ValueError("images must be 2-D uint8 grayscale arrays")
+        if a.dtype != np.uint8 or not (a.ndim == 2 or (a.ndim == 3 and a.shape[2] == 3)):
+            raise ValueError("images must be uint8 HxW grayscale (or HxWx3 BGR) arrays")
         return a
 
     # ------------------------------------------------------------------ reference API
@@ -81,7 +83,7 @@ class PoseEstimator:
         """-> (R (B,3,3) f64, t (B,3,1) f64, status (B,) i32).  Never raises per pair."""
         imgs1 = [self._gray(i) for i in imgs1]
         imgs2 = [self._gray(i) for i in imgs2]
-        H, W = imgs1[0].shape
+        H, W = imgs1[0].shape[:2]
         out = self._ensure_engine(W, H, len(imgs1)).estimate_batch(imgs1, imgs2, self.K)
         self.last = out
         return out["R"], out["t"], out["status"]
@@ -92,7 +94,7 @@ class PoseEstimator:
         results are bit-identical to ``estimate_batch(frames[:-1], frames[1:])``.
         -> (R (F-1,3,3), t (F-1,3,1), status (F-1,))."""
         frames = [self._gray(f) for f in frames]
-        H, W = frames[0].shape
+        H, W = frames[0].shape[:2]
         out = self._ensure_engine(W, H, len(frames) - 1).estimate_sequence(frames, self.K)
         self.last = out
         return out["R"], out["t"], out["status"]

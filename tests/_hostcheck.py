@@ -35,6 +35,13 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
+def gray(bgr, mode):
+    bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+    out = np.zeros(bgr.shape[:-1], np.uint8)
+    lib().hc_gray(_p(bgr), out.size, int(mode), _p(out))
+    return out
+
+
 def resize(src, dw, dh, xo, xc, yo, yc):
     src = np.ascontiguousarray(src)
     out = np.zeros((dh, dw), np.uint8)

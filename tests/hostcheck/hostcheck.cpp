@@ -22,6 +22,9 @@ void hc_hamming(const uint32_t* q, int nq, const uint32_t* t, int nt, int mode, 
     }
 }
 
+void hc_gray(const uint8_t* bgr, int n, int mode, uint8_t* out) {
+  for (int i = 0; i < n; ++i) out[i] = (uint8_t)gray_from_bgr(bgr[3 * i], bgr[3 * i + 1], bgr[3 * i + 2], mode);
+}
 void hc_resize(const uint8_t* src, int sw, int sh, uint8_t* dst, int dw, int dh, const int* xo,
                const int* xc, const int* yo, const int* yc) {
   for (int y = 0; y < dh; ++y)

@@ -106,8 +106,11 @@ def test_constructor_contract():
         rpe_b200.PoseEstimator(K, norm_type="L2")
     e = rpe_b200.PoseEstimator(K, "orb", "hamming", 300, 2000, True)
     assert (e.max_matches, e.nfeatures, e.use_vp_refinement) == (300, 2000, True)
-    with pytest.raises(ValueError, match="2-D uint8"):
-        e._gray(np.zeros((4, 4, 3), np.uint8))
+    with pytest.raises(ValueError, match="uint8 HxW grayscale"):
+        e._gray(np.zeros((4, 4, 4), np.uint8))
+    with pytest.raises(ValueError, match="uint8 HxW grayscale"):
+        e._gray(np.zeros((4, 4), np.float32))
+    assert e._gray(np.zeros((4, 4, 3), np.uint8)).shape == (4, 4, 3)      # BGR is converted on the GPU
     with pytest.raises(ValueError):
         rpe_b200.EngineConfig(match_mode="flann").to_c()
 

@@ -328,3 +328,41 @@ def test_sequence_equals_pair_batch(engine):
         engine.estimate_sequence([frames[0]] * 6, K)
     with pytest.raises(Exception):
         engine.estimate_sequence([frames[0]], K)
+
+
+def test_bgr_ingest_bit_exact_and_equal_to_host_gray(engine):
+    """k_bgr2gray == cv2.cvtColor(BGR2GRAY) / IMREAD_GRAYSCALE(PNG) bit for bit (widths that are and are not
+    multiples of 4 / 16), and BGR frames through the batch / sequence calls give exactly the results of the
+    host-converted gray frames (load_image, image_loader.py:23-28)."""
+    from rpe_b200 import _lib as L
+    from oracle.gray import bgr_to_gray
+    rng = np.random.default_rng(5)
+    for (H, W) in [(48, 64), (33, 61), (50, 130), (480, 640), (37, 645)]:
+        img = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+        assert np.array_equal(engine.bgr_to_gray(img, L.GRAY_CVTCOLOR), cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)), (H, W)
+        ok, buf = cv2.imencode(".png", img)
+        assert np.array_equal(engine.bgr_to_gray(img, L.GRAY_IMREAD_PNG), cv2.imdecode(buf, cv2.IMREAD_GRAYSCALE))
+        assert np.array_equal(engine.bgr_to_gray(img, L.GRAY_IMREAD_PNG), bgr_to_gray(img, 1))
+    # colourised fixtures: gray frame g -> BGR with distinct channels, so the conversion matters
+    frames = []
+    for n in ("sim_000000.png", "sim_000015.png", "sim_000030.png"):
+        g = load_gray(n)
+        frames.append(np.stack([g, np.roll(g, 1, 1) // 2 + 60, 255 - g // 2], axis=2))
+    grays = [cv2.cvtColor(f, cv2.COLOR_BGR2GRAY) for f in frames]
+    K = default_K()
+    engine.set_pipeline(32, 4)
+    want = engine.estimate_sequence(grays, K)
+    assert (want["status"] == 0).all()
+    want_desc = engine.keypoints(1, 1)["desc"]
+    for src in (frames, np.ascontiguousarray(np.stack(frames))):
+        got = engine.estimate_sequence(src, K)
+        for k in ("R", "t", "euler", "status", "info"):
+            assert np.array_equal(got[k], want[k]), k
+        assert np.array_equal(engine.keypoints(1, 1)["desc"], want_desc)
+        assert np.array_equal(engine.get_stage(0, 1, L.STAGE_PYRAMID_LEVEL, 0).reshape(480, 640), grays[1])
+    got = engine.estimate_batch(frames[:-1], frames[1:], K)
+    for k in ("R", "t", "euler", "status", "info"):
+        assert np.array_equal(got[k], want[k]), k
+    # back to gray input on the same handle
+    again = engine.estimate_sequence(grays, K)
+    assert np.array_equal(again["R"], want["R"])
