@@ -3,8 +3,10 @@
 // max_matches cut (src/core/pose_estimator.py:131, :144-151) and, for BASELINE configs 3-5,
 // knnMatch(k=2) + ratio test.
 //
-// k_hamming: bound by the XU pipe (POPC, 16 lanes/clk/SM), not by HBM; carry-save adders on the
-// ALU pipe (match_math.cuh) cut the POPCs per 256-bit distance from 8 to 5.  Each thread keeps kQPT query
+// k_hamming: bound by the XU pipe (POPC, 16 lanes/clk/SM) and the ALU pipe (LOP3, 64 lanes/clk/SM) together,
+// not by HBM; carry-save adders on the ALU pipe (match_math.cuh) cut the POPCs per 256-bit distance from 8
+// to 5 or 4, the key arithmetic runs on the FMA pipe (IMAD), and the default variant alternates the 5- and
+// 4-POPC forms so that both pipes sit near 18/64 clk per distance.  Each thread keeps kQPT query
 // descriptors (8 x u32 each) in registers, train descriptors stream through a shared-memory
 // tile read with 128-bit broadcast loads; nearest / second nearest are tracked as packed
 // (dist << 20 | index) keys, which reproduces OpenCV's tie rule (lowest index) for free.
@@ -20,15 +22,15 @@ constexpr int kQPB = kMatchThreads * kQPT;    // queries per block
 constexpr int kTrainTile = 128;               // train descriptors per shared-memory tile
 
 __device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) {
-  uint32_t d;
-  asm("min.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));   // VIMNMX3 on sm_100
-  return d;
+  return __vimin3_u32(a, b, c);   // VIMNMX3 on sm_100
 }
 
-// kFma: keys built with multiply-adds (FMA pipe) and two train descriptors folded per top-2 update
-template <bool kTop2, bool kCsa4, bool kFma>
+// kFma: keys built with multiply-adds (FMA pipe) and two train descriptors folded per top-2 update;
+// kMix (with kFma): the even train descriptor of each pair uses three carry-save adders + five POPCs, the odd
+// one four adders + four POPCs, which balances the ALU pipe (LOP3) against the XU pipe (POPC)
+template <bool kTop2, bool kCsa4, bool kFma, bool kMix = false>
 __global__ void __launch_bounds__(kMatchThreads)
-k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride, int pstep,
+k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride, int pstep, uint32_t m20,
           uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
   __shared__ uint4 s_train[kTrainTile * 2];
   const int pair = blockIdx.y;
@@ -67,8 +69,8 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
         const uint4 a0 = s_train[2 * j], b0 = s_train[2 * j + 1], a1 = s_train[2 * j + 2], b1 = s_train[2 * j + 3];
 #pragma unroll
         for (int k = 0; k < kQPT; ++k) {
-          const uint32_t k0 = hamming256_key<kCsa4>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j));
-          const uint32_t k1 = hamming256_key<kCsa4>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1));
+          const uint32_t k0 = hamming256_key<kCsa4 && !kMix>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20);
+          const uint32_t k1 = hamming256_key<kCsa4 || kMix>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20);
           if (kTop2) {
             const uint32_t m = min(k0, k1), M = max(k0, k1);
             best2[k] = umin3(max(best1[k], m), best2[k], M);
@@ -82,7 +84,7 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
         const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
 #pragma unroll
         for (int k = 0; k < kQPT; ++k) {
-          const uint32_t key = hamming256_key<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j));
+          const uint32_t key = hamming256_key<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20);
           if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
           best1[k] = min(best1[k], key);
         }
@@ -115,15 +117,18 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
 void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int pstep, int mode,
                   cudaStream_t s, int* launches) {
   const int qblocks = (kp_stride + kQPB - 1) / kQPB;
-  static const int variant = getenv("RPE_MATCH_VARIANT") ? atoi(getenv("RPE_MATCH_VARIANT")) : 0;   // tuning knob
+  static const int variant = getenv("RPE_MATCH_VARIANT") ? atoi(getenv("RPE_MATCH_VARIANT")) : 4;   // tuning knob (B200: 4.14 / 4.25 / 3.96 / 3.95 / 3.84 ms for 0..4)
   const bool top2 = mode == RPE_MATCH_RATIO;
   dim3 grid(qblocks, n_pairs, top2 ? 1 : 2);
-  // 0: CSA3, 1: CSA4, 2: CSA3 + FMA-pipe keys + paired update, 3: CSA4 + FMA-pipe keys + paired update
+  // 0: CSA3, 1: CSA4, 2: CSA3 + FMA-pipe keys + paired update, 3: CSA4 + FMA-pipe keys + paired update,
+  // 4: as 2 / 3 with CSA3 and CSA4 alternating
   auto k = top2 ? (variant == 1 ? k_hamming<true, true, false> : variant == 2 ? k_hamming<true, false, true>
-                   : variant == 3 ? k_hamming<true, true, true> : k_hamming<true, false, false>)
+                   : variant == 3 ? k_hamming<true, true, true> : variant == 4 ? k_hamming<true, false, true, true>
+                   : k_hamming<true, false, false>)
                 : (variant == 1 ? k_hamming<false, true, false> : variant == 2 ? k_hamming<false, false, true>
-                   : variant == 3 ? k_hamming<false, true, true> : k_hamming<false, false, false>);
-  k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, mb.fwd1, mb.fwd2, mb.bwd1);
+                   : variant == 3 ? k_hamming<false, true, true> : variant == 4 ? k_hamming<false, false, true, true>
+                   : k_hamming<false, false, false>);
+  k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, mb.fwd1, mb.fwd2, mb.bwd1);
   ++*launches;
 }
 

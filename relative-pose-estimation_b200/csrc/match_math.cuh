@@ -58,22 +58,24 @@ RPE_HD uint32_t hamming256(const uint32_t q[8], uint32_t t0, uint32_t t1, uint32
 // network already fills (ncu: pipe_alu 73 %, pipe_xu 77 % with the plain form).  idx < 2^20.
 template <bool kCsa4>
 RPE_HD uint32_t hamming256_key(const uint32_t q[8], uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, uint32_t t4,
-                               uint32_t t5, uint32_t t6, uint32_t t7, uint32_t idx) {
+                               uint32_t t5, uint32_t t6, uint32_t t7, uint32_t idx, uint32_t m20) {
+  // m20 = 2^20 passed at run time: a literal would be strength-reduced to LEA / SHF on the ALU pipe
   const uint32_t x0 = q[0] ^ t0, x1 = q[1] ^ t1, x2 = q[2] ^ t2, x3 = q[3] ^ t3;
   const uint32_t x4 = q[4] ^ t4, x5 = q[5] ^ t5, x6 = q[6] ^ t6, x7 = q[7] ^ t7;
   const uint32_t s0 = xor3(x0, x1, x2), c0 = maj3(x0, x1, x2);
   const uint32_t s1 = xor3(x3, x4, x5), c1 = maj3(x3, x4, x5);
   const uint32_t s2 = xor3(s0, s1, x6), c2 = maj3(s0, s1, x6);
-  uint32_t key = popc32(s2) * 0x100000u + idx;
-  key = popc32(x7) * 0x100000u + key;
+  const uint32_t m21 = 2u * m20, m22 = 4u * m20;
+  uint32_t key = popc32(s2) * m20 + idx;
+  key = popc32(x7) * m20 + key;
   if (kCsa4) {
     const uint32_t s3 = xor3(c0, c1, c2), c3 = maj3(c0, c1, c2);
-    key = popc32(s3) * 0x200000u + key;
-    key = popc32(c3) * 0x400000u + key;
+    key = popc32(s3) * m21 + key;
+    key = popc32(c3) * m22 + key;
   } else {
-    key = popc32(c0) * 0x200000u + key;
-    key = popc32(c1) * 0x200000u + key;
-    key = popc32(c2) * 0x200000u + key;
+    key = popc32(c0) * m21 + key;
+    key = popc32(c1) * m21 + key;
+    key = popc32(c2) * m21 + key;
   }
   return key;
 }

@@ -18,6 +18,8 @@ void hc_hamming(const uint32_t* q, int nq, const uint32_t* t, int nt, int mode, 
       const uint32_t* b = t + 8 * j;
       out[i * nt + j] = mode == 0   ? (int)hamming256<false>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7])
                         : mode == 1 ? (int)hamming256<true>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7])
+                        : mode == 3 ? (int)(hamming256_key<false>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7], 0u, 1u << 20) >> 20)
+                        : mode == 4 ? (int)(hamming256_key<true>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7], 0u, 1u << 20) >> 20)
                                     : (int)hamming256_plain(a, b);
     }
 }
