@@ -43,7 +43,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=128, help="pairs per GPU per step")
     ap.add_argument("--cpu-pairs", type=int, default=24, help="pairs in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--inflight", type=int, default=2, help="engine handles used alternately (batches in flight)")
+    ap.add_argument("--inflight", type=int, default=1, help="engine handles used alternately")
+    ap.add_argument("--depth", type=int, default=2, help="batches pending per handle (rpe_submit_* / rpe_wait_batch; max 2)")
     ap.add_argument("--chunk", type=int, default=32, help="pairs per pipeline chunk (rpe_set_pipeline)")
     ap.add_argument("--streams", type=int, default=1, help="pipeline streams per handle (rpe_set_pipeline); 1 = no chunking")
     ap.add_argument("--no-stream", action="store_true", help="skip the extra consecutive-frame (config 5) pass")
@@ -207,8 +208,8 @@ def run_b200(args):
     ecfg = rpe_b200.EngineConfig(max_width=W, max_height=H, max_pairs=B, nfeatures=CFG["nfeatures"],
                                  nlevels=CFG["nlevels"], match_mode=CFG["match_mode"], ratio=CFG["ratio"],
                                  max_matches=CFG["max_matches"], ransac_max_iters=CFG["ransac_max_iters"])
-    # `inflight` handles used alternately: batch n+1 is submitted before the results of batch n are
-    # waited for, so its upload / kernel heads overlap the tail of batch n (rpe_submit_batch / rpe_wait_batch)
+    # batch n+1 is submitted before the results of batch n are waited for (rpe_submit_* / rpe_wait_batch, two
+    # pending per handle): its upload and ORB / matcher kernels run under the RANSAC / pose tail of batch n
     engines = [rpe_b200.Engine(ecfg, device=local) for _ in range(max(1, args.inflight))]
     eng = engines[0]
     stream = torch.cuda.Stream()
@@ -226,9 +227,10 @@ def run_b200(args):
     def run_steps(n, submit):
         """n steps over the handles, at most len(engines) batches in flight; returns launches, last result"""
         launches, out, q = 0, None, []
+        cap = len(engines) * max(1, min(2, args.depth))
         for i in range(n):
             e = engines[i % len(engines)]
-            if len(q) == len(engines):
+            if len(q) == cap:
                 d = q.pop(0)
                 out = d.wait()
                 launches += sum(d.stage_times()[1].values())
@@ -378,8 +380,8 @@ def run_b200(args):
                       "pairs_per_gpu_per_step": B, "image_bytes_per_step": int(2 * B * H * W),
                       "l2_policy": "inputs larger than L2 (236 MB of frames + 1.2 GB of pyramids per step)",
                       "parallelism": f"{world} independent shards, no collective",
-                      "pipeline": {"handles_in_flight": len(engines), "chunk_pairs": args.chunk,
-                                   "streams": args.streams},
+                      "pipeline": {"handles": len(engines), "batches_pending_per_handle": max(1, min(2, args.depth)),
+                                   "chunk_pairs": args.chunk, "streams": args.streams},
                       "mean_keypoints_per_image": nkp, "ok_fraction": ok_frac},
            "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": int(2 * B * H * W + 72),
                    "d2h_bytes_per_step": int(B * (15 * 8 + 3 * 4)), "ms_per_step": ms_e2e / args.steps},

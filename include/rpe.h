@@ -83,13 +83,13 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out);
 void rpe_destroy(rpe_handle* h);
 /* run all work of this handle on an existing CUDA stream (cudaStream_t); NULL = own stream */
 int rpe_set_stream(rpe_handle* h, void* cuda_stream);
-/* sub-batch pipeline of the HOST-buffer batch calls: pairs are processed in chunks of `chunk_pairs`
- * over internal streams forked from / joined into the handle's stream.  n_streams = 1: no pipeline
- * (one chunk on the handle's stream); n >= 2: one copy stream + (n - 1) compute streams used
- * round-robin, so the image upload of chunk c+1 and the kernel tails of chunk c overlap.  Default:
- * 32 pairs x 4 streams (best for one blocking call at a time; measured 6995 vs 6392 pairs/s).  With
- * two handles in flight (rpe_submit_batch) use n_streams = 1: batches already overlap each other.
- * Device-resident inputs are never chunked.  Results do not depend on these settings. */
+/* Scheduling of one handle: the dense kernels (ORB, matcher) run in order on the handle's stream; image
+ * uploads run ahead on an internal copy stream, and the latency-bound geometry tail (RANSAC, recoverPose,
+ * result D2H) on an internal high-priority stream, so they overlap the dense kernels of the next chunk or
+ * of the next submitted batch.  rpe_set_pipeline: n_streams = 1: a batch is one chunk (right when batches
+ * are submitted back to back: they overlap each other); n_streams >= 2: a batch is cut into chunks of
+ * `chunk_pairs` pairs, so that inside ONE blocking call the upload of chunk c+1 and the tail of chunk c
+ * hide under the dense kernels.  Default: 32 pairs, chunked.  Results do not depend on these settings. */
 int rpe_set_pipeline(rpe_handle* h, int32_t chunk_pairs, int32_t n_streams);
 /* pixel format of the images given to the batch / sequence calls (host or device): channels = 1 (default):
  * H x W uint8 gray; channels = 3: H x W x 3 interleaved BGR as cv2.imread returns it, converted to gray on the
@@ -112,9 +112,10 @@ int rpe_estimate_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t*
 /* asynchronous form of rpe_estimate_batch: rpe_submit_batch enqueues the uploads and kernels and
  * returns without waiting; rpe_wait_batch blocks until the results of the submitted batch are in the
  * output pointers given at submit time.  The images and the output arrays must stay valid until
- * rpe_wait_batch returns; one batch may be pending per handle (other calls on the handle fail with
- * RPE_ERR_INVALID meanwhile).  Two handles used alternately overlap the upload of one batch with the
- * kernels of the other (see bench.py e2e). */
+ * rpe_wait_batch returns.  TWO batches may be pending per handle (a third submit, and every other call on
+ * the handle, fails with RPE_ERR_INVALID meanwhile); rpe_wait_batch waits for the OLDEST one.  Submitting
+ * batch n+1 before waiting for batch n keeps the GPU full: upload and ORB / matcher kernels of n+1 run
+ * under the RANSAC / recoverPose tail of n (see bench.py). */
 int rpe_submit_batch(rpe_handle* h, const uint8_t* const* img1, const uint8_t* const* img2,
                      int32_t B, int32_t H, int32_t W, size_t pitch, const double K[9],
                      double* R, double* t, double* euler, int32_t* status, int32_t* info);

@@ -55,24 +55,32 @@ struct rpe_handle {
   int device = 0;
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
-  // sub-batch pipeline: chunks of chunk_pairs pairs round-robin over n_workers streams, so that the
-  // H2D copy and the latency-bound tail kernels (select, RANSAC, pose) of one chunk overlap the
-  // dense kernels of the next
+  // Three-stream software pipeline, depth two batches.  The dense kernels (ORB, matcher) of every chunk
+  // of every batch run in order on `stream`; image uploads run ahead on s_copy (as soon as the ORB of
+  // the previous batch has released the pyramid slabs); the latency-bound geometry tail (RANSAC,
+  // recoverPose, D2H; one CTA per pair) runs on the high-priority s_tail under the dense kernels of the
+  // next chunk / batch.  Tail buffers exist twice (set = seq & 1).
   static constexpr int kMaxWorkers = 4;
-  cudaStream_t wstream[kMaxWorkers] = {};
-  // outputs of a submitted, not yet waited-for batch (rpe_submit_batch / rpe_wait_batch)
-  struct Pending { bool active = false; int B = 0; double* R = nullptr; double* t = nullptr; double* euler = nullptr;
-                   int32_t* status = nullptr; int32_t* info = nullptr; } pending;
+  static constexpr int kDepth = 2;
+  cudaStream_t s_copy = nullptr, s_tail = nullptr;
+  // outputs of submitted, not yet waited-for batches (rpe_submit_* / rpe_wait_batch), oldest first
+  struct Pending { int B = 0; int set = 0; double* R = nullptr; double* t = nullptr; double* euler = nullptr;
+                   int32_t* status = nullptr; int32_t* info = nullptr; } pend[kDepth];
+  int n_pending = 0;
+  unsigned long long seq = 0;          // batches enqueued so far
   static constexpr int kChunkEvents = 64;
-  cudaEvent_t ev_fork = nullptr, ev_done[kMaxWorkers] = {}, ev_chunk[kChunkEvents] = {};
+  cudaEvent_t ev_up[kChunkEvents] = {}, ev_dense[kChunkEvents] = {};
+  cudaEvent_t ev_done_call[kDepth] = {};
+  uint8_t* pyr2[kDepth] = {};          // the pyramid slabs exist twice too: batch n+1 is uploaded while batch n is in ORB
   int chunk_pairs = 32, n_workers = 4;
   int NI = 0, NP = 0;
   int kp_stride = 0, cand_stride = 0, mcap = 0, sort_cap_orb = 0, sort_cap_match = 0;
   size_t pyr_stride = 0;
   OrbBuffers ob{};
-  MatchBuffers mb{};
-  GeomBuffers gb{};
-  double* dK = nullptr;
+  MatchBuffers mb[kDepth] = {};
+  GeomBuffers gb[kDepth] = {};
+  double* dK[kDepth] = {};
+  int last_set = 0;          // tail-buffer set of the last completed batch / stage call (rpe_get_stage)
   std::vector<void*> allocs;
   std::map<std::pair<int, int>, Geometry> geoms;
   const Geometry* last_geom = nullptr;
@@ -83,9 +91,9 @@ struct rpe_handle {
   size_t bgr_stage_stride = 0, bgr_stage_imgs = 0;
   int last_pstep = 2;       // image slots of pair p in the last batch: pstep*p, pstep*p + 1
   // pinned host staging for results: R(9) t(3) euler(3) doubles, status + 4 info ints, K
-  double* h_out_d = nullptr;
-  int32_t* h_out_i = nullptr;
-  double* h_K = nullptr;
+  double* h_out_d[kDepth] = {};
+  int32_t* h_out_i[kDepth] = {};   // status | num_matches | pose count | rinfo (4) per pair
+  double* h_K[kDepth] = {};
   // profiling
   bool profiling = false;
   cudaEvent_t ev[RPE_T_COUNT + 1] = {};
@@ -276,7 +284,8 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out) {
   int rc = RPE_OK;
   auto A = [&](int r) { if (rc == RPE_OK) rc = r; };
   const size_t NI = h->NI, NP = h->NP, L = cfg->nlevels, KS = h->kp_stride, CS = h->cand_stride, MC = h->mcap;
-  A(dalloc(h, &h->ob.pyr, NI * h->pyr_stride));
+  for (int k = 0; k < rpe_handle::kDepth; ++k) A(dalloc(h, &h->pyr2[k], NI * h->pyr_stride));
+  h->ob.pyr = h->pyr2[0];
   A(dalloc(h, &h->ob.blur, NI * h->pyr_stride));
   A(dalloc(h, &h->ob.cand_key, NI * CS));
   // cand_cnt, hist and img_flags are cleared with one memset per batch: keep them contiguous
@@ -292,30 +301,41 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out) {
   A(dalloc(h, &h->ob.kp_angle, NI * KS)); A(dalloc(h, &h->ob.kp_resp, NI * KS)); A(dalloc(h, &h->ob.kp_oct, NI * KS));
   A(dalloc(h, &h->ob.desc, NI * KS * 32));
   A(dalloc(h, &h->ob.kp_n, NI));
-  A(dalloc(h, &h->mb.fwd1, NP * KS)); A(dalloc(h, &h->mb.fwd2, NP * KS)); A(dalloc(h, &h->mb.bwd1, NP * KS));
-  A(dalloc(h, &h->mb.m_q, NP * MC)); A(dalloc(h, &h->mb.m_t, NP * MC)); A(dalloc(h, &h->mb.m_d, NP * MC));
-  A(dalloc(h, &h->mb.m_n, NP));
-  A(dalloc(h, &h->mb.pts1, NP * MC * 2)); A(dalloc(h, &h->mb.pts2, NP * MC * 2));
-  A(dalloc(h, &h->gb.npts, NP * MC * 4));
-  A(dalloc(h, &h->gb.E, NP * 9));
-  A(dalloc(h, &h->gb.rmask, NP * MC)); A(dalloc(h, &h->gb.pmask, NP * MC));
-  A(dalloc(h, &h->gb.rinfo, NP * 4));
-  A(dalloc(h, &h->gb.R, NP * 9)); A(dalloc(h, &h->gb.t, NP * 3)); A(dalloc(h, &h->gb.euler, NP * 3));
-  A(dalloc(h, &h->gb.pose_cnt, NP)); A(dalloc(h, &h->gb.status, NP));
-  A(dalloc(h, &h->dK, 9));
+  A(dalloc(h, &h->mb[0].fwd1, NP * KS)); A(dalloc(h, &h->mb[0].fwd2, NP * KS)); A(dalloc(h, &h->mb[0].bwd1, NP * KS));
+  for (int k = 0; k < rpe_handle::kDepth; ++k) {
+    MatchBuffers& mb = h->mb[k];
+    GeomBuffers& gb = h->gb[k];
+    mb.fwd1 = h->mb[0].fwd1; mb.fwd2 = h->mb[0].fwd2; mb.bwd1 = h->mb[0].bwd1;   // dense-stream only: one copy
+    A(dalloc(h, &mb.m_q, NP * MC)); A(dalloc(h, &mb.m_t, NP * MC)); A(dalloc(h, &mb.m_d, NP * MC));
+    A(dalloc(h, &mb.m_n, NP)); A(dalloc(h, &mb.pstat, NP));
+    A(dalloc(h, &mb.pts1, NP * MC * 2)); A(dalloc(h, &mb.pts2, NP * MC * 2));
+    A(dalloc(h, &gb.npts, NP * MC * 4));
+    A(dalloc(h, &gb.E, NP * 9));
+    A(dalloc(h, &gb.rmask, NP * MC)); A(dalloc(h, &gb.pmask, NP * MC));
+    A(dalloc(h, &gb.rinfo, NP * 4));
+    A(dalloc(h, &gb.R, NP * 9)); A(dalloc(h, &gb.t, NP * 3)); A(dalloc(h, &gb.euler, NP * 3));
+    A(dalloc(h, &gb.pose_cnt, NP)); A(dalloc(h, &gb.status, NP));
+    A(dalloc(h, &h->dK[k], 9));
+  }
   if (rc == RPE_OK && cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaStreamCreate failed");
   h->stream = h->own_stream;
-  for (int i = 0; i < rpe_handle::kMaxWorkers && rc == RPE_OK; ++i) {
-    if (cudaStreamCreateWithFlags(&h->wstream[i], cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming) != cudaSuccess)
-      rc = fail(RPE_ERR_CUDA, "worker stream creation failed");
+  if (rc == RPE_OK) {
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&h->s_tail, cudaStreamNonBlocking, prio_hi) != cudaSuccess)
+      rc = fail(RPE_ERR_CUDA, "pipeline stream creation failed");
   }
-  if (rc == RPE_OK && cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
   for (int i = 0; i < rpe_handle::kChunkEvents && rc == RPE_OK; ++i)
-    if (cudaEventCreateWithFlags(&h->ev_chunk[i], cudaEventDisableTiming) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
-  if (rc == RPE_OK && cudaMallocHost((void**)&h->h_out_d, NP * 15 * sizeof(double)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
-  if (rc == RPE_OK && cudaMallocHost((void**)&h->h_out_i, NP * 5 * sizeof(int32_t)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
-  if (rc == RPE_OK && cudaMallocHost((void**)&h->h_K, 9 * sizeof(double)) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
+    if (cudaEventCreateWithFlags(&h->ev_up[i], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_dense[i], cudaEventDisableTiming) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
+  for (int k = 0; k < rpe_handle::kDepth && rc == RPE_OK; ++k) {
+    if (cudaEventCreateWithFlags(&h->ev_done_call[k], cudaEventDisableTiming) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
+    if (rc == RPE_OK && (cudaMallocHost((void**)&h->h_out_d[k], NP * 15 * sizeof(double)) != cudaSuccess ||
+                         cudaMallocHost((void**)&h->h_out_i[k], NP * 7 * sizeof(int32_t)) != cudaSuccess ||
+                         cudaMallocHost((void**)&h->h_K[k], 9 * sizeof(double)) != cudaSuccess))
+      rc = fail(RPE_ERR_CUDA, "cudaMallocHost failed");
+  }
   if (rc == RPE_OK) {
     for (int i = 0; i <= RPE_T_COUNT; ++i)
       if (cudaEventCreate(&h->ev[i]) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
@@ -338,23 +358,27 @@ void rpe_destroy(rpe_handle* h) {
   for (void* p : h->allocs) cudaFree(p);
   for (auto& kv : h->geoms) { cudaFree(kv.second.d_taps); cudaFree(kv.second.d_ftab); cudaFree(kv.second.d_btab); }
   if (h->bgr_stage) cudaFree(h->bgr_stage);
-  if (h->gb.tr_subset) { cudaFree(h->gb.tr_subset); cudaFree(h->gb.tr_nmodels); cudaFree(h->gb.tr_counts); cudaFree(h->gb.tr_models); }
-  if (h->h_out_d) cudaFreeHost(h->h_out_d);
-  if (h->h_out_i) cudaFreeHost(h->h_out_i);
-  if (h->h_K) cudaFreeHost(h->h_K);
+  if (h->gb[0].tr_subset) { cudaFree(h->gb[0].tr_subset); cudaFree(h->gb[0].tr_nmodels); cudaFree(h->gb[0].tr_counts); cudaFree(h->gb[0].tr_models); }
+  for (int k = 0; k < rpe_handle::kDepth; ++k) {
+    if (h->h_out_d[k]) cudaFreeHost(h->h_out_d[k]);
+    if (h->h_out_i[k]) cudaFreeHost(h->h_out_i[k]);
+    if (h->h_K[k]) cudaFreeHost(h->h_K[k]);
+    if (h->ev_done_call[k]) cudaEventDestroy(h->ev_done_call[k]);
+  }
   for (int i = 0; i <= RPE_T_COUNT; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
-  for (int i = 0; i < rpe_handle::kMaxWorkers; ++i) {
-    if (h->wstream[i]) cudaStreamDestroy(h->wstream[i]);
-    if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+  if (h->s_copy) cudaStreamDestroy(h->s_copy);
+  if (h->s_tail) cudaStreamDestroy(h->s_tail);
+  for (int i = 0; i < rpe_handle::kChunkEvents; ++i) {
+    if (h->ev_up[i]) cudaEventDestroy(h->ev_up[i]);
+    if (h->ev_dense[i]) cudaEventDestroy(h->ev_dense[i]);
   }
-  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
-  for (int i = 0; i < rpe_handle::kChunkEvents; ++i) if (h->ev_chunk[i]) cudaEventDestroy(h->ev_chunk[i]);
   delete h;
 }
 
 int rpe_set_stream(rpe_handle* h, void* s) {
   if (!h) return fail(RPE_ERR_INVALID, "null handle");
+  if (h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   h->stream = s ? (cudaStream_t)s : h->own_stream;
   return RPE_OK;
 }
@@ -369,7 +393,7 @@ int rpe_set_pipeline(rpe_handle* h, int32_t chunk_pairs, int32_t n_streams) {
 int rpe_set_input_format(rpe_handle* h, int32_t channels, int32_t gray_mode) {
   if (!h || (channels != 1 && channels != 3) || (gray_mode != RPE_GRAY_CVTCOLOR && gray_mode != RPE_GRAY_IMREAD_PNG))
     return fail(RPE_ERR_INVALID, "channels must be 1 or 3, gray_mode RPE_GRAY_*");
-  if (h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   h->in_channels = channels;
   h->gray_mode = gray_mode;
   return RPE_OK;
@@ -402,8 +426,9 @@ int rpe_get_stage_times(rpe_handle* h, float* ms, int32_t* launches) {
 // ---------------------------------------------------------------------------------------------
 // Slot views: the same buffer structs with every pointer advanced to image slot img0 = 2 * pair0,
 // so the kernels (which index from 0) work on a sub-batch.
-static OrbBuffers orb_view(const rpe_handle* h, int img0) {
+static OrbBuffers orb_view(const rpe_handle* h, int set, int img0) {
   OrbBuffers b = h->ob;
+  b.pyr = h->pyr2[set];
   const size_t i = (size_t)img0, L = h->cfg.nlevels, CS = h->cand_stride, KS = h->kp_stride;
   b.pyr += i * h->pyr_stride; b.blur += i * h->pyr_stride;
   b.cand_key += i * CS; b.sel_key += i * CS; b.sel_resp += i * CS;
@@ -413,16 +438,16 @@ static OrbBuffers orb_view(const rpe_handle* h, int img0) {
   b.kp_oct += i * KS; b.desc += i * KS * 32; b.kp_n += i;
   return b;
 }
-static MatchBuffers match_view(const rpe_handle* h, int pair0) {
-  MatchBuffers m = h->mb;
+static MatchBuffers match_view(const rpe_handle* h, int set, int pair0) {
+  MatchBuffers m = h->mb[set];
   const size_t p = (size_t)pair0, KS = h->kp_stride, MC = h->mcap;
   m.fwd1 += p * KS; m.fwd2 += p * KS; m.bwd1 += p * KS;
-  m.m_q += p * MC; m.m_t += p * MC; m.m_d += p * MC; m.m_n += p;
+  m.m_q += p * MC; m.m_t += p * MC; m.m_d += p * MC; m.m_n += p; m.pstat += p;
   m.pts1 += p * MC * 2; m.pts2 += p * MC * 2;
   return m;
 }
-static GeomBuffers geom_view(const rpe_handle* h, int pair0) {
-  GeomBuffers g = h->gb;
+static GeomBuffers geom_view(const rpe_handle* h, int set, int pair0) {
+  GeomBuffers g = h->gb[set];
   const size_t p = (size_t)pair0, MC = h->mcap;
   g.npts += p * MC * 4; g.E += p * 9; g.rmask += p * MC; g.pmask += p * MC; g.rinfo += p * 4;
   g.R += p * 9; g.t += p * 3; g.euler += p * 3; g.pose_cnt += p; g.status += p;
@@ -431,7 +456,7 @@ static GeomBuffers geom_view(const rpe_handle* h, int pair0) {
 }
 
 static inline void mark(rpe_handle* h, int i, bool prof) {
-  if (prof) cudaEventRecord(h->ev[i], h->stream);
+  if (prof) cudaEventRecord(h->ev[i], h->stream);   // profiling runs every stage on the handle's stream
 }
 
 static int finish_profile(rpe_handle* h) {
@@ -447,8 +472,8 @@ static int clear_counters(rpe_handle* h, cudaStream_t s) {
 }
 
 // ORB over image slots [img0, img0 + n_img) on stream s (counters already cleared)
-static int run_orb(rpe_handle* h, const Geometry& G, int img0, int n_img, cudaStream_t s, bool prof) {
-  OrbBuffers b = orb_view(h, img0);
+static int run_orb(rpe_handle* h, const Geometry& G, int set, int img0, int n_img, cudaStream_t s, bool prof) {
+  OrbBuffers b = orb_view(h, set, img0);
   b.taps = G.d_taps;
   b.ftab = G.d_ftab;
   b.btab = G.d_btab;
@@ -475,10 +500,10 @@ static RansacParams ransac_params(const rpe_handle* h) {
 }
 
 // match -> sort/cut over pair slots [pair0, pair0 + nb) on stream s (dense, XU-pipe bound)
-static int run_match(rpe_handle* h, int pair0, int nb, int pstep, cudaStream_t s, bool prof) {
+static int run_match(rpe_handle* h, int set, int pair0, int nb, int pstep, cudaStream_t s, bool prof) {
   int* ln = h->launches;
-  const OrbBuffers ob = orb_view(h, pstep * pair0);
-  const MatchBuffers mb = match_view(h, pair0);
+  const OrbBuffers ob = orb_view(h, set, pstep * pair0);
+  const MatchBuffers mb = match_view(h, set, pair0);
   mark(h, RPE_T_MATCH, prof);
   launch_match(ob, mb, h->kp_stride, nb, pstep, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
   mark(h, RPE_T_MATCH_SORT, prof);
@@ -489,61 +514,61 @@ static int run_match(rpe_handle* h, int pair0, int nb, int pstep, cudaStream_t s
 }
 
 // RANSAC -> pose over pair slots [pair0, pair0 + nb) on stream s (one CTA per pair: latency bound)
-static int run_geometry(rpe_handle* h, int pair0, int nb, int pstep, cudaStream_t s, bool prof) {
+// (reads only the tail-buffer set: never the ORB buffers, which the next batch may be overwriting)
+static int run_geometry(rpe_handle* h, int set, int pair0, int nb, cudaStream_t s, bool prof) {
   int* ln = h->launches;
-  const OrbBuffers ob = orb_view(h, pstep * pair0);
-  const MatchBuffers mb = match_view(h, pair0);
-  const GeomBuffers gb = geom_view(h, pair0);
+  const MatchBuffers mb = match_view(h, set, pair0);
+  const GeomBuffers gb = geom_view(h, set, pair0);
   mark(h, RPE_T_RANSAC, prof);
-  launch_normalize(mb, gb, h->mcap, nb, h->dK, s, &ln[RPE_T_RANSAC]);
-  launch_ransac(mb, gb, h->mcap, nb, h->dK, ransac_params(h), s, &ln[RPE_T_RANSAC]);
+  launch_normalize(mb, gb, h->mcap, nb, h->dK[set], s, &ln[RPE_T_RANSAC]);
+  launch_ransac(mb, gb, h->mcap, nb, h->dK[set], ransac_params(h), s, &ln[RPE_T_RANSAC]);
   mark(h, RPE_T_POSE, prof);
-  launch_pose(mb, gb, h->mcap, nb, ransac_params(h), ob.img_flags, ob.kp_n, pstep, s, &ln[RPE_T_POSE]);
+  launch_pose(mb, gb, h->mcap, nb, ransac_params(h), mb.pstat, s, &ln[RPE_T_POSE]);
   RPE_CK(cudaGetLastError());
   return RPE_OK;
 }
 
-static int upload_K(rpe_handle* h, const double K[9]) {
-  memcpy(h->h_K, K, 9 * sizeof(double));
-  RPE_CK(cudaMemcpyAsync(h->dK, h->h_K, 9 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+static int upload_K(rpe_handle* h, int set, const double K[9]) {
+  memcpy(h->h_K[set], K, 9 * sizeof(double));
+  RPE_CK(cudaMemcpyAsync(h->dK[set], h->h_K[set], 9 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
   return RPE_OK;
 }
 
-// async D2H of the results of pair slots [pair0, pair0 + nb) into the pinned staging buffers
-static int download_async(rpe_handle* h, int pair0, int nb, bool info, cudaStream_t s) {
-  double* hd = h->h_out_d;
-  int32_t* hi = h->h_out_i;
+// async D2H of the results of pair slots [pair0, pair0 + nb) of a set into its pinned staging buffers
+static int download_async(rpe_handle* h, int set, int pair0, int nb, cudaStream_t s) {
+  double* hd = h->h_out_d[set];
+  int32_t* hi = h->h_out_i[set];
+  const GeomBuffers& gb = h->gb[set];
   const size_t NP = h->NP, p = pair0, n = nb;
-  RPE_CK(cudaMemcpyAsync(hd + p * 9, h->gb.R + p * 9, n * 9 * sizeof(double), cudaMemcpyDeviceToHost, s));
-  RPE_CK(cudaMemcpyAsync(hd + NP * 9 + p * 3, h->gb.t + p * 3, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
-  RPE_CK(cudaMemcpyAsync(hd + NP * 12 + p * 3, h->gb.euler + p * 3, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
-  RPE_CK(cudaMemcpyAsync(hi + p, h->gb.status + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-  if (info) {
-    RPE_CK(cudaMemcpyAsync(hi + NP + p, h->mb.m_n + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-    RPE_CK(cudaMemcpyAsync(hi + 2 * NP + p, h->gb.pose_cnt + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-  }
+  RPE_CK(cudaMemcpyAsync(hd + p * 9, gb.R + p * 9, n * 9 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hd + NP * 9 + p * 3, gb.t + p * 3, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hd + NP * 12 + p * 3, gb.euler + p * 3, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hi + p, gb.status + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hi + NP + p, h->mb[set].m_n + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hi + 2 * NP + p, gb.pose_cnt + p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(hi + 3 * NP + p * 4, gb.rinfo + p * 4, n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   return RPE_OK;
 }
 
-static int finish_results(rpe_handle* h, int B, double* R, double* t, double* euler, int32_t* status, int32_t* info) {
-  double* hd = h->h_out_d;
-  int32_t* hi = h->h_out_i;
-  RPE_CK(cudaStreamSynchronize(h->stream));
-  if (R) memcpy(R, hd, (size_t)B * 9 * sizeof(double));
-  if (t) memcpy(t, hd + (size_t)h->NP * 9, (size_t)B * 3 * sizeof(double));
-  if (euler) memcpy(euler, hd + (size_t)h->NP * 12, (size_t)B * 3 * sizeof(double));
-  if (status) memcpy(status, hi, (size_t)B * sizeof(int32_t));
-  if (info) {
-    // rinfo is small: fetch {best, iters} synchronously (stream already idle)
-    std::vector<int32_t> ri((size_t)B * 4);
-    RPE_CK(cudaMemcpy(ri.data(), h->gb.rinfo, ri.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
-    for (int i = 0; i < B; ++i) {
-      info[4 * i + 0] = hi[h->NP + i];
-      info[4 * i + 1] = hi[2 * h->NP + i];
-      info[4 * i + 2] = ri[4 * i + 1];
-      info[4 * i + 3] = ri[4 * i + 2];
+// wait for a batch's tail (its last D2H) and hand the staged results to the caller
+static int finish_results(rpe_handle* h, const rpe_handle::Pending& p) {
+  const double* hd = h->h_out_d[p.set];
+  const int32_t* hi = h->h_out_i[p.set];
+  const size_t NP = h->NP, B = p.B;
+  RPE_CK(cudaEventSynchronize(h->ev_done_call[p.set]));
+  if (p.R) memcpy(p.R, hd, B * 9 * sizeof(double));
+  if (p.t) memcpy(p.t, hd + NP * 9, B * 3 * sizeof(double));
+  if (p.euler) memcpy(p.euler, hd + NP * 12, B * 3 * sizeof(double));
+  if (p.status) memcpy(p.status, hi, B * sizeof(int32_t));
+  if (p.info) {
+    for (size_t i = 0; i < B; ++i) {
+      p.info[4 * i + 0] = hi[NP + i];                 // num_matches
+      p.info[4 * i + 1] = hi[2 * NP + i];             // recoverPose count
+      p.info[4 * i + 2] = hi[3 * NP + 4 * i + 1];     // RANSAC inliers
+      p.info[4 * i + 3] = hi[3 * NP + 4 * i + 2];     // RANSAC iterations
     }
   }
+  h->last_set = p.set;
   return finish_profile(h);
 }
 
@@ -592,14 +617,14 @@ static int ensure_bgr_stage(rpe_handle* h, int n_img, int H, int W) {
 
 // copy the images of slots [img0, img0 + ni) into level 0 of their pyramid slabs; BGR input goes
 // through the staging buffer (or straight from an aligned device buffer) and k_bgr2gray
-static int upload_images(rpe_handle* h, const Geometry& G, const BatchSource& src, int img0, int ni, int H, int W,
-                         cudaStream_t s) {
+static int upload_images(rpe_handle* h, const Geometry& G, const BatchSource& src, int set, int img0, int ni, int H,
+                         int W, cudaStream_t s) {
   const bool bgr = src.channels == 3;
   const int p0 = G.g.lv[0].pitch;                                    // gray pitch of level 0
   const int dp = bgr ? align_up(3 * W, 16) : p0;                     // device pitch of the copied rows
   const size_t row = (size_t)W * src.channels;
   const size_t dstride = bgr ? h->bgr_stage_stride : h->pyr_stride;
-  uint8_t* pyr0 = h->ob.pyr + (size_t)img0 * h->pyr_stride;
+  uint8_t* pyr0 = h->pyr2[set] + (size_t)img0 * h->pyr_stride;
   uint8_t* dst = bgr ? h->bgr_stage + (size_t)img0 * dstride : pyr0;
   const uint8_t* conv_src = dst;
   size_t conv_stride = dstride;
@@ -643,93 +668,84 @@ static void fill_host_source(BatchSource& src, const uint8_t* const* img1, const
   src.host_stride = stride;
 }
 
-// The whole hot path over B pairs (pair batch: 2B images; sequence: B + 1 frames).  Profiling (or
-// n_streams == 1): one chunk on the handle's stream, with an event between stages when profiling.
-// Otherwise a copy / compute stream pipeline over chunks of images, forked from and joined back into
-// the handle's stream.
+// The whole hot path over B pairs (pair batch: 2B images; sequence: B + 1 frames), enqueued without
+// waiting.  Profiling: one chunk, every stage on the handle's stream with an event between stages.
+// Otherwise the three-stream pipeline described at rpe_handle: uploads on s_copy, dense kernels of all
+// chunks in order on the handle's stream, geometry tail + D2H on s_tail.
 static int enqueue_batch(rpe_handle* h, const BatchSource& src, int B, int H, int W, const double K[9], double* R,
                          double* t, double* euler, int32_t* status, int32_t* info) {
-  if (h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is still pending: call rpe_wait_batch first");
+  if (h->n_pending >= rpe_handle::kDepth) return fail(RPE_ERR_INVALID, "two submitted batches are pending: call rpe_wait_batch first");
+  const bool prof = h->profiling;
+  if (prof && h->n_pending) return fail(RPE_ERR_INVALID, "profiling needs one batch at a time: call rpe_wait_batch first");
   const Geometry* G;
   RPE_TRY(get_geometry(h, W, H, &G));
-  reset_profile(h);
-  const bool prof = h->profiling;
   const int pstep = src.sequence ? 1 : 2;
   const int n_img = src.sequence ? B + 1 : 2 * B;
   if (src.pitch < (size_t)W * src.channels) return fail(RPE_ERR_INVALID, "pitch smaller than one image row");
   if (src.d_images && src.img_stride < src.pitch * (size_t)H) return fail(RPE_ERR_INVALID, "img_stride smaller than one image");
   if (src.channels == 3) RPE_TRY(ensure_bgr_stage(h, h->NI, H, W));
+  reset_profile(h);
+  // buffer set of this batch; the batch that used it last (seq - 2) has been waited for (n_pending < 2), so its
+  // pyramid slabs and tail buffers are free and the upload can start at once
+  const int set = (int)(h->seq & 1);
+  cudaStream_t s_main = h->stream;
+  cudaStream_t s_copy = (prof || src.d_images) ? s_main : h->s_copy;   // device inputs: a cheap D2D copy, in order
+  cudaStream_t s_tail = prof ? s_main : h->s_tail;
   mark(h, RPE_T_H2D, prof);
-  RPE_TRY(upload_K(h, K));
-  RPE_TRY(clear_counters(h, h->stream));
-  // device-resident inputs have no upload to hide: one chunk (chunking only costs kernel tails)
-  const int chunk_img = (prof || h->n_workers < 2 || src.d_images) ? n_img : std::min(n_img, 2 * h->chunk_pairs);
+  RPE_TRY(upload_K(h, set, K));
+  RPE_TRY(clear_counters(h, s_main));
+  const int chunk_img = (prof || h->n_workers < 2) ? n_img : std::min(n_img, 2 * h->chunk_pairs);
   const int n_chunks = (n_img + chunk_img - 1) / chunk_img;
-  if (n_chunks == 1) {
-    RPE_TRY(upload_images(h, *G, src, 0, n_img, H, W, h->stream));
-    RPE_TRY(run_orb(h, *G, 0, n_img, h->stream, prof));
-    RPE_TRY(run_match(h, 0, B, pstep, h->stream, prof));
-    RPE_TRY(run_geometry(h, 0, B, pstep, h->stream, prof));
-    mark(h, RPE_T_D2H, prof);
-    RPE_TRY(download_async(h, 0, B, info != nullptr, h->stream));
-    if (prof) cudaEventRecord(h->ev[RPE_T_COUNT], h->stream);
-  } else {
-    // copy stream + (n_workers - 1) compute streams.  The image upload of chunk c+1 runs under the
-    // kernels of chunk c; chunks alternate between the compute streams so that the tail of one
-    // chunk's kernels (and its latency-bound RANSAC / pose) is filled by the next chunk's kernels.
-    // Sequence mode: the pair that straddles two chunks needs the features of the previous chunk's
-    // last frame, so a chunk's matcher waits for the previous chunk's ORB (e_orb).
-    cudaStream_t s_copy = h->wstream[0];
-    const int nc = h->n_workers - 1;
-    RPE_CK(cudaEventRecord(h->ev_fork, h->stream));
-    for (int w = 0; w <= nc; ++w) RPE_CK(cudaStreamWaitEvent(h->wstream[w], h->ev_fork, 0));
-    cudaEvent_t e_orb_prev = nullptr;
-    for (int c = 0; c < n_chunks; ++c) {
-      const int img0 = c * chunk_img, ni = std::min(chunk_img, n_img - img0);
-      // pairs completed by this chunk: [pair0, pair1)
-      const int pair0 = src.sequence ? std::max(img0 - 1, 0) : img0 / 2;
-      const int pair1 = src.sequence ? img0 + ni - 1 : (img0 + ni) / 2;
-      cudaEvent_t e_up = h->ev_chunk[(2 * c) % rpe_handle::kChunkEvents];
-      cudaEvent_t e_orb = h->ev_chunk[(2 * c + 1) % rpe_handle::kChunkEvents];
-      cudaStream_t s_dense = h->wstream[1 + c % nc];
-      RPE_TRY(upload_images(h, *G, src, img0, ni, H, W, s_copy));
+  for (int c = 0; c < n_chunks; ++c) {
+    const int img0 = c * chunk_img, ni = std::min(chunk_img, n_img - img0);
+    // pairs completed by this chunk: [pair0, pair1); in a sequence the pair that straddles two chunks
+    // belongs to the later one (same stream: its first frame's features are already there)
+    const int pair0 = src.sequence ? std::max(img0 - 1, 0) : img0 / 2;
+    const int pair1 = src.sequence ? img0 + ni - 1 : (img0 + ni) / 2;
+    cudaEvent_t e_up = h->ev_up[c % rpe_handle::kChunkEvents];
+    cudaEvent_t e_dense = h->ev_dense[c % rpe_handle::kChunkEvents];
+    RPE_TRY(upload_images(h, *G, src, set, img0, ni, H, W, s_copy));
+    if (s_copy != s_main) {
       RPE_CK(cudaEventRecord(e_up, s_copy));
-      RPE_CK(cudaStreamWaitEvent(s_dense, e_up, 0));
-      RPE_TRY(run_orb(h, *G, img0, ni, s_dense, false));
-      if (src.sequence) {
-        RPE_CK(cudaEventRecord(e_orb, s_dense));
-        if (e_orb_prev) RPE_CK(cudaStreamWaitEvent(s_dense, e_orb_prev, 0));
-        e_orb_prev = e_orb;
-      }
-      if (pair1 > pair0) {
-        RPE_TRY(run_match(h, pair0, pair1 - pair0, pstep, s_dense, false));
-        RPE_TRY(run_geometry(h, pair0, pair1 - pair0, pstep, s_dense, false));
-        RPE_TRY(download_async(h, pair0, pair1 - pair0, info != nullptr, s_dense));
-      }
+      RPE_CK(cudaStreamWaitEvent(s_main, e_up, 0));
     }
-    for (int w = 0; w <= nc; ++w) {
-      RPE_CK(cudaEventRecord(h->ev_done[w], h->wstream[w]));
-      RPE_CK(cudaStreamWaitEvent(h->stream, h->ev_done[w], 0));
+    RPE_TRY(run_orb(h, *G, set, img0, ni, s_main, prof));
+    if (pair1 > pair0) {
+      RPE_TRY(run_match(h, set, pair0, pair1 - pair0, pstep, s_main, prof));
+      if (s_tail != s_main) {
+        RPE_CK(cudaEventRecord(e_dense, s_main));
+        RPE_CK(cudaStreamWaitEvent(s_tail, e_dense, 0));
+      }
+      RPE_TRY(run_geometry(h, set, pair0, pair1 - pair0, s_tail, prof));
+      mark(h, RPE_T_D2H, prof && c == n_chunks - 1);
+      RPE_TRY(download_async(h, set, pair0, pair1 - pair0, s_tail));
     }
   }
+  if (prof) cudaEventRecord(h->ev[RPE_T_COUNT], s_main);
+  RPE_CK(cudaEventRecord(h->ev_done_call[set], s_tail));
   h->last_geom = G;
   h->last_pairs = B;
   h->last_pstep = pstep;
-  h->pending.active = true; h->pending.B = B;
-  h->pending.R = R; h->pending.t = t; h->pending.euler = euler; h->pending.status = status; h->pending.info = info;
+  rpe_handle::Pending& p = h->pend[h->n_pending++];
+  p.B = B; p.set = set; p.R = R; p.t = t; p.euler = euler; p.status = status; p.info = info;
+  ++h->seq;
   return RPE_OK;
 }
 
+// oldest pending batch
 static int wait_batch(rpe_handle* h) {
-  if (!h->pending.active) return fail(RPE_ERR_INVALID, "no submitted batch to wait for");
-  const rpe_handle::Pending p = h->pending;
-  h->pending.active = false;
+  if (!h->n_pending) return fail(RPE_ERR_INVALID, "no submitted batch to wait for");
+  const rpe_handle::Pending p = h->pend[0];
+  h->pend[0] = h->pend[1];
+  --h->n_pending;
   RPE_CK(cudaSetDevice(h->device));
-  return finish_results(h, p.B, p.R, p.t, p.euler, p.status, p.info);
+  return finish_results(h, p);
 }
 
+// blocking form: nothing else may be pending, so that the results waited for are this call's
 static int run_batch(rpe_handle* h, const BatchSource& src, int B, int H, int W, const double K[9], double* R,
                      double* t, double* euler, int32_t* status, int32_t* info) {
+  if (h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   RPE_TRY(enqueue_batch(h, src, B, H, W, K, R, t, euler, status, info));
   return wait_batch(h);
 }
@@ -824,15 +840,16 @@ int rpe_estimate_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t 
 int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size_t pitch, float* x, float* y,
                    float* size, float* angle, float* response, int32_t* octave, uint8_t* desc, int32_t* n_out,
                    int32_t* flags_out) {
-  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   RPE_TRY(check_batch(h, 1, H, W, pitch));
   if (!img || !n_out || pitch < (size_t)W) return fail(RPE_ERR_INVALID, "null argument / bad pitch");
   const Geometry* G;
   RPE_TRY(get_geometry(h, W, H, &G));
   reset_profile(h);
-  RPE_CK(cudaMemcpy2DAsync(h->ob.pyr, G->g.lv[0].pitch, img, pitch, W, H, cudaMemcpyHostToDevice, h->stream));
+  RPE_CK(cudaMemcpy2DAsync(h->pyr2[0], G->g.lv[0].pitch, img, pitch, W, H, cudaMemcpyHostToDevice, h->stream));
   RPE_TRY(clear_counters(h, h->stream));
-  RPE_TRY(run_orb(h, *G, 0, 1, h->stream, false));
+  RPE_TRY(run_orb(h, *G, 0, 0, 1, h->stream, false));
+  h->last_set = 0;
   h->last_geom = G;
   h->last_pairs = 0;
   h->last_pstep = 2;
@@ -858,7 +875,7 @@ int rpe_orb_detect(rpe_handle* h, const uint8_t* img, int32_t H, int32_t W, size
 
 int rpe_bgr_to_gray(rpe_handle* h, const uint8_t* bgr, int32_t H, int32_t W, size_t pitch, int32_t gray_mode,
                     uint8_t* gray) {
-  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   RPE_TRY(check_batch(h, 1, H, W, pitch));
   if (!bgr || !gray || pitch < (size_t)3 * W || (gray_mode != RPE_GRAY_CVTCOLOR && gray_mode != RPE_GRAY_IMREAD_PNG))
     return fail(RPE_ERR_INVALID, "bad argument");
@@ -868,17 +885,17 @@ int rpe_bgr_to_gray(rpe_handle* h, const uint8_t* bgr, int32_t H, int32_t W, siz
   reset_profile(h);
   const int dp = align_up(3 * W, 16), p0 = G->g.lv[0].pitch;
   RPE_CK(cudaMemcpy2DAsync(h->bgr_stage, dp, bgr, pitch, (size_t)3 * W, H, cudaMemcpyHostToDevice, h->stream));
-  launch_bgr2gray(h->bgr_stage, h->bgr_stage_stride, dp, h->ob.pyr, h->pyr_stride, p0, W, H, 1, gray_mode, h->stream,
+  launch_bgr2gray(h->bgr_stage, h->bgr_stage_stride, dp, h->pyr2[0], h->pyr_stride, p0, W, H, 1, gray_mode, h->stream,
                   &h->launches[RPE_T_H2D]);
   RPE_CK(cudaGetLastError());
-  RPE_CK(cudaMemcpy2DAsync(gray, W, h->ob.pyr, p0, W, H, cudaMemcpyDeviceToHost, h->stream));
+  RPE_CK(cudaMemcpy2DAsync(gray, W, h->pyr2[0], p0, W, H, cudaMemcpyDeviceToHost, h->stream));
   RPE_CK(cudaStreamSynchronize(h->stream));
   return RPE_OK;
 }
 
 int rpe_match(rpe_handle* h, const uint8_t* desc1, int32_t n1, const uint8_t* desc2, int32_t n2, int32_t* matches,
               int32_t* m_out) {
-  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   if (!h || !m_out || n1 < 0 || n2 < 0) return fail(RPE_ERR_INVALID, "bad argument");
   if (n1 > h->kp_stride || n2 > h->kp_stride) return fail(RPE_ERR_CAPACITY, "more descriptors than the handle's keypoint capacity");
   RPE_CK(cudaSetDevice(h->device));
@@ -891,19 +908,19 @@ int rpe_match(rpe_handle* h, const uint8_t* desc1, int32_t n1, const uint8_t* de
   RPE_CK(cudaMemcpyAsync(h->ob.kp_n, nn, sizeof nn, cudaMemcpyHostToDevice, s));
   RPE_CK(cudaStreamSynchronize(s));   // nn is a stack buffer
   int* ln = h->launches;
-  launch_match(h->ob, h->mb, h->kp_stride, 1, 2, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
-  launch_build_matches(h->ob, h->mb, h->kp_stride, h->mcap, h->sort_cap_match, 1, 2, h->cfg.match_mode, h->cfg.ratio,
+  launch_match(h->ob, h->mb[0], h->kp_stride, 1, 2, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
+  launch_build_matches(h->ob, h->mb[0], h->kp_stride, h->mcap, h->sort_cap_match, 1, 2, h->cfg.match_mode, h->cfg.ratio,
                        h->cfg.max_matches, s, &ln[RPE_T_MATCH_SORT]);
   RPE_CK(cudaGetLastError());
   int32_t m = 0;
-  RPE_CK(cudaMemcpyAsync(&m, h->mb.m_n, sizeof m, cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaMemcpyAsync(&m, h->mb[0].m_n, sizeof m, cudaMemcpyDeviceToHost, s));
   RPE_CK(cudaStreamSynchronize(s));
   *m_out = m;
   if (matches && m) {
     std::vector<int32_t> q(m), t(m), d(m);
-    RPE_CK(cudaMemcpy(q.data(), h->mb.m_q, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
-    RPE_CK(cudaMemcpy(t.data(), h->mb.m_t, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
-    RPE_CK(cudaMemcpy(d.data(), h->mb.m_d, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    RPE_CK(cudaMemcpy(q.data(), h->mb[0].m_q, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    RPE_CK(cudaMemcpy(t.data(), h->mb[0].m_t, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    RPE_CK(cudaMemcpy(d.data(), h->mb[0].m_d, m * sizeof(int32_t), cudaMemcpyDeviceToHost));
     for (int i = 0; i < m; ++i) { matches[3 * i] = q[i]; matches[3 * i + 1] = t[i]; matches[3 * i + 2] = d[i]; }
   }
   return RPE_OK;
@@ -913,80 +930,81 @@ static int upload_points(rpe_handle* h, const float* pts1, const float* pts2, in
   if (m < 0 || m > h->mcap) return fail(RPE_ERR_CAPACITY, "more points than the handle's match capacity");
   cudaStream_t s = h->stream;
   if (m) {
-    RPE_CK(cudaMemcpyAsync(h->mb.pts1, pts1, (size_t)m * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
-    RPE_CK(cudaMemcpyAsync(h->mb.pts2, pts2, (size_t)m * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
+    RPE_CK(cudaMemcpyAsync(h->mb[0].pts1, pts1, (size_t)m * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
+    RPE_CK(cudaMemcpyAsync(h->mb[0].pts2, pts2, (size_t)m * 2 * sizeof(float), cudaMemcpyHostToDevice, s));
   }
-  RPE_CK(cudaMemcpyAsync(h->mb.m_n, &m, sizeof m, cudaMemcpyHostToDevice, s));
-  RPE_TRY(upload_K(h, K));
+  RPE_CK(cudaMemcpyAsync(h->mb[0].m_n, &m, sizeof m, cudaMemcpyHostToDevice, s));
+  RPE_TRY(upload_K(h, 0, K));
   RPE_CK(cudaStreamSynchronize(s));
+  h->last_set = 0;
   int dummy = 0;
-  launch_normalize(h->mb, h->gb, h->mcap, 1, h->dK, s, &dummy);
+  launch_normalize(h->mb[0], h->gb[0], h->mcap, 1, h->dK[0], s, &dummy);
   return RPE_OK;
 }
 
 int rpe_find_essential(rpe_handle* h, const float* pts1, const float* pts2, int32_t m, const double K[9], double* E,
                        uint8_t* mask, int32_t* info) {
-  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   if (!h || !K || (m > 0 && (!pts1 || !pts2))) return fail(RPE_ERR_INVALID, "bad argument");
   RPE_CK(cudaSetDevice(h->device));
   reset_profile(h);
-  if (!h->gb.tr_subset) {
+  if (!h->gb[0].tr_subset) {
     const int cap = (h->cfg.ransac_max_iters + 63) / 64 * 64;
-    RPE_CK(cudaMalloc((void**)&h->gb.tr_subset, (size_t)cap * 5 * sizeof(int32_t)));
-    RPE_CK(cudaMalloc((void**)&h->gb.tr_nmodels, (size_t)cap * sizeof(int32_t)));
-    RPE_CK(cudaMalloc((void**)&h->gb.tr_counts, (size_t)cap * 10 * sizeof(int32_t)));
-    RPE_CK(cudaMalloc((void**)&h->gb.tr_models, (size_t)cap * 90 * sizeof(double)));
-    h->gb.tr_cap = cap;
+    RPE_CK(cudaMalloc((void**)&h->gb[0].tr_subset, (size_t)cap * 5 * sizeof(int32_t)));
+    RPE_CK(cudaMalloc((void**)&h->gb[0].tr_nmodels, (size_t)cap * sizeof(int32_t)));
+    RPE_CK(cudaMalloc((void**)&h->gb[0].tr_counts, (size_t)cap * 10 * sizeof(int32_t)));
+    RPE_CK(cudaMalloc((void**)&h->gb[0].tr_models, (size_t)cap * 90 * sizeof(double)));
+    h->gb[0].tr_cap = cap;
   }
   RPE_TRY(upload_points(h, pts1, pts2, m, K));
-  launch_ransac(h->mb, h->gb, h->mcap, 1, h->dK, ransac_params(h), h->stream, &h->launches[RPE_T_RANSAC]);
+  launch_ransac(h->mb[0], h->gb[0], h->mcap, 1, h->dK[0], ransac_params(h), h->stream, &h->launches[RPE_T_RANSAC]);
   RPE_CK(cudaGetLastError());
   RPE_CK(cudaStreamSynchronize(h->stream));
-  if (E) RPE_CK(cudaMemcpy(E, h->gb.E, 9 * sizeof(double), cudaMemcpyDeviceToHost));
-  if (mask && m) RPE_CK(cudaMemcpy(mask, h->gb.rmask, m, cudaMemcpyDeviceToHost));
-  if (info) RPE_CK(cudaMemcpy(info, h->gb.rinfo, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (E) RPE_CK(cudaMemcpy(E, h->gb[0].E, 9 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (mask && m) RPE_CK(cudaMemcpy(mask, h->gb[0].rmask, m, cudaMemcpyDeviceToHost));
+  if (info) RPE_CK(cudaMemcpy(info, h->gb[0].rinfo, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost));
   return RPE_OK;
 }
 
 int rpe_ransac_trace(rpe_handle* h, int32_t max_hyp, int32_t* subset, int32_t* nmodels, int32_t* counts,
                      double* models, int32_t* n_hyp) {
-  if (!h || !h->gb.tr_subset || !n_hyp) return fail(RPE_ERR_INVALID, "no trace available");
+  if (!h || !h->gb[0].tr_subset || !n_hyp) return fail(RPE_ERR_INVALID, "no trace available");
   RPE_CK(cudaSetDevice(h->device));
   int32_t ri[4];
-  RPE_CK(cudaMemcpy(ri, h->gb.rinfo, sizeof ri, cudaMemcpyDeviceToHost));
-  const int n = std::min(std::min(ri[3], max_hyp), h->gb.tr_cap);
+  RPE_CK(cudaMemcpy(ri, h->gb[0].rinfo, sizeof ri, cudaMemcpyDeviceToHost));
+  const int n = std::min(std::min(ri[3], max_hyp), h->gb[0].tr_cap);
   *n_hyp = n;
   if (n <= 0) return RPE_OK;
-  if (subset) RPE_CK(cudaMemcpy(subset, h->gb.tr_subset, (size_t)n * 5 * sizeof(int32_t), cudaMemcpyDeviceToHost));
-  if (nmodels) RPE_CK(cudaMemcpy(nmodels, h->gb.tr_nmodels, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost));
-  if (counts) RPE_CK(cudaMemcpy(counts, h->gb.tr_counts, (size_t)n * 10 * sizeof(int32_t), cudaMemcpyDeviceToHost));
-  if (models) RPE_CK(cudaMemcpy(models, h->gb.tr_models, (size_t)n * 90 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (subset) RPE_CK(cudaMemcpy(subset, h->gb[0].tr_subset, (size_t)n * 5 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (nmodels) RPE_CK(cudaMemcpy(nmodels, h->gb[0].tr_nmodels, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (counts) RPE_CK(cudaMemcpy(counts, h->gb[0].tr_counts, (size_t)n * 10 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (models) RPE_CK(cudaMemcpy(models, h->gb[0].tr_models, (size_t)n * 90 * sizeof(double), cudaMemcpyDeviceToHost));
   return RPE_OK;
 }
 
 int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const float* pts2, int32_t m,
                      const double K[9], double* R, double* t, double* euler, int32_t* count, uint8_t* mask) {
-  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   if (!h || !E || !K || (m > 0 && (!pts1 || !pts2))) return fail(RPE_ERR_INVALID, "bad argument");
   RPE_CK(cudaSetDevice(h->device));
   reset_profile(h);
-  RPE_CK(cudaMemcpy(h->gb.E, E, 9 * sizeof(double), cudaMemcpyHostToDevice));
+  RPE_CK(cudaMemcpy(h->gb[0].E, E, 9 * sizeof(double), cudaMemcpyHostToDevice));
   RPE_TRY(upload_points(h, pts1, pts2, m, K));
-  GeomBuffers gb = h->gb;
+  GeomBuffers gb = h->gb[0];
   gb.rinfo = nullptr;
-  launch_pose(h->mb, gb, h->mcap, 1, ransac_params(h), nullptr, nullptr, 2, h->stream, &h->launches[RPE_T_POSE]);
+  launch_pose(h->mb[0], gb, h->mcap, 1, ransac_params(h), nullptr, h->stream, &h->launches[RPE_T_POSE]);
   RPE_CK(cudaGetLastError());
   RPE_CK(cudaStreamSynchronize(h->stream));
-  if (R) RPE_CK(cudaMemcpy(R, h->gb.R, 9 * sizeof(double), cudaMemcpyDeviceToHost));
-  if (t) RPE_CK(cudaMemcpy(t, h->gb.t, 3 * sizeof(double), cudaMemcpyDeviceToHost));
-  if (euler) RPE_CK(cudaMemcpy(euler, h->gb.euler, 3 * sizeof(double), cudaMemcpyDeviceToHost));
-  if (count) RPE_CK(cudaMemcpy(count, h->gb.pose_cnt, sizeof(int32_t), cudaMemcpyDeviceToHost));
-  if (mask && m) RPE_CK(cudaMemcpy(mask, h->gb.pmask, m, cudaMemcpyDeviceToHost));
+  if (R) RPE_CK(cudaMemcpy(R, h->gb[0].R, 9 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (t) RPE_CK(cudaMemcpy(t, h->gb[0].t, 3 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (euler) RPE_CK(cudaMemcpy(euler, h->gb[0].euler, 3 * sizeof(double), cudaMemcpyDeviceToHost));
+  if (count) RPE_CK(cudaMemcpy(count, h->gb[0].pose_cnt, sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (mask && m) RPE_CK(cudaMemcpy(mask, h->gb[0].pmask, m, cudaMemcpyDeviceToHost));
   return RPE_OK;
 }
 
 int rpe_get_stage(rpe_handle* h, int32_t pair, int32_t view, int32_t stage, int32_t arg, void* out, size_t* n) {
-  if (h && h->pending.active) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   if (!h || !n || !out) return fail(RPE_ERR_INVALID, "null argument");
   if (pair < 0 || pair >= h->NP || view < 0 || view > 1) return fail(RPE_ERR_INVALID, "bad pair/view");
   RPE_CK(cudaSetDevice(h->device));
@@ -1001,13 +1019,13 @@ int rpe_get_stage(rpe_handle* h, int32_t pair, int32_t view, int32_t stage, int3
   };
   int32_t kn = 0, mn = 0;
   RPE_CK(cudaMemcpy(&kn, h->ob.kp_n + img, sizeof kn, cudaMemcpyDeviceToHost));
-  RPE_CK(cudaMemcpy(&mn, h->mb.m_n + pair, sizeof mn, cudaMemcpyDeviceToHost));
+  RPE_CK(cudaMemcpy(&mn, h->mb[h->last_set].m_n + pair, sizeof mn, cudaMemcpyDeviceToHost));
   switch (stage) {
     case RPE_STAGE_PYRAMID_LEVEL:
     case RPE_STAGE_BLURRED_LEVEL: {
       if (!h->last_geom || arg < 0 || arg >= h->cfg.nlevels) return fail(RPE_ERR_INVALID, "no geometry / bad level");
       const LevelGeom& L = h->last_geom->g.lv[arg];
-      const uint8_t* base = (stage == RPE_STAGE_PYRAMID_LEVEL ? h->ob.pyr : h->ob.blur) + img * h->pyr_stride + L.off;
+      const uint8_t* base = (stage == RPE_STAGE_PYRAMID_LEVEL ? h->pyr2[h->last_set] : h->ob.blur) + img * h->pyr_stride + L.off;
       const size_t bytes = (size_t)L.w * L.h;
       if (cap < bytes) return fail(RPE_ERR_INVALID, "buffer too small");
       RPE_CK(cudaMemcpy2D(out, L.w, base, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost));
@@ -1024,9 +1042,9 @@ int rpe_get_stage(rpe_handle* h, int32_t pair, int32_t view, int32_t stage, int3
     case RPE_STAGE_MATCHES: {
       std::vector<int32_t> q(mn), t(mn), d(mn), o((size_t)mn * 3);
       if (mn) {
-        RPE_CK(cudaMemcpy(q.data(), h->mb.m_q + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
-        RPE_CK(cudaMemcpy(t.data(), h->mb.m_t + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
-        RPE_CK(cudaMemcpy(d.data(), h->mb.m_d + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        RPE_CK(cudaMemcpy(q.data(), h->mb[h->last_set].m_q + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        RPE_CK(cudaMemcpy(t.data(), h->mb[h->last_set].m_t + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        RPE_CK(cudaMemcpy(d.data(), h->mb[h->last_set].m_d + pair * MC, mn * sizeof(int32_t), cudaMemcpyDeviceToHost));
       }
       for (int i = 0; i < mn; ++i) { o[3 * i] = q[i]; o[3 * i + 1] = t[i]; o[3 * i + 2] = d[i]; }
       const size_t c = std::min(o.size() * sizeof(int32_t), cap);
@@ -1034,11 +1052,11 @@ int rpe_get_stage(rpe_handle* h, int32_t pair, int32_t view, int32_t stage, int3
       *n = c;
       return RPE_OK;
     }
-    case RPE_STAGE_PTS1: return copy(h->mb.pts1 + pair * MC * 2, (size_t)mn * 2 * sizeof(float));
-    case RPE_STAGE_PTS2: return copy(h->mb.pts2 + pair * MC * 2, (size_t)mn * 2 * sizeof(float));
-    case RPE_STAGE_E: return copy(h->gb.E + pair * 9, 9 * sizeof(double));
-    case RPE_STAGE_RANSAC_MASK: return copy(h->gb.rmask + pair * MC, mn);
-    case RPE_STAGE_POSE_MASK: return copy(h->gb.pmask + pair * MC, mn);
+    case RPE_STAGE_PTS1: return copy(h->mb[h->last_set].pts1 + pair * MC * 2, (size_t)mn * 2 * sizeof(float));
+    case RPE_STAGE_PTS2: return copy(h->mb[h->last_set].pts2 + pair * MC * 2, (size_t)mn * 2 * sizeof(float));
+    case RPE_STAGE_E: return copy(h->gb[h->last_set].E + pair * 9, 9 * sizeof(double));
+    case RPE_STAGE_RANSAC_MASK: return copy(h->gb[h->last_set].rmask + pair * MC, mn);
+    case RPE_STAGE_POSE_MASK: return copy(h->gb[h->last_set].pmask + pair * MC, mn);
     default: return fail(RPE_ERR_INVALID, "unknown stage");
   }
 }

@@ -178,8 +178,8 @@ constexpr int kPoseThreads = 128;
 
 __global__ void __launch_bounds__(kPoseThreads)
 k_pose(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npts, const double* __restrict__ E_in,
-       const int32_t* __restrict__ rinfo, RansacParams rp, const uint32_t* __restrict__ img_flags,
-       const int32_t* __restrict__ kp_n, int pstep, double* __restrict__ R_out, double* __restrict__ t_out,
+       const int32_t* __restrict__ rinfo, RansacParams rp, const int32_t* __restrict__ pstat,
+       double* __restrict__ R_out, double* __restrict__ t_out,
        double* __restrict__ euler_out, int32_t* __restrict__ pose_cnt, uint8_t* __restrict__ pmask,
        int32_t* __restrict__ status) {
   __shared__ double sR[2][9];
@@ -190,11 +190,11 @@ k_pose(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npt
   const int M = m_n[pair];
   // status, mirroring the reference's RuntimeErrors
   int stat = RPE_STATUS_OK;
-  if (kp_n != nullptr && (kp_n[pstep * pair] == 0 || kp_n[pstep * pair + 1] == 0)) stat = RPE_STATUS_NO_DESCRIPTORS;
+  const int ps = pstat != nullptr ? pstat[pair] : 0;     // written by k_build_matches
+  if (ps & 1) stat = RPE_STATUS_NO_DESCRIPTORS;
   else if (M < 5) stat = RPE_STATUS_INSUFFICIENT_MATCHES;
   else if (rinfo != nullptr && rinfo[pair * 4] == 0) stat = RPE_STATUS_E_FAILED;
-  uint32_t fl = 0;
-  if (img_flags != nullptr) fl = img_flags[pstep * pair] | img_flags[pstep * pair + 1];
+  const uint32_t fl = (uint32_t)ps & RPE_STATUS_FLAG_OVERFLOW;
   if (stat != RPE_STATUS_OK) {
     if (tid < 9) R_out[pair * 9 + tid] = 0.0;
     if (tid < 3) { t_out[pair * 3 + tid] = 0.0; euler_out[pair * 3 + tid] = 0.0; }
@@ -250,8 +250,8 @@ k_pose(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npt
 }
 
 void launch_pose(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, RansacParams rp,
-                 const uint32_t* img_flags, const int32_t* kp_n, int pstep, cudaStream_t s, int* launches) {
-  k_pose<<<n_pairs, kPoseThreads, 0, s>>>(mb.m_n, mcap, gb.npts, gb.E, gb.rinfo, rp, img_flags, kp_n, pstep, gb.R, gb.t,
+                 const int32_t* pstat, cudaStream_t s, int* launches) {
+  k_pose<<<n_pairs, kPoseThreads, 0, s>>>(mb.m_n, mcap, gb.npts, gb.E, gb.rinfo, rp, pstat, gb.R, gb.t,
                                           gb.euler, gb.pose_cnt, gb.pmask, gb.status);
   ++*launches;
 }

@@ -160,7 +160,8 @@ k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, 
                 int kp_stride, int pstep, const uint32_t* __restrict__ fwd1, const uint32_t* __restrict__ fwd2,
                 const uint32_t* __restrict__ bwd1, int mode, double ratio, int max_matches, int mcap,
                 int sort_cap, int32_t* __restrict__ m_q, int32_t* __restrict__ m_t, int32_t* __restrict__ m_d,
-                int32_t* __restrict__ m_n, float* __restrict__ pts1, float* __restrict__ pts2) {
+                int32_t* __restrict__ m_n, float* __restrict__ pts1, float* __restrict__ pts2,
+                const uint32_t* __restrict__ img_flags, int32_t* __restrict__ pstat) {
   extern __shared__ uint32_t s_keys[];          // sort_cap entries
   __shared__ uint32_t s_hist[258];
   __shared__ uint32_t s_warp[kBuildThreads / 32];
@@ -249,7 +250,14 @@ k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, 
     pts1[2 * o] = x1[q]; pts1[2 * o + 1] = y1[q];
     pts2[2 * o] = x2[t]; pts2[2 * o + 1] = y2[t];
   }
-  if (tid == 0) m_n[pair] = (int32_t)n;
+  if (tid == 0) {
+    m_n[pair] = (int32_t)n;
+    // what k_pose needs to know about the two images, so that the geometry tail never touches the ORB
+    // buffers (the next batch's ORB may already be overwriting them): bit 0 = an image without
+    // descriptors, bit 8 = a candidate / tie list overflowed
+    const uint32_t fl = img_flags != nullptr ? (img_flags[v1] | img_flags[v2]) : 0u;
+    pstat[pair] = ((n1 == 0 || n2 == 0) ? 1 : 0) | (fl ? RPE_STATUS_FLAG_OVERFLOW : 0);
+  }
 }
 
 void launch_build_matches(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int mcap, int sort_cap,
@@ -258,7 +266,7 @@ void launch_build_matches(const OrbBuffers& ob, const MatchBuffers& mb, int kp_s
   k_build_matches<<<n_pairs, kBuildThreads, (size_t)sort_cap * 4, s>>>(
       ob.kp_x, ob.kp_y, ob.kp_n, kp_stride, pstep, mb.fwd1, mb.fwd2, mb.bwd1, mode, ratio, max_matches, mcap,
       sort_cap,
-      mb.m_q, mb.m_t, mb.m_d, mb.m_n, mb.pts1, mb.pts2);
+      mb.m_q, mb.m_t, mb.m_d, mb.m_n, mb.pts1, mb.pts2, ob.img_flags, mb.pstat);
   ++*launches;
 }
 

@@ -10,8 +10,10 @@
 //   kp_*         f32/i32 [NI][kp_stride]   final keypoints, canonical (octave, y, x) order; kp_n [NI]
 //   desc         u8  [NI][kp_stride][32]
 //   fwd1/fwd2/bwd1 u32 [NP][kp_stride]     packed (dist<<20 | index) nearest / second nearest
-//   m_q/m_t/m_d  i32 [NP][mcap], pts1/pts2 f32 [NP][mcap][2], npts f64 [NP][mcap][4], m_n [NP]
+//   m_q/m_t/m_d  i32 [NP][mcap], pts1/pts2 f32 [NP][mcap][2], npts f64 [NP][mcap][4], m_n, pstat [NP]
 //   E f64 [NP][9], rmask/pmask u8 [NP][mcap], rinfo i32 [NP][4], R/t/euler f64, status i32 [NP]
+// Everything from m_q down exists TWICE (set = batch sequence number & 1): the geometry tail of batch n
+// (RANSAC, recoverPose, D2H; its own stream) runs under the ORB / matcher kernels of batch n + 1.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -76,6 +78,7 @@ struct MatchBuffers {
   uint32_t* fwd1; uint32_t* fwd2; uint32_t* bwd1;
   int32_t* m_q; int32_t* m_t; int32_t* m_d; int32_t* m_n;
   float* pts1; float* pts2;
+  int32_t* pstat;   // [NP] per pair: bit 0 = an image without descriptors, RPE_STATUS_FLAG_OVERFLOW = list overflow
 };
 
 struct GeomBuffers {
@@ -121,7 +124,7 @@ void launch_normalize(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, i
 void launch_ransac(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, const double* dK,
                    RansacParams rp, cudaStream_t s, int* launches);
 void launch_pose(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, RansacParams rp,
-                 const uint32_t* img_flags, const int32_t* kp_n, int pstep, cudaStream_t s, int* launches);
+                 const int32_t* pstat, cudaStream_t s, int* launches);
 int setup_orb_attributes(int sort_cap);
 int setup_match_attributes(int sort_cap);
 int setup_geom_attributes();

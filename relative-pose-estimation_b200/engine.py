@@ -59,6 +59,7 @@ class Engine:
         L.check(self._lib.rpe_get_capacity(self._h, C.byref(kc), C.byref(mc)), "rpe_get_capacity")
         self.kp_cap, self.match_cap = kc.value, mc.value
         self._fmt = (1, L.GRAY_CVTCOLOR)
+        self._pending = []                    # submitted, not yet waited-for batches (oldest first; at most 2)
         self.gray_mode = L.GRAY_CVTCOLOR      # arithmetic used when BGR images are passed (see set_input_format)
 
     def close(self):
@@ -172,7 +173,7 @@ class Engine:
         R, t, e, st, info = self._outputs(B)
         L.check(self._lib.rpe_submit_batch(self._h, p1, p2, B, H, W, frames.strides[1], _ptr(K), _ptr(R), _ptr(t),
                                            _ptr(e), _ptr(st), _ptr(info)), "rpe_submit_batch")
-        self._pending = ({"R": R, "t": t, "euler": e, "status": st, "info": info}, frames, K)
+        self._pending.append(({"R": R, "t": t, "euler": e, "status": st, "info": info}, frames, K))
         return self
 
     def submit_device(self, dev_ptr: int, img_stride: int, B: int, H: int, W: int, pitch: int, K):
@@ -182,14 +183,15 @@ class Engine:
         L.check(self._lib.rpe_submit_batch_device(self._h, C.c_void_p(dev_ptr), img_stride, B, H, W, pitch, _ptr(K),
                                                   _ptr(R), _ptr(t), _ptr(e), _ptr(st), _ptr(info)),
                 "rpe_submit_batch_device")
-        self._pending = ({"R": R, "t": t, "euler": e, "status": st, "info": info}, None, K)
+        self._pending.append(({"R": R, "t": t, "euler": e, "status": st, "info": info}, None, K))
         return self
 
     def wait(self):
-        """Block until the submitted batch is done (rpe_wait_batch) and return its result dict."""
+        """Block until the OLDEST submitted batch is done (rpe_wait_batch) and return its result dict.
+        Two batches may be pending per engine: the second one's upload and ORB / matcher kernels run under
+        the first one's RANSAC / recoverPose tail."""
         L.check(self._lib.rpe_wait_batch(self._h), "rpe_wait_batch")
-        out, self._pending = self._pending[0], None
-        return out
+        return self._pending.pop(0)[0]
 
     def estimate_batch_device(self, dev_ptr: int, img_stride: int, B: int, H: int, W: int, pitch: int, K):
         """Inputs resident in device memory (e.g. a torch uint8 CUDA tensor's data_ptr())."""
@@ -230,7 +232,7 @@ class Engine:
         R, t, e, st, info = self._outputs(F - 1)
         L.check(self._lib.rpe_submit_sequence(self._h, ptrs, F, H, W, pitch, _ptr(K), _ptr(R), _ptr(t), _ptr(e),
                                               _ptr(st), _ptr(info)), "rpe_submit_sequence")
-        self._pending = ({"R": R, "t": t, "euler": e, "status": st, "info": info}, keep, K)
+        self._pending.append(({"R": R, "t": t, "euler": e, "status": st, "info": info}, keep, K))
         return self
 
     def submit_sequence_device(self, dev_ptr: int, img_stride: int, F: int, H: int, W: int, pitch: int, K):
@@ -240,7 +242,7 @@ class Engine:
         L.check(self._lib.rpe_submit_sequence_device(self._h, C.c_void_p(dev_ptr), img_stride, F, H, W, pitch,
                                                      _ptr(K), _ptr(R), _ptr(t), _ptr(e), _ptr(st), _ptr(info)),
                 "rpe_submit_sequence_device")
-        self._pending = ({"R": R, "t": t, "euler": e, "status": st, "info": info}, None, K)
+        self._pending.append(({"R": R, "t": t, "euler": e, "status": st, "info": info}, None, K))
         return self
 
     def estimate_sequence_device(self, dev_ptr: int, img_stride: int, F: int, H: int, W: int, pitch: int, K):

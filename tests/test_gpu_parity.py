@@ -270,8 +270,8 @@ def test_pipeline_chunks_do_not_change_results(engine):
 
 
 def test_submit_wait_equals_blocking_call(engine):
-    """rpe_submit_batch / rpe_wait_batch over two handles in flight == the blocking call; a second
-    submit on a busy handle and stage calls while a batch is pending are refused."""
+    """rpe_submit_batch / rpe_wait_batch, two batches pending on one handle plus a second handle in flight ==
+    the blocking calls; a third submit on a busy handle and stage calls while a batch is pending are refused."""
     import rpe_b200
     from rpe_b200._lib import RpeError
     a, b, c = load_gray("sim_000000.png"), load_gray("sim_000015.png"), load_gray("sim_000030.png")
@@ -284,15 +284,37 @@ def test_submit_wait_equals_blocking_call(engine):
     try:
         engine.submit_interleaved(frames1, K)
         other.submit_interleaved(frames2, K)
+        engine.submit_interleaved(frames2, K)             # second pending batch on the same handle
         with pytest.raises(RpeError):
             engine.submit_interleaved(frames2, K)
         with pytest.raises(RpeError):
             engine.orb_detect(a)
-        got1, got2 = engine.wait(), other.wait()
+        with pytest.raises(RpeError):
+            engine.estimate_batch_interleaved(frames1, K)
+        got1, got2, got3 = engine.wait(), other.wait(), engine.wait()
         for k in ("R", "t", "euler", "status", "info"):
             assert np.array_equal(got1[k], want1[k]) and np.array_equal(got2[k], want2[k]), k
+            assert np.array_equal(got3[k], want2[k]), k
         with pytest.raises(RpeError):
             engine.wait()
+        # a long alternating run with two batches always in flight: every result is its own batch's
+        engine.set_pipeline(1, 2)
+        q = []
+        for i in range(9):
+            if len(q) == 2:
+                j, got = q.pop(0), engine.wait()
+                assert np.array_equal(got["R"], (want1 if j % 2 == 0 else want2)["R"]), j
+                assert np.array_equal(got["info"], (want1 if j % 2 == 0 else want2)["info"]), j
+            engine.submit_interleaved(frames1 if i % 2 == 0 else frames2, K)
+            q.append(i)
+        for j in q:
+            got = engine.wait()
+            assert np.array_equal(got["t"], (want1 if j % 2 == 0 else want2)["t"]), j
+        engine.set_pipeline(32, 3)
+        # stage accessors read the last completed batch
+        m = engine.get_stage(0, 0, 9, 0, np.int32).copy()
+        engine.estimate_batch_interleaved(frames1, K)
+        assert np.array_equal(m, engine.get_stage(0, 0, 9, 0, np.int32))
     finally:
         other.close()
 
