@@ -170,7 +170,7 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
     L.ftile0 = ftile0; ftile0 += L.ftiles_x * L.ftiles_y;
     for (int ty = 0; ty < L.ftiles_y; ++ty)
       for (int tx = 0; tx < L.ftiles_x; ++tx) G.ftab.push_back(((uint32_t)l << 24) | ((uint32_t)ty << 12) | (uint32_t)tx);
-    for (int sy = 0; sy < (L.h + 127) / 128; ++sy)
+    for (int sy = 0; sy < (L.h + 2 * kBlurRows - 1) / (2 * kBlurRows); ++sy)
       for (int sx = 0; sx < (L.w + 127) / 128; ++sx) G.btab.push_back(((uint32_t)l << 24) | ((uint32_t)sy << 12) | (uint32_t)sx);
     if (l > 0) {
       L.xtab = (int)G.taps.size(); linear_exact_taps(w[l - 1], w[l], G.taps);

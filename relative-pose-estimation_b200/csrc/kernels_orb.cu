@@ -439,17 +439,23 @@ void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_
 }
 
 // ------------------------------------------------------------------ K6: 7x7 sigma-2 blur (f32 FMA separable)
-// Register sliding window, no shared memory.  One thread = 4 adjacent columns (one output word)
-// x TWO row strips of kBlurRows rows that are walked in lockstep, so that every f32 operation
-// is a packed f32x2 instruction (FFMA2 / FADD2 / FMUL2 of sm_100: lane 0 = strip A, lane 1 =
-// strip B; each lane is an IEEE round-to-nearest f32 operation, so the results are those of the
-// scalar blur_row7 / blur_col7_sum in orb_math.cuh bit for bit).  One warp = 128 columns.
-// Per input row and strip the thread loads three words (columns x-4 .. x+7, L1-shared with its
-// neighbours), converts the ten bytes it needs with the 2^23 mantissa trick (PRMT + FADD2: no
-// I2F), runs the row pass for its four columns and keeps the last seven row results in
-// registers; the column pass and the round-to-nearest-even store come out of that window.
-// Work items (level, strip pair, segment) come from btab.
-constexpr int kBlurRows = 64;
+// One WARP = one work item (btab): 128 columns x TWO row strips of kBlurRows rows that are walked in
+// lockstep, so that every f32 operation is a packed f32x2 instruction (FFMA2 / FADD2 / FMUL2 of sm_100:
+// lane 0 = strip A, lane 1 = strip B; each lane is an IEEE round-to-nearest f32 operation, so the results
+// are those of the scalar blur_row7 / blur_col7_sum in orb_math.cuh bit for bit).
+//  (1) TMA: the warp's lanes issue one bulk copy per input row (rows y-3 .. y+n+2, reflected at the top /
+//      bottom of the level by choosing the SOURCE row; 16 bytes of halo left and right) onto the warp's own
+//      mbarrier: no registers, no software prefetch (ncu on the register-prefetch version: 18 % of the
+//      issued instructions were MOVs, stall_long_sb 25 %);
+//  (2) edge warps mirror three columns (reflect-101) into the halo in shared memory, so the row loop has
+//      no edge cases at all;
+//  (3) per row: six LDS.32 (pixels x-4 .. x+7 of both strips), ten u8 -> f32 conversions with the 2^23
+//      mantissa trick (PRMT + FADD2: no I2F), the row pass for four columns into a 7-row register window,
+//      the column pass out of that window, round-to-nearest-even by the 1.5 * 2^23 trick, one STG.32 per
+//      strip.  The loop is unrolled by 7, so the window needs no register moves.
+constexpr int kBlurSP = 160;                      // staged bytes per row: pixels x0 - 16 .. x0 + 143
+constexpr int kBlurSR = 6 + 7 * ((kBlurRows + 6) / 7);   // staged row slots per strip (loop runs in groups of 7)
+constexpr int kBlurWarpBytes = 2 * kBlurSR * kBlurSP;
 
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 __device__ __forceinline__ float2 u8x2_to_f32(uint32_t wa, uint32_t wb, uint32_t sel) {
@@ -476,100 +482,102 @@ __device__ __forceinline__ float2 blur_col7_x2(float2 r0, float2 r1, float2 r2, 
   return s;
 }
 
-__global__ void __launch_bounds__(128)
+// row pass of one staged row of both strips for this lane's four columns
+__device__ __forceinline__ void blur_rows_x2(const uint8_t* rowA, const uint8_t* rowB, float2* out) {
+  const uint32_t a0 = *reinterpret_cast<const uint32_t*>(rowA), a1 = *reinterpret_cast<const uint32_t*>(rowA + 4),
+                 a2 = *reinterpret_cast<const uint32_t*>(rowA + 8);
+  const uint32_t b0 = *reinterpret_cast<const uint32_t*>(rowB), b1 = *reinterpret_cast<const uint32_t*>(rowB + 4),
+                 b2 = *reinterpret_cast<const uint32_t*>(rowB + 8);
+  float2 v[10];   // pixels x-3 .. x+6
+  v[0] = u8x2_to_f32(a0, b0, 0x7441); v[1] = u8x2_to_f32(a0, b0, 0x7442); v[2] = u8x2_to_f32(a0, b0, 0x7443);
+  v[3] = u8x2_to_f32(a1, b1, 0x7440); v[4] = u8x2_to_f32(a1, b1, 0x7441); v[5] = u8x2_to_f32(a1, b1, 0x7442);
+  v[6] = u8x2_to_f32(a1, b1, 0x7443);
+  v[7] = u8x2_to_f32(a2, b2, 0x7440); v[8] = u8x2_to_f32(a2, b2, 0x7441); v[9] = u8x2_to_f32(a2, b2, 0x7442);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) out[c] = blur_row7_x2(v + c);
+}
+
+__global__ void __launch_bounds__(128, 4)
 k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
        const uint32_t* __restrict__ btab) {
-  const int img = blockIdx.y;
-  const int item = blockIdx.x * 4 + (threadIdx.x >> 5);
-  if (item >= g.total_bitems) return;
-  const uint32_t e = __ldg(btab + item);                   // level<<24 | strip pair<<12 | segment
+  extern __shared__ __align__(128) uint8_t s_blur[];
+  __shared__ __align__(8) uint64_t s_bar[4];
+  const int img = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int item = blockIdx.x * 4 + warp;
+  if (item >= g.total_bitems) return;                       // warps are independent: no CTA-wide barrier below
+  const uint32_t e = __ldg(btab + item);                    // level<<24 | strip pair<<12 | segment
   const LevelGeom& L = g.lv[e >> 24];
-  const int x = ((int)(e & 0xfff) * 32 + (threadIdx.x & 31)) * 4;
-  const int yA = (int)((e >> 12) & 0xfff) * (2 * kBlurRows), yB = yA + kBlurRows;
-  if (x >= L.w) return;
   const int w = L.w, h = L.h, pitch = L.pitch;
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off + x;
-  uint8_t* dst = blur + (size_t)img * g.pyr_stride + L.off + x;
-  // Columns x-3 .. x+6 that fall outside the image are mirrored (reflect-101).  The mirrored pixel
-  // always lies inside the three words a0 a1 a2 = pixels x-4 .. x+7 this thread loads anyway, so an
-  // edge thread only needs per-value (word, byte) selectors: wsel 0..2, bsel = PRMT selector.
-  const bool edge = x < 4 || x + 7 > w;
-  const int left = x >= 4 ? -4 : 0;                         // x == 0: a0 is never selected, keep the load in bounds
-  uint32_t wsel = 0, bsel[10];
-#pragma unroll
-  for (int k = 0; k < 10; ++k) {
-    const int idx = edge ? reflect101(x - 3 + k, w) - (x - 4) : k + 1;   // 0 .. 11
-    wsel |= (uint32_t)(idx >> 2) << (2 * k);
-    bsel[k] = 0x7440u | (uint32_t)(idx & 3);
-  }
+  const int x0 = (int)(e & 0xfff) * 128;
+  const int yA = (int)((e >> 12) & 0xfff) * (2 * kBlurRows), yB = yA + kBlurRows;
   const int nA = min(kBlurRows, h - yA), nB = min(kBlurRows, h - yB);   // nB may be <= 0: strip B idle
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
+  uint8_t* sA = s_blur + warp * kBlurWarpBytes;
+  uint8_t* sB = sA + kBlurSR * kBlurSP;
+  uint64_t* bar = &s_bar[warp];
+
+  // (1) stage rows: global columns [gx0, gx1) land at shared column gx0 - (x0 - 16)
+  const int gx0 = max(x0 - 16, 0), gx1 = min(x0 + 144, pitch);
+  const uint32_t rb = (uint32_t)(gx1 - gx0);
+  const int rowsA = nA + 6, rowsB = nB > 0 ? nB + 6 : 0;
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    mbar_arrive_expect_tx(bar, rb * (uint32_t)(rowsA + rowsB));
+  }
+  __syncwarp();
+  for (int r = lane; r < rowsA + rowsB; r += 32) {
+    const bool isB = r >= rowsA;
+    const int rr = isB ? r - rowsA : r;
+    const int sy = min(max(reflect101((isB ? yB : yA) - 3 + rr, h), 0), h - 1);
+    bulk_copy_g2s((isB ? sB : sA) + rr * kBlurSP + (gx0 - (x0 - 16)), src + (size_t)sy * pitch + gx0, rb, bar);
+  }
+  mbar_wait(bar, 0);
+  // (2) reflect-101 columns for the warps at the left / right border of the level
+  if (x0 == 0 || x0 + 128 + 3 > w) {
+    for (int r = lane; r < rowsA + rowsB; r += 32) {
+      uint8_t* row = (r >= rowsA ? sB + (r - rowsA) * kBlurSP : sA + r * kBlurSP) + 16 - x0;   // row[p] = pixel p
+      if (x0 == 0) { row[-1] = row[1]; row[-2] = row[2]; row[-3] = row[3]; }
+      if (x0 + 128 + 3 > w) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) row[w + k] = row[max(w - 2 - k, 0)];
+      }
+    }
+    __syncwarp();
+  }
+  // (3) rows
+  const int x = x0 + 4 * lane;
+  const uint8_t* pA = sA + 12 + 4 * lane;                  // pixels x - 4 .. x + 7 of a staged row
+  const uint8_t* pB = sB + 12 + 4 * lane;
+  uint8_t* dA = blur + (size_t)img * g.pyr_stride + L.off + (size_t)yA * pitch + x;
+  uint8_t* dB = dA + (size_t)kBlurRows * pitch;
+  const bool col_ok = x < w;
   float2 win[7][4];
 #pragma unroll
-  for (int i = 0; i < 7; ++i)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) win[i][c] = f2(0.f, 0.f);
-
-  // the six words of input row r + 2 are requested while row r is processed (the loop is otherwise
-  // bound by load latency: ncu stall_long_sb 53 % without the prefetch)
-  uint32_t pf[2][6];
-  auto fetch = [&](int r, uint32_t* o) {
-    const int rr = min(r, nA + 5);                          // stay on rows this strip pair really needs
-    const uint8_t* rowA = src + (uint32_t)(reflect101(yA - 3 + rr, h) * pitch);
-    const uint8_t* rowB = src + (uint32_t)(min(reflect101(yB - 3 + rr, h), h - 1) * pitch);   // in bounds even when idle
-    o[0] = __ldg(reinterpret_cast<const uint32_t*>(rowA + left));
-    o[1] = __ldg(reinterpret_cast<const uint32_t*>(rowA));
-    o[2] = __ldg(reinterpret_cast<const uint32_t*>(rowA + 4));
-    o[3] = __ldg(reinterpret_cast<const uint32_t*>(rowB + left));
-    o[4] = __ldg(reinterpret_cast<const uint32_t*>(rowB));
-    o[5] = __ldg(reinterpret_cast<const uint32_t*>(rowB + 4));
-  };
-  fetch(0, pf[0]);
-  fetch(1, pf[1]);
-  for (int base = 0; base < nA + 6; base += 7) {
+  for (int i = 0; i < 6; ++i) blur_rows_x2(pA + i * kBlurSP, pB + i * kBlurSP, win[i]);
+  for (int base = 0; base < nA; base += 7) {
 #pragma unroll
     for (int i = 0; i < 7; ++i) {
-      const int r = base + i;
-      if (r < nA + 6) {
-        float2 v[10];
-        const uint32_t a0 = pf[0][0], a1 = pf[0][1], a2 = pf[0][2], b0 = pf[0][3], b1 = pf[0][4], b2 = pf[0][5];
+      const int o = base + i;                               // output row of the strip; its last input row is o + 6
+      const int slot = (6 + i) % 7;
+      blur_rows_x2(pA + (o + 6) * kBlurSP, pB + (o + 6) * kBlurSP, win[slot]);
+      uint32_t oa[4], ob[4];
 #pragma unroll
-        for (int k = 0; k < 6; ++k) pf[0][k] = pf[1][k];
-        fetch(r + 2, pf[1]);
-        if (!edge) {
-          v[0] = u8x2_to_f32(a0, b0, 0x7441); v[1] = u8x2_to_f32(a0, b0, 0x7442); v[2] = u8x2_to_f32(a0, b0, 0x7443);
-          v[3] = u8x2_to_f32(a1, b1, 0x7440); v[4] = u8x2_to_f32(a1, b1, 0x7441); v[5] = u8x2_to_f32(a1, b1, 0x7442);
-          v[6] = u8x2_to_f32(a1, b1, 0x7443);
-          v[7] = u8x2_to_f32(a2, b2, 0x7440); v[8] = u8x2_to_f32(a2, b2, 0x7441); v[9] = u8x2_to_f32(a2, b2, 0x7442);
-        } else {
-#pragma unroll
-          for (int k = 0; k < 10; ++k) {
-            const uint32_t ws = (wsel >> (2 * k)) & 3u;
-            v[k] = u8x2_to_f32(ws == 0 ? a0 : (ws == 1 ? a1 : a2), ws == 0 ? b0 : (ws == 1 ? b1 : b2), bsel[k]);
-          }
-        }
-#pragma unroll
-        for (int c = 0; c < 4; ++c) win[i][c] = blur_row7_x2(v + c);
-        if (r >= 6) {
-          uint32_t oa[4], ob[4];
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const float2 sum = blur_col7_x2(win[(i + 1) % 7][c], win[(i + 2) % 7][c], win[(i + 3) % 7][c],
-                                            win[(i + 4) % 7][c], win[(i + 5) % 7][c], win[(i + 6) % 7][c], win[i][c]);
-            // 0 <= sum <= 255: adding 1.5 * 2^23 leaves rint(sum) (ties to even) in the low byte
-            const float2 o = __fadd2_rn(sum, f2(12582912.0f, 12582912.0f));
-            oa[c] = __float_as_uint(o.x);
-            ob[c] = __float_as_uint(o.y);
-          }
-          const uint32_t orow = (uint32_t)((r - 6) * pitch);
-          {
-            const uint32_t lo = __byte_perm(oa[0], oa[1], 0x0040), hi = __byte_perm(oa[2], oa[3], 0x0040);
-            *reinterpret_cast<uint32_t*>(dst + (uint32_t)(yA * pitch) + orow) = __byte_perm(lo, hi, 0x5410);
-          }
-          if (r - 6 < nB) {
-            const uint32_t lo = __byte_perm(ob[0], ob[1], 0x0040), hi = __byte_perm(ob[2], ob[3], 0x0040);
-            *reinterpret_cast<uint32_t*>(dst + (uint32_t)(yB * pitch) + orow) = __byte_perm(lo, hi, 0x5410);
-          }
-        }
+      for (int c = 0; c < 4; ++c) {
+        const float2 sum = blur_col7_x2(win[(slot + 1) % 7][c], win[(slot + 2) % 7][c], win[(slot + 3) % 7][c],
+                                        win[(slot + 4) % 7][c], win[(slot + 5) % 7][c], win[(slot + 6) % 7][c],
+                                        win[slot][c]);
+        // 0 <= sum <= 255: adding 1.5 * 2^23 leaves rint(sum) (ties to even) in the low byte
+        const float2 q = __fadd2_rn(sum, f2(12582912.0f, 12582912.0f));
+        oa[c] = __float_as_uint(q.x);
+        ob[c] = __float_as_uint(q.y);
+      }
+      if (col_ok && o < nA) {
+        const uint32_t lo = __byte_perm(oa[0], oa[1], 0x0040), hi = __byte_perm(oa[2], oa[3], 0x0040);
+        *reinterpret_cast<uint32_t*>(dA + (size_t)o * pitch) = __byte_perm(lo, hi, 0x5410);
+      }
+      if (col_ok && o < nB) {
+        const uint32_t lo = __byte_perm(ob[0], ob[1], 0x0040), hi = __byte_perm(ob[2], ob[3], 0x0040);
+        *reinterpret_cast<uint32_t*>(dB + (size_t)o * pitch) = __byte_perm(lo, hi, 0x5410);
       }
     }
   }
@@ -578,7 +586,7 @@ k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8
 void launch_blur(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   if (g.total_bitems == 0) return;
   dim3 grid((g.total_bitems + 3) / 4, n_img);
-  k_blur<<<grid, 128, 0, s>>>(g, b.pyr, b.blur, b.btab);
+  k_blur<<<grid, 128, 4 * kBlurWarpBytes, s>>>(g, b.pyr, b.blur, b.btab);
   ++*launches;
 }
 
@@ -701,6 +709,7 @@ void launch_describe(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStrea
 }
 
 int setup_orb_attributes(int sort_cap) {
+  if (cudaFuncSetAttribute(k_blur, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kBlurWarpBytes) != cudaSuccess) return 1;
   return (int)cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_cap * 8);
 }
 

@@ -38,7 +38,7 @@ struct OrbGeom {
   int fast_threshold;
   int total_tiles;
   int total_ftiles;
-  int total_bitems;        // blur work items (one warp each): 128 columns x two 64-row strips
+  int total_bitems;        // blur work items (one warp each): 128 columns x two kBlurRows-row strips
   int cand_stride;
   int kp_stride;
   int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)
@@ -51,6 +51,7 @@ constexpr int kTileW = 64;
 constexpr int kTileH = 32;
 constexpr int kFastTW = 120;
 constexpr int kFastTH = 30;
+constexpr int kBlurRows = 32;    // blur work item = 128 columns x two strips of kBlurRows rows (one warp)
 constexpr int kFastOrigin = 24;  // FAST tiles start at x = y = 24 (a multiple of 4): only scores in [30, size-30) can matter
 
 struct OrbBuffers {
