@@ -11,8 +11,11 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OBJ = os.path.join(HERE, "build")
-LIB = os.path.join(HERE, "librpe_b200.so")
+# A/B builds: RPE_LIB_VARIANT=name RPE_EXTRA_DEFS="-DX=1" -> librpe_b200_name.so (default: librpe_b200.so)
+_VAR = os.environ.get("RPE_LIB_VARIANT", "")
+_VAR = "" if _VAR in ("", "base") else "_" + _VAR
+OBJ = os.path.join(HERE, "build" + _VAR)
+LIB = os.path.join(HERE, f"librpe_b200{_VAR}.so")
 SOURCES = ["kernels_orb.cu", "kernels_match.cu", "kernels_geom.cu", "engine.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-ffp-contract=off"]
@@ -47,7 +50,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(src):
         obj = os.path.join(OBJ, src.replace(".cu", ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + os.environ.get("RPE_EXTRA_DEFS", "").split() + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
