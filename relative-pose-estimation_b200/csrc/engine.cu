@@ -505,7 +505,7 @@ static int run_match(rpe_handle* h, int set, int pair0, int nb, int pstep, cudaS
   const OrbBuffers ob = orb_view(h, set, pstep * pair0);
   const MatchBuffers mb = match_view(h, set, pair0);
   mark(h, RPE_T_MATCH, prof);
-  launch_match(ob, mb, h->kp_stride, nb, pstep, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
+  launch_match(ob, mb, h->kp_stride, h->cfg.nfeatures, nb, pstep, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
   mark(h, RPE_T_MATCH_SORT, prof);
   launch_build_matches(ob, mb, h->kp_stride, h->mcap, h->sort_cap_match, nb, pstep, h->cfg.match_mode, h->cfg.ratio,
                        h->cfg.max_matches, s, &ln[RPE_T_MATCH_SORT]);
@@ -908,7 +908,7 @@ int rpe_match(rpe_handle* h, const uint8_t* desc1, int32_t n1, const uint8_t* de
   RPE_CK(cudaMemcpyAsync(h->ob.kp_n, nn, sizeof nn, cudaMemcpyHostToDevice, s));
   RPE_CK(cudaStreamSynchronize(s));   // nn is a stack buffer
   int* ln = h->launches;
-  launch_match(h->ob, h->mb[0], h->kp_stride, 1, 2, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
+  launch_match(h->ob, h->mb[0], h->kp_stride, h->cfg.nfeatures, 1, 2, h->cfg.match_mode, s, &ln[RPE_T_MATCH]);
   launch_build_matches(h->ob, h->mb[0], h->kp_stride, h->mcap, h->sort_cap_match, 1, 2, h->cfg.match_mode, h->cfg.ratio,
                        h->cfg.max_matches, s, &ln[RPE_T_MATCH_SORT]);
   RPE_CK(cudaGetLastError());

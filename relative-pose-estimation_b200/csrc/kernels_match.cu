@@ -28,18 +28,27 @@ __device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) {
 // kFma: keys built with multiply-adds (FMA pipe) and two train descriptors folded per top-2 update;
 // kMix (with kFma): the even train descriptor of each pair uses three carry-save adders + five POPCs, the odd
 // one four adders + four POPCs, which balances the ALU pipe (LOP3) against the XU pipe (POPC)
-template <bool kTop2, bool kCsa4, bool kFma, bool kMix = false>
+// kLin (with kFma): operands in the linearly pre-combined layout of match_math.cuh (hamming_mix): queries are
+// rewritten in registers, train descriptors when a thread stages them in shared memory (one descriptor per
+// thread); 13 LOP3 + 4 POPC per distance
+template <bool kTop2, bool kCsa4, bool kFma, bool kMix = false, bool kLin = false>
 __global__ void __launch_bounds__(kMatchThreads)
 k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride, int pstep, uint32_t m20,
-          uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
+          int nsplit, uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
   __shared__ uint4 s_train[kTrainTile * 2];
   const int pair = blockIdx.y;
   const int dir = blockIdx.z;                  // 0: view1 -> view2, 1: view2 -> view1
   // image slots of the two views: pstep = 2 (pair batch: 2p, 2p+1) or 1 (consecutive frames: p, p+1)
   const int qi = pstep * pair + dir, ti = pstep * pair + 1 - dir;
-  const int nq = kp_n[qi], nt = kp_n[ti];
-  const int q0 = blockIdx.x * kQPB;
+  const int nq = kp_n[qi], nt_all = kp_n[ti];
+  // blockIdx.x = query block * nsplit + split: each CTA scans one slice of the train set (finer work units: the
+  // last wave of a launch stays full); slices are merged with atomicMin on the packed keys, see below
+  const int split = nsplit > 1 ? blockIdx.x % nsplit : 0;
+  const int q0 = (nsplit > 1 ? blockIdx.x / nsplit : blockIdx.x) * kQPB;
   if (q0 >= nq) return;
+  const int slice = nsplit > 1 ? (((nt_all + nsplit - 1) / nsplit + 1) & ~1) : nt_all;
+  const int tbeg = split * slice, nt = min(nt_all, tbeg + slice);
+  if (tbeg >= nt && nsplit > 1) return;
   const uint4* dq = reinterpret_cast<const uint4*>(desc + (size_t)qi * kp_stride * 32);
   const uint4* dt = reinterpret_cast<const uint4*>(desc + (size_t)ti * kp_stride * 32);
   const int tid = threadIdx.x;
@@ -52,13 +61,25 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
     const uint4 a = dq[2 * qq], b = dq[2 * qq + 1];
     q[k][0] = a.x; q[k][1] = a.y; q[k][2] = a.z; q[k][3] = a.w;
     q[k][4] = b.x; q[k][5] = b.y; q[k][6] = b.z; q[k][7] = b.w;
+    if (kLin) hamming_mix(q[k]);
     best1[k] = 0xffffffffu;
     best2[k] = 0xffffffffu;
   }
-  for (int t0 = 0; t0 < nt; t0 += kTrainTile) {
+  static_assert(kTrainTile == kMatchThreads, "one staged train descriptor per thread");
+  for (int t0 = tbeg; t0 < nt; t0 += kTrainTile) {
     const int tn = min(kTrainTile, nt - t0);
     __syncthreads();
-    for (int i = tid; i < tn * 2; i += kMatchThreads) s_train[i] = dt[2 * t0 + i];
+    if (kLin) {
+      if (tid < tn) {
+        const uint4 a = dt[2 * (t0 + tid)], b = dt[2 * (t0 + tid) + 1];
+        uint32_t d[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        hamming_mix(d);
+        s_train[2 * tid] = make_uint4(d[0], d[1], d[2], d[3]);
+        s_train[2 * tid + 1] = make_uint4(d[4], d[5], d[6], d[7]);
+      }
+    } else {
+      for (int i = tid; i < tn * 2; i += kMatchThreads) s_train[i] = dt[2 * t0 + i];
+    }
     __syncthreads();
     if (kFma) {
       // pairs of train descriptors: with m <= M the two new keys, the two smallest of {best1, best2, m, M}
@@ -69,8 +90,10 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
         const uint4 a0 = s_train[2 * j], b0 = s_train[2 * j + 1], a1 = s_train[2 * j + 2], b1 = s_train[2 * j + 3];
 #pragma unroll
         for (int k = 0; k < kQPT; ++k) {
-          const uint32_t k0 = hamming256_key<kCsa4 && !kMix>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20);
-          const uint32_t k1 = hamming256_key<kCsa4 || kMix>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20);
+          const uint32_t k0 = kLin ? hamming256_mixed_key<kCsa4 && !kMix>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20)
+                                   : hamming256_key<kCsa4 && !kMix>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20);
+          const uint32_t k1 = kLin ? hamming256_mixed_key<kCsa4 || kMix>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20)
+                                   : hamming256_key<kCsa4 || kMix>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20);
           if (kTop2) {
             const uint32_t m = min(k0, k1), M = max(k0, k1);
             best2[k] = umin3(max(best1[k], m), best2[k], M);
@@ -84,7 +107,8 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
         const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
 #pragma unroll
         for (int k = 0; k < kQPT; ++k) {
-          const uint32_t key = hamming256_key<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20);
+          const uint32_t key = kLin ? hamming256_mixed_key<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20)
+                                    : hamming256_key<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20);
           if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
           best1[k] = min(best1[k], key);
         }
@@ -108,27 +132,59 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
   for (int k = 0; k < kQPT; ++k) {
     const int qq = q0 + tid + k * kMatchThreads;
     if (qq < nq) {
-      o1[qq] = best1[k];
-      if (kTop2) fwd2[(size_t)pair * kp_stride + qq] = best2[k];
+      if (nsplit > 1) {
+        // outputs preset to 0xffffffff.  Every key except the overall minimum loses one atomicMin on o1 (as
+        // the new value or as the displaced old one) and is then offered to the second-nearest slot
+        const uint32_t old = atomicMin(&o1[qq], best1[k]);
+        if (kTop2) {
+          uint32_t* o2 = fwd2 + (size_t)pair * kp_stride + qq;
+          const uint32_t loser = max(old, best1[k]);
+          if (loser != 0xffffffffu) atomicMin(o2, loser);
+          if (best2[k] != 0xffffffffu) atomicMin(o2, best2[k]);
+        }
+      } else {
+        o1[qq] = best1[k];
+        if (kTop2) fwd2[(size_t)pair * kp_stride + qq] = best2[k];
+      }
     }
   }
 }
 
-void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int pstep, int mode,
-                  cudaStream_t s, int* launches) {
+// train-set slices per query block.  Finer work units keep every SM busy to the end of the launch (B200, 128 pairs x
+// 5000 x 5000: 3.58 / 3.41 / 3.38 ms with 1 / 4 / 8 slices); a slice keeps >= ~5 shared-memory tiles of work so
+// that loading the queries and the three atomics per query stay negligible
+static int pick_nsplit(int nfeatures) {
+  static const int forced = getenv("RPE_MATCH_SPLIT") ? atoi(getenv("RPE_MATCH_SPLIT")) : 0;   // tuning knob
+  if (forced > 0) return forced;
+  return max(1, min(32, (nfeatures + 5 * kTrainTile / 2) / (5 * kTrainTile)));
+}
+
+void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int nfeatures, int n_pairs, int pstep,
+                  int mode, cudaStream_t s, int* launches) {
   const int qblocks = (kp_stride + kQPB - 1) / kQPB;
-  static const int variant = getenv("RPE_MATCH_VARIANT") ? atoi(getenv("RPE_MATCH_VARIANT")) : 4;   // tuning knob (B200: 4.14 / 4.25 / 3.96 / 3.95 / 3.84 ms for 0..4)
+  static const int variant = getenv("RPE_MATCH_VARIANT") ? atoi(getenv("RPE_MATCH_VARIANT")) : 6;   // tuning knob (B200: 4.14 / 4.25 / 3.96 / 3.95 / 3.84 / 3.60 / 3.58 / 3.92 ms for 0..7)
   const bool top2 = mode == RPE_MATCH_RATIO;
-  dim3 grid(qblocks, n_pairs, top2 ? 1 : 2);
+
   // 0: CSA3, 1: CSA4, 2: CSA3 + FMA-pipe keys + paired update, 3: CSA4 + FMA-pipe keys + paired update,
   // 4: as 2 / 3 with CSA3 and CSA4 alternating
-  auto k = top2 ? (variant == 1 ? k_hamming<true, true, false> : variant == 2 ? k_hamming<true, false, true>
+  // 5: pre-combined operands, CSA4 (13 LOP3 + 4 POPC); 6: pre-combined, CSA3 / CSA4 alternating; 7: pre-combined, CSA3
+  auto k = top2 ? (variant == 5 ? k_hamming<true, true, true, false, true> : variant == 6 ? k_hamming<true, false, true, true, true>
+                   : variant == 7 ? k_hamming<true, false, true, false, true> : variant == 1 ? k_hamming<true, true, false> : variant == 2 ? k_hamming<true, false, true>
                    : variant == 3 ? k_hamming<true, true, true> : variant == 4 ? k_hamming<true, false, true, true>
                    : k_hamming<true, false, false>)
-                : (variant == 1 ? k_hamming<false, true, false> : variant == 2 ? k_hamming<false, false, true>
+                : (variant == 5 ? k_hamming<false, true, true, false, true> : variant == 6 ? k_hamming<false, false, true, true, true>
+                   : variant == 7 ? k_hamming<false, false, true, false, true> : variant == 1 ? k_hamming<false, true, false> : variant == 2 ? k_hamming<false, false, true>
                    : variant == 3 ? k_hamming<false, true, true> : variant == 4 ? k_hamming<false, false, true, true>
                    : k_hamming<false, false, false>);
-  k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, mb.fwd1, mb.fwd2, mb.bwd1);
+  const int ndir = top2 ? 1 : 2;
+  const int nsplit = pick_nsplit(min(nfeatures, kp_stride));
+  if (nsplit > 1) {
+    const size_t bytes = (size_t)n_pairs * kp_stride * sizeof(uint32_t);
+    cudaMemsetAsync(mb.fwd1, 0xff, bytes, s);
+    cudaMemsetAsync(top2 ? mb.fwd2 : mb.bwd1, 0xff, bytes, s);
+  }
+  dim3 grid(qblocks * nsplit, n_pairs, ndir);
+  k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, nsplit, mb.fwd1, mb.fwd2, mb.bwd1);
   ++*launches;
 }
 

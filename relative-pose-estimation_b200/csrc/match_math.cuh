@@ -80,6 +80,53 @@ RPE_HD uint32_t hamming256_key(const uint32_t q[8], uint32_t t0, uint32_t t1, ui
   return key;
 }
 
+// ---- linearly pre-combined operands ("mixed" layout) -------------------------------------------------
+// XOR is linear, so any XOR-combination of the words of x = q ^ t equals the same combination of q's words
+// XOR the same combination of t's.  hamming_mix() rewrites a descriptor d[0..7] in place as
+//   m = { d0, d1, d0^d1^d2, d3, d4, d3^d4^d5, d0^..^d6, d7 }
+// (an invertible map, done once per descriptor when it is loaded), after which the SUM outputs of the three
+// carry-save adders are single XORs of mixed words and the CARRY outputs follow from two addends and the sum
+// (maj(a, b, a^b^s) = LOP3 0xD4 of (a, b, s)): 13 LOP3 + 4 POPC per 256-bit distance instead of 16 + 4, and the
+// words x2, x5, x6 are never formed.  Exact integer arithmetic.
+RPE_HD uint32_t carry_from_sum(uint32_t a, uint32_t b, uint32_t s) {   // maj(a, b, c) given s = a ^ b ^ c
+#if defined(__CUDA_ARCH__)
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xD4;" : "=r"(d) : "r"(a), "r"(b), "r"(s));
+  return d;
+#else
+  const uint32_t c = a ^ b ^ s;
+  return (a & b) | (a & c) | (b & c);
+#endif
+}
+RPE_HD void hamming_mix(uint32_t d[8]) {
+  const uint32_t m2 = d[0] ^ d[1] ^ d[2], m5 = d[3] ^ d[4] ^ d[5];
+  d[6] = m2 ^ m5 ^ d[6];
+  d[2] = m2;
+  d[5] = m5;
+}
+// q and t0..t7 in the mixed layout; kCsa4 as above (false: 11 LOP3 + 5 POPC)
+template <bool kCsa4>
+RPE_HD uint32_t hamming256_mixed_key(const uint32_t q[8], uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3,
+                                     uint32_t t4, uint32_t t5, uint32_t t6, uint32_t t7, uint32_t idx, uint32_t m20) {
+  const uint32_t x0 = q[0] ^ t0, x1 = q[1] ^ t1, s0 = q[2] ^ t2;
+  const uint32_t x3 = q[3] ^ t3, x4 = q[4] ^ t4, s1 = q[5] ^ t5;
+  const uint32_t s2 = q[6] ^ t6, x7 = q[7] ^ t7;
+  const uint32_t c0 = carry_from_sum(x0, x1, s0), c1 = carry_from_sum(x3, x4, s1), c2 = carry_from_sum(s0, s1, s2);
+  const uint32_t m21 = 2u * m20, m22 = 4u * m20;
+  uint32_t key = popc32(s2) * m20 + idx;
+  key = popc32(x7) * m20 + key;
+  if (kCsa4) {
+    const uint32_t s3 = xor3(c0, c1, c2), c3 = maj3(c0, c1, c2);
+    key = popc32(s3) * m21 + key;
+    key = popc32(c3) * m22 + key;
+  } else {
+    key = popc32(c0) * m21 + key;
+    key = popc32(c1) * m21 + key;
+    key = popc32(c2) * m21 + key;
+  }
+  return key;
+}
+
 // reference form (tests): eight independent popcounts
 RPE_HD uint32_t hamming256_plain(const uint32_t q[8], const uint32_t t[8]) {
   uint32_t d = 0;

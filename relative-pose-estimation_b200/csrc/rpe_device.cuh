@@ -115,7 +115,7 @@ void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_
 void launch_blur(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
 void launch_describe(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches);
 // pstep: image slots of pair p are pstep*p and pstep*p + 1 (2 = pair batch, 1 = consecutive frames)
-void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int n_pairs, int pstep, int mode,
+void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int nfeatures, int n_pairs, int pstep, int mode,
                   cudaStream_t s, int* launches);
 void launch_build_matches(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int mcap,
                           int sort_cap, int n_pairs, int pstep, int mode, double ratio, int max_matches,

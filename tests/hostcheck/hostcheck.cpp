@@ -16,6 +16,14 @@ void hc_hamming(const uint32_t* q, int nq, const uint32_t* t, int nt, int mode, 
     for (int j = 0; j < nt; ++j) {
       const uint32_t* a = q + 8 * i;
       const uint32_t* b = t + 8 * j;
+      if (mode == 5 || mode == 6) {   // linearly pre-combined operands (hamming_mix), 4- / 3-adder forms
+        uint32_t am[8], bm[8];
+        memcpy(am, a, 32); memcpy(bm, b, 32);
+        hamming_mix(am); hamming_mix(bm);
+        out[i * nt + j] = mode == 5 ? (int)(hamming256_mixed_key<true>(am, bm[0], bm[1], bm[2], bm[3], bm[4], bm[5], bm[6], bm[7], 0u, 1u << 20) >> 20)
+                                    : (int)(hamming256_mixed_key<false>(am, bm[0], bm[1], bm[2], bm[3], bm[4], bm[5], bm[6], bm[7], 0u, 1u << 20) >> 20);
+        continue;
+      }
       out[i * nt + j] = mode == 0   ? (int)hamming256<false>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7])
                         : mode == 1 ? (int)hamming256<true>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7])
                         : mode == 3 ? (int)(hamming256_key<false>(a, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7], 0u, 1u << 20) >> 20)

@@ -159,7 +159,7 @@ def test_hamming_carry_save_forms_are_exact():
     q[0] = 0; q[1] = 255; t[0] = 0; t[1] = 255; t[2] = q[5]
     q[2] = np.unpackbits(np.arange(32, dtype=np.uint8))[:32] * 255     # sparse / dense word mixes
     want = np.unpackbits(q[:, None, :] ^ t[None, :, :], axis=2).sum(axis=2).astype(np.int32)
-    for mode in (0, 1, 2, 3, 4):          # 3 / 4: the multiply-add key forms (hamming256_key)
+    for mode in (0, 1, 2, 3, 4, 5, 6):    # 3 / 4: the multiply-add key forms (hamming256_key); 5 / 6: pre-combined operands
         assert np.array_equal(hc.hamming(q, t, mode), want), mode
     assert want[1, 0] == 256 and want[0, 0] == 0 and want[5, 2] == 0
 
