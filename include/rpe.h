@@ -187,6 +187,22 @@ int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const 
                      int32_t m, const double K[9], double* R, double* t, double* euler,
                      int32_t* count, uint8_t* mask);
 
+/* replaces PoseEvaluator.evaluate_sequence + compute_summary_statistics (reference:
+ * src/core/pose_evaluator.py:32-134, :136-157) with rotation_error / translation_direction_error /
+ * euler_to_rotation (reference: src/utils/geometry.py:128-174, :82-125, :208-236), on the device.
+ * Host inputs, n frames: est_R[n*9] (world rotations as BatchProcessor composes them), est_t[n*3],
+ * est_euler[n*3] and gt_euler[n*3] = (yaw, pitch, roll) degrees, gt_pos[n*3] = (x, y, z).
+ * errors[n*5] = roll, pitch, yaw (wrapped to [0, 180]), rotation, translation-direction error in degrees (the
+ * last against gt_pos[i] - gt_pos[i-1]; 0 for i = 0); summary[5*5] = per metric, in that order: mean, std
+ * (population), median, max, min.  Either output may be NULL. */
+int rpe_evaluate_sequence(rpe_handle* h, int32_t n, const double* est_R, const double* est_t,
+                          const double* est_euler, const double* gt_euler, const double* gt_pos,
+                          int32_t euler_convention, double* errors, double* summary);
+
+/* the summary half alone (compute_summary_statistics, reference: src/core/pose_evaluator.py:136-157) over a
+ * host errors[n*5] table laid out as above */
+int rpe_summarize_errors(rpe_handle* h, int32_t n, const double* errors, double* summary);
+
 /* intermediate results of the LAST batch call, for stage-wise parity:
  * copies up to *n bytes to `out` and stores the byte count in *n.  `view` selects frame pair + view of a
  * sequence call (image slot pair + view) or view 1 / 2 of a pair-batch call (slot 2*pair + view). */

@@ -16,7 +16,7 @@ _VAR = os.environ.get("RPE_LIB_VARIANT", "")
 _VAR = "" if _VAR in ("", "base") else "_" + _VAR
 OBJ = os.path.join(HERE, "build" + _VAR)
 LIB = os.path.join(HERE, f"librpe_b200{_VAR}.so")
-SOURCES = ["kernels_orb.cu", "kernels_match.cu", "kernels_geom.cu", "engine.cu"]
+SOURCES = ["kernels_orb.cu", "kernels_match.cu", "kernels_geom.cu", "kernels_eval.cu", "engine.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-ffp-contract=off"]
 

@@ -87,6 +87,8 @@ struct rpe_handle {
   int last_pairs = 0;
   // input format of the batch / sequence calls (rpe_set_input_format) + lazily allocated BGR staging
   int in_channels = 1, gray_mode = RPE_GRAY_CVTCOLOR;
+  double* eval_buf = nullptr;   // rpe_evaluate_sequence scratch (grown on demand)
+  size_t eval_cap = 0;
   uint8_t* bgr_stage = nullptr;
   size_t bgr_stage_stride = 0, bgr_stage_imgs = 0;
   int last_pstep = 2;       // image slots of pair p in the last batch: pstep*p, pstep*p + 1
@@ -358,6 +360,7 @@ void rpe_destroy(rpe_handle* h) {
   for (void* p : h->allocs) cudaFree(p);
   for (auto& kv : h->geoms) { cudaFree(kv.second.d_taps); cudaFree(kv.second.d_ftab); cudaFree(kv.second.d_btab); }
   if (h->bgr_stage) cudaFree(h->bgr_stage);
+  if (h->eval_buf) cudaFree(h->eval_buf);
   if (h->gb[0].tr_subset) { cudaFree(h->gb[0].tr_subset); cudaFree(h->gb[0].tr_nmodels); cudaFree(h->gb[0].tr_counts); cudaFree(h->gb[0].tr_models); }
   for (int k = 0; k < rpe_handle::kDepth; ++k) {
     if (h->h_out_d[k]) cudaFreeHost(h->h_out_d[k]);
@@ -1000,6 +1003,58 @@ int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const 
   if (euler) RPE_CK(cudaMemcpy(euler, h->gb[0].euler, 3 * sizeof(double), cudaMemcpyDeviceToHost));
   if (count) RPE_CK(cudaMemcpy(count, h->gb[0].pose_cnt, sizeof(int32_t), cudaMemcpyDeviceToHost));
   if (mask && m) RPE_CK(cudaMemcpy(mask, h->gb[0].pmask, m, cudaMemcpyDeviceToHost));
+  return RPE_OK;
+}
+
+int rpe_evaluate_sequence(rpe_handle* h, int32_t n, const double* est_R, const double* est_t, const double* est_euler,
+                          const double* gt_euler, const double* gt_pos, int32_t euler_convention, double* errors,
+                          double* summary) {
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (!h || n < 1 || !est_R || !est_t || !est_euler || !gt_euler || !gt_pos) return fail(RPE_ERR_INVALID, "bad argument");
+  if (euler_convention != RPE_EULER_YUP && euler_convention != RPE_EULER_ZYX) return fail(RPE_ERR_INVALID, "bad euler convention");
+  RPE_CK(cudaSetDevice(h->device));
+  // scratch: inputs 9 + 3 + 3 + 3 + 3 doubles per frame, errors 5 per frame, summary 25; grown on demand
+  const size_t per = 21 + 5, need = (size_t)n * per + 25;
+  if (need > h->eval_cap) {
+    if (h->eval_buf) cudaFree(h->eval_buf);
+    h->eval_buf = nullptr; h->eval_cap = 0;
+    RPE_CK(cudaMalloc((void**)&h->eval_buf, need * sizeof(double)));
+    h->eval_cap = need;
+  }
+  double* d = h->eval_buf;
+  double *dR = d, *dt = dR + 9 * (size_t)n, *de = dt + 3 * (size_t)n, *dg = de + 3 * (size_t)n, *dp = dg + 3 * (size_t)n,
+         *derr = dp + 3 * (size_t)n, *dsum = derr + 5 * (size_t)n;
+  cudaStream_t s = h->stream;
+  RPE_CK(cudaMemcpyAsync(dR, est_R, 9 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+  RPE_CK(cudaMemcpyAsync(dt, est_t, 3 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+  RPE_CK(cudaMemcpyAsync(de, est_euler, 3 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+  RPE_CK(cudaMemcpyAsync(dg, gt_euler, 3 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+  RPE_CK(cudaMemcpyAsync(dp, gt_pos, 3 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+  launch_evaluate(n, dR, dt, de, dg, dp, euler_convention, derr, dsum, s);
+  RPE_CK(cudaGetLastError());
+  if (errors) RPE_CK(cudaMemcpyAsync(errors, derr, 5 * (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (summary) RPE_CK(cudaMemcpyAsync(summary, dsum, 25 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  RPE_CK(cudaStreamSynchronize(s));
+  return RPE_OK;
+}
+
+int rpe_summarize_errors(rpe_handle* h, int32_t n, const double* errors, double* summary) {
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (!h || n < 1 || !errors || !summary) return fail(RPE_ERR_INVALID, "bad argument");
+  RPE_CK(cudaSetDevice(h->device));
+  const size_t need = (size_t)n * 5 + 25;
+  if (need > h->eval_cap) {
+    if (h->eval_buf) cudaFree(h->eval_buf);
+    h->eval_buf = nullptr; h->eval_cap = 0;
+    RPE_CK(cudaMalloc((void**)&h->eval_buf, need * sizeof(double)));
+    h->eval_cap = need;
+  }
+  double *derr = h->eval_buf, *dsum = derr + 5 * (size_t)n;
+  RPE_CK(cudaMemcpyAsync(derr, errors, 5 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  launch_eval_summary(n, derr, dsum, h->stream);
+  RPE_CK(cudaGetLastError());
+  RPE_CK(cudaMemcpyAsync(summary, dsum, 25 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  RPE_CK(cudaStreamSynchronize(h->stream));
   return RPE_OK;
 }
 

@@ -126,6 +126,10 @@ void launch_ransac(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int 
                    RansacParams rp, cudaStream_t s, int* launches);
 void launch_pose(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, RansacParams rp,
                  const int32_t* pstat, cudaStream_t s, int* launches);
+// sequence evaluation: per-frame errors [n][5] + summary [5][5], all device pointers
+void launch_evaluate(int n, const double* est_R, const double* est_t, const double* est_euler, const double* gt_euler,
+                     const double* gt_pos, int convention, double* errors, double* summary, cudaStream_t s);
+void launch_eval_summary(int n, const double* errors, double* summary, cudaStream_t s);
 int setup_orb_attributes(int sort_cap);
 int setup_match_attributes(int sort_cap);
 int setup_geom_attributes();

@@ -310,6 +310,24 @@ class Engine:
                                            _ptr(e), C.byref(cnt), _ptr(mask)), "rpe_recover_pose")
         return {"R": R, "t": t, "euler": e, "count": cnt.value, "mask": mask[:m]}
 
+    def evaluate_sequence(self, est_R, est_t, est_euler, gt_euler, gt_pos, euler_convention: int = L.EULER_YUP):
+        """rpe_evaluate_sequence: per-frame errors (n, 5) = roll, pitch, yaw, rotation, translation-direction (deg)
+        and summary (5, 5) = per metric mean, std, median, max, min.  Angles are (yaw, pitch, roll) degrees."""
+        est_R = np.ascontiguousarray(est_R, dtype=np.float64).reshape(-1, 9)
+        n = est_R.shape[0]
+        a = [np.ascontiguousarray(v, dtype=np.float64).reshape(n, 3) for v in (est_t, est_euler, gt_euler, gt_pos)]
+        errors = np.zeros((n, 5)); summary = np.zeros((5, 5))
+        L.check(self._lib.rpe_evaluate_sequence(self._h, n, _ptr(est_R), _ptr(a[0]), _ptr(a[1]), _ptr(a[2]), _ptr(a[3]),
+                                                int(euler_convention), _ptr(errors), _ptr(summary)),
+                "rpe_evaluate_sequence")
+        return errors, summary
+
+    def summarize_errors(self, errors):
+        errors = np.ascontiguousarray(errors, dtype=np.float64).reshape(-1, 5)
+        summary = np.zeros((5, 5))
+        L.check(self._lib.rpe_summarize_errors(self._h, errors.shape[0], _ptr(errors), _ptr(summary)), "rpe_summarize_errors")
+        return summary
+
     def get_stage(self, pair: int, view: int, stage: int, arg: int = 0, dtype=np.uint8, nbytes: int | None = None):
         if nbytes is None:
             nbytes = max(self.kp_cap * 32, self.cfg.max_width * self.cfg.max_height)
