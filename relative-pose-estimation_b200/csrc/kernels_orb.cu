@@ -346,7 +346,40 @@ __device__ __forceinline__ uint32_t f32_orderable(float f) {
 
 constexpr int kSelThreads = 512;
 
-__global__ void __launch_bounds__(kSelThreads)
+// Called by the 32 lanes of one warp: the largest bin b of a 256-bin histogram with sum(hist[b..255]) >= k, and
+// k minus the count above b (b = 0 when the whole histogram holds fewer than k).  Every lane returns the result.
+__device__ __forceinline__ void warp_select_bin(const uint32_t* hist, uint32_t k, uint32_t* bin, uint32_t* k_rest) {
+  const int lane = threadIdx.x & 31;
+  uint32_t loc[8], sum = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { loc[j] = hist[255 - 8 * lane - j]; sum += loc[j]; }   // lane 0 owns the top bins
+  uint32_t inc = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  const uint32_t exc = inc - sum, total = __shfl_sync(0xffffffffu, inc, 31);
+  uint32_t b = 0, r = k - (total - loc[7]);      // fallback (lane 31: loc[7] = hist[0])
+  const bool mine = total >= k && exc < k && inc >= k;
+  if (mine) {
+    uint32_t cum = exc;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (cum + loc[j] >= k) { b = 255 - 8 * lane - j; r = k - cum; break; }
+      cum += loc[j];
+    }
+  }
+  const uint32_t who = __ballot_sync(0xffffffffu, mine);
+  const int src_lane = who ? (__ffs(who) - 1) : 31;
+  *bin = __shfl_sync(0xffffffffu, b, src_lane);
+  *k_rest = __shfl_sync(0xffffffffu, r, src_lane);
+}
+
+#ifndef RPE_SEL_MINB
+#define RPE_SEL_MINB 2
+#endif
+__global__ void __launch_bounds__(kSelThreads, RPE_SEL_MINB)
 k_select(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr,
          const uint32_t* __restrict__ cand_key, const uint32_t* __restrict__ cand_cnt,
          const uint32_t* __restrict__ hist, uint32_t* __restrict__ sel_key, float* __restrict__ sel_resp,
@@ -367,36 +400,33 @@ k_select(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr,
   uint32_t* sk = sel_key + (size_t)img * g.cand_stride + L.cand_off;
   float* sr = sel_resp + (size_t)img * g.cand_stride + L.cand_off;
 
-  // (1) threshold on the FAST score for retainBest(2 * quota)
-  if (tid == 0) {
-    uint32_t thr = 0;
-    if (n > 2 * quota) {
-      const uint32_t* h = hist + (size_t)(img * g.nlevels + level) * 256;
-      uint32_t cum = 0;
-      for (int s = 255; s >= 0; --s) {
-        cum += h[s];
-        if (cum >= 2 * quota) { thr = (uint32_t)s; break; }
-      }
-    }
-    s_thr1 = thr;
-    s_cnt = 0;
+  // (1) threshold on the FAST score for retainBest(2 * quota): the histogram goes to shared memory and warp 0
+  //     finds the cut (a one-thread scan of 256 global words cost more than the Harris pass)
+  if (tid < 256) s_hist[tid] = hist[(size_t)(img * g.nlevels + level) * 256 + tid];
+  if (tid == 0) { s_thr1 = 0; s_cnt = 0; }
+  __syncthreads();
+  if (tid < 32 && n > 2 * quota) {
+    uint32_t rest;
+    warp_select_bin(s_hist, 2 * quota, &s_thr1, &rest);
   }
   __syncthreads();
   const uint32_t thr1 = s_thr1;
-  // (2) survivors + Harris
+  // (2) survivors are compacted first, so that every lane of a warp has a Harris response to compute
+  //     (about one candidate in ten survives: computing it in place left 3 of 32 lanes busy)
   if (quota > 0) {
     for (uint32_t i = tid; i < n; i += kSelThreads) {
       const uint32_t key = ck[i];
-      if ((key >> 24) < thr1) continue;
-      const int x = key & 0xfff, y = (key >> 12) & 0xfff;
-      const float r = harris_response(src + (size_t)y * L.pitch + x, L.pitch);
-      const uint32_t j = atomicAdd(&s_cnt, 1u);
-      sk[j] = key & 0xffffffu;
-      sr[j] = r;
+      if ((key >> 24) >= thr1) sk[atomicAdd(&s_cnt, 1u)] = key & 0xffffffu;
     }
   }
   __syncthreads();
   const uint32_t n1 = s_cnt;
+  for (uint32_t j = tid; j < n1; j += kSelThreads) {
+    const uint32_t key = sk[j];
+    const int x = key & 0xfff, y = (key >> 12) & 0xfff;
+    sr[j] = harris_response(src + (size_t)y * L.pitch + x, L.pitch);
+  }
+  __syncthreads();
   // (3) quota-th largest response (exact), ties kept
   uint32_t thr_key = 0;
   if (n1 > quota) {
@@ -412,15 +442,14 @@ k_select(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr,
         if ((k & mask) == (prefix & mask)) atomicAdd(&s_hist[(k >> shift) & 255u], 1u);
       }
       __syncthreads();
-      if (tid == 0) {
-        uint32_t k = s_k;
-        int b = 255;
-        for (; b > 0; --b) {
-          if (s_hist[b] >= k) break;
-          k -= s_hist[b];
+      if (tid < 32) {
+        uint32_t b, k;
+        warp_select_bin(s_hist, s_k, &b, &k);
+        __syncwarp();
+        if (tid == 0) {
+          s_k = k;
+          s_prefix = prefix | (b << shift);
         }
-        s_k = k;
-        s_prefix = prefix | ((uint32_t)b << shift);
       }
       __syncthreads();
     }
