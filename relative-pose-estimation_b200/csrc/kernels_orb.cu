@@ -205,14 +205,16 @@ __device__ __forceinline__ void fast_issue(const OrbGeom& g, const FastTile& T, 
   const int row_bytes = min(kFastIP, L.pitch - T.astart);
   const int n_rows = min(kFastIH, L.h - (T.y0 - 4));
 #if RPE_FAST_CPASYNC
-  // 16-byte asynchronous copies (LDGSTS) by all threads, one commit group per tile
+  // 16-byte asynchronous copies (LDGSTS) by all threads, one commit group per tile.  Chunk q of this thread is
+  // (row, 16-byte column) = ((tid + 256 q) / 10, (tid + 256 q) % 10): tile-independent, the compiler hoists it
+  const uint8_t* base = T.src + (size_t)(T.y0 - 4) * L.pitch + T.astart;
 #pragma unroll
   for (int q = 0; q < (kFastIH * (kFastIP / 16) + 255) / 256; ++q) {
     const int idx = tid + 256 * q;
-    const int row = idx / (kFastIP / 16), col = idx - row * (kFastIP / 16);
-    if (row < n_rows && col * 16 < row_bytes)
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(buf + row * kFastIP + col * 16)),
-                   "l"(T.src + (size_t)(T.y0 - 4 + row) * L.pitch + T.astart + col * 16) : "memory");
+    const int row = idx / (kFastIP / 16), col16 = (idx - row * (kFastIP / 16)) * 16;
+    if (row < n_rows && col16 < row_bytes)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(buf) + row * kFastIP + col16),
+                   "l"(base + row * L.pitch + col16) : "memory");
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
 #else
@@ -273,21 +275,40 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
     const int lo = min(max(xlo - xq, 0), 4), hi = min(max(xhi - xq, 0), 4);
     const uint32_t vmask = (uint32_t)(0x80808080ull << (8 * lo)) & (uint32_t)(0x80808080ull >> (8 * (4 - hi)));
     const uint32_t* wimg = reinterpret_cast<const uint32_t*>(simg) + (ib >> 2) + lane;
+    // the four rows of the warp first, then ONE compaction: per-lane count -> warp scan -> one shared atomic per
+    // warp -> straight-line predicated stores (no per-lane loop over set bits: candidates cluster, so the loop ran
+    // to the worst lane's count)
+    uint32_t cw[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const int sr = warp * 4 + k;
       const int y = y0 - 1 + sr;
-      if (y < ylo || y >= yhi) continue;                   // warp-uniform
-      const uint32_t* row = wimg + (sr + 3) * (kFastIP / 4);
-      uint32_t cand = fast_compass4(row[-1], row[0], row[1], row[-3 * (kFastIP / 4)], row[3 * (kFastIP / 4)], t4) & vmask;
-      if (cand == 0) continue;
-      uint32_t pos = atomicAdd(&s_ncand, (uint32_t)__popc(cand));
-      const uint32_t e0 = (uint32_t)((sr << 7) | (4 * lane));
-      while (cand) {
-        const int jj = (__ffs(cand) - 1) >> 3;
-        s_cand[pos++] = (uint16_t)(e0 + jj);
-        cand &= cand - 1;
+      cw[k] = 0;
+      if (y >= ylo && y < yhi) {                           // warp-uniform
+        const uint32_t* row = wimg + (sr + 3) * (kFastIP / 4);
+        cw[k] = fast_compass4(row[-1], row[0], row[1], row[-3 * (kFastIP / 4)], row[3 * (kFastIP / 4)], t4) & vmask;
       }
+    }
+    // bit 7 - k of byte j = row k, pixel j of this lane's quad
+    const uint32_t merged = cw[0] | (cw[1] >> 1) | (cw[2] >> 2) | (cw[3] >> 3);
+    if (__any_sync(0xffffffffu, merged != 0)) {
+      const uint32_t c = (uint32_t)__popc(merged);
+      uint32_t inc = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+      }
+      uint32_t base = 0;
+      if (lane == 31) base = atomicAdd(&s_ncand, inc);
+      base = __shfl_sync(0xffffffffu, base, 31);
+      uint16_t* out = s_cand + base + inc - c;
+      const uint32_t e00 = (uint32_t)((warp * 4) << 7) | (uint32_t)(4 * lane);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj)
+          if (merged & (0x80u >> k << (8 * jj))) *out++ = (uint16_t)(e00 + (k << 7) + jj);
     }
     __syncthreads();
 
