@@ -158,6 +158,54 @@ def cpu_reference_rate(n_pairs: int, first_pair: int = 900000):
     return n_pairs / dt, dt, cv2.getNumThreads(), ok
 
 
+def _shard_worker(wid, steps, n, barrier, q):
+    """One host core of the process-per-core mode (SURVEY 8d ii): cv2 single-threaded, own pairs, timed loops
+    started together on a barrier."""
+    import cv2
+    from oracle.reference_path import PathConfig, ReferencePath
+    from rpe_b200.synth import synth_K, synth_pair
+    cv2.setNumThreads(1)
+    K = synth_K(CFG["W"], CFG["H"])
+    ref = ReferencePath(K, PathConfig(nfeatures=CFG["nfeatures"], nlevels=CFG["nlevels"], match_mode=CFG["match_mode"],
+                                      ratio=CFG["ratio"], max_matches=CFG["max_matches"],
+                                      ransac_max_iters=CFG["ransac_max_iters"]))
+    pairs = [synth_pair(CFG["synth_cfg"], 800000 + wid * 64 + i, CFG["W"], CFG["H"])[:2] for i in range(n)]
+    ref.estimate(*pairs[0])                       # warm-up call
+    walls = []
+    for _ in range(steps):
+        barrier.wait()
+        t0 = time.perf_counter()
+        for a, b in pairs:
+            try:
+                ref.estimate(a, b)
+            except RuntimeError:
+                pass
+        walls.append(time.perf_counter() - t0)
+    q.put((wid, walls))
+
+
+def cpu_reference_rate_sharded(steps: int, n_per_proc: int):
+    """The reference's CPU path as one single-threaded process per host core, pairs sharded over the processes:
+    the CPU's best throughput mode for a stream of independent pairs.  Returns (pairs/s, procs, seconds)."""
+    import multiprocessing as mp
+    procs = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    ctx = mp.get_context("spawn")                 # CUDA may be initialised in this process: never fork
+    barrier, q = ctx.Barrier(procs), ctx.Queue()
+    ps = [ctx.Process(target=_shard_worker, args=(w, steps, n_per_proc, barrier, q), daemon=True) for w in range(procs)]
+    for p_ in ps:
+        p_.start()
+    res = [q.get(timeout=600) for _ in ps]
+    for p_ in ps:
+        p_.join(timeout=60)
+    wall = sum(max(r[1][s] for r in res) for s in range(steps))     # per step: until the slowest core is done
+    return steps * n_per_proc * procs / wall, procs, wall
+
+
+def cv2_threads_str():
+    import cv2
+    return str(cv2.getNumThreads())
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -172,12 +220,24 @@ def run_reference(args):
         rates.append(r); t_all += dt
     value = args.steps * n / t_all
     sample = f"{n} synthetic 1280x720 pairs per step x {args.steps} steps, cv2 threads={threads}"
+    modes = {"cv2_threads": value}
+    try:
+        v2, procs, wall2 = cpu_reference_rate_sharded(args.steps, 2)
+        modes["process_per_core"] = v2
+        if v2 > value:      # report the CPU's better mode
+            value, threads, t_all = v2, procs, wall2
+            n = 2 * procs
+            sample = (f"{procs} single-threaded processes x 2 synthetic 1280x720 pairs per step x {args.steps} steps "
+                      f"(cv2 {modes['cv2_threads']:.1f} pairs/s with its own {cv2_threads_str()} threads)")
+    except Exception as e:      # the thread mode above always exists
+        modes["process_per_core_error"] = repr(e)[:200]
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps,
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f32/f64", "data": "synthetic",
            "config": {"workload": "cfg3: synthetic 1280x720 pair batch, ORB 5000, ratio 0.75, RANSAC 2000",
                       "pairs_per_step": n, **{k: CFG[k] for k in ("nfeatures", "nlevels", "match_mode", "max_matches")}},
-           "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": sample},
+           "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": sample,
+                            "modes": modes},
            "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
     print(json.dumps(out), flush=True)
@@ -342,19 +402,26 @@ def run_b200(args):
         stages["match"]["popc32_per_s"] = B * 8 * nkp * nkp / mm
     kernel_stages = ["pyramid", "fast", "select", "blur", "describe", "match", "match_sort", "ransac", "pose"]
     dom = max(kernel_stages, key=lambda k: stages[k]["ms_per_step"])
-    traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
-    except Exception:
-        pass
     # roofline object: the slowest HBM-bound kernel (pyramid / FAST / blur stream the images).  The
     # matcher, when dominant, is bound by the popc (XU) pipe, not by HBM: its pipe fraction is in `xu_pipe`.
     rf_stage = max(("pyramid", "fast", "blur"), key=lambda k: stages[k]["ms_per_step"])
+    traffic = None      # DRAM bytes per launch from the committed ncu --set full capture, scaled to this step's images
+    try:
+        per_img = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[rf_stage]["dram_bytes_per_image"]
+        traffic = per_img * 2 * B
+    except Exception:
+        pass
     sm_hz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
     popc_peak = 148 * 16 * sm_hz * 1e6          # 16 POPC lanes / clk / SM (XU pipe), 148 SMs
-    xu = {"kernel": "match", "achieved_popc32_per_s": stages["match"].get("popc32_per_s"),
-          "peak_popc32_per_s": popc_peak, "frac": (stages["match"].get("popc32_per_s") or 0.0) / popc_peak,
-          "note": "peak = 148 SMs x 16 popc/clk x median SM clock; ncu sm__inst_executed_pipe_xu confirms (profiles/)"}
+    # the kernel issues 4.5 POPC per 256-bit distance (carry-save adders fold the 8 xor words into 5 / 4 words on
+    # alternate train descriptors), not 8: the pipe fraction counts ISSUED popcounts
+    popc_issued = 4.5 / 8.0 * (stages["match"].get("popc32_per_s") or 0.0)
+    xu = {"kernel": "match", "distances_per_s": (stages["match"].get("popc32_per_s") or 0.0) / 8.0,
+          "popc_issued_per_distance": 4.5, "achieved_popc32_per_s": popc_issued,
+          "plain_form_equivalent_popc32_per_s": stages["match"].get("popc32_per_s"),
+          "peak_popc32_per_s": popc_peak, "frac": popc_issued / popc_peak,
+          "note": "peak = 148 SMs x 16 popc/clk x median SM clock; ncu sm__inst_executed_pipe_xu = 93 % and pipe_alu = "
+                  "83 % on this kernel (profiles/r01_ncu_full_b32_summary_v4.txt)"}
     roofline = {"kernel": rf_stage, "bound": "hbm", "achieved": stages[rf_stage]["gbs"], "peak": hbm_peak,
                 "unit": "GB/s", "frac": stages[rf_stage]["frac_hbm"], "traffic": traffic, "peak_source": peak_src,
                 "xu_pipe": xu, "dominant_stage": dom, "share_of_step": stages[dom]["ms_per_step"] / (ms_prof / args.steps),
@@ -369,7 +436,16 @@ def run_b200(args):
         rate, dt, threads, ok = cpu_reference_rate(args.cpu_pairs)
         cpu = {"value": rate, "unit": "pairs/s", "cores": threads, "kind": "port",
                "sample": f"{args.cpu_pairs} synthetic 1280x720 cfg3 pairs in {dt:.1f}s, cv2 {threads} threads "
-                         f"(same cv2 calls as PoseEstimator.estimate)"}
+                         f"(same cv2 calls as PoseEstimator.estimate)", "modes": {"cv2_threads": rate}}
+        try:        # the CPU's other mode: one single-threaded process per core (SURVEY 8d ii); the better one is reported
+            r2, procs, wall2 = cpu_reference_rate_sharded(1, 3)
+            cpu["modes"]["process_per_core"] = r2
+            if r2 > rate:
+                cpu.update(value=r2, cores=procs,
+                           sample=f"{procs} single-threaded processes x 3 synthetic 1280x720 cfg3 pairs in {wall2:.1f}s "
+                                  f"(same cv2 calls as PoseEstimator.estimate); cv2's own {threads} threads: {rate:.1f} pairs/s")
+        except Exception as e:
+            cpu["modes"]["process_per_core_error"] = repr(e)[:200]
 
     out = {"metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
