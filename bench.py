@@ -40,7 +40,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=128, help="pairs per GPU per step")
+    ap.add_argument("--batch", type=int, default=None, help="pairs per GPU per step (default 128; config 4: 16)")
+    ap.add_argument("--config", type=int, default=3, choices=[3, 4],
+                    help="BASELINE.json config: 3 = 1280x720 / 5000 features (the headline workload, default); "
+                         "4 = 3840x2160 / 20000 features / 8 levels (stress line item, not the bench line)")
     ap.add_argument("--cpu-pairs", type=int, default=24, help="pairs in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--inflight", type=int, default=1, help="engine handles used alternately")
@@ -234,7 +237,7 @@ def run_reference(args):
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps,
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f32/f64", "data": "synthetic",
-           "config": {"workload": "cfg3: synthetic 1280x720 pair batch, ORB 5000, ratio 0.75, RANSAC 2000",
+           "config": {"workload": workload_name(),
                       "pairs_per_step": n, **{k: CFG[k] for k in ("nfeatures", "nlevels", "match_mode", "max_matches")}},
            "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": sample,
                             "modes": modes},
@@ -408,7 +411,7 @@ def run_b200(args):
     traffic = None      # DRAM bytes per launch from the committed ncu --set full capture, scaled to this step's images
     try:
         per_img = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[rf_stage]["dram_bytes_per_image"]
-        traffic = per_img * 2 * B
+        traffic = per_img * 2 * B if CFG["synth_cfg"] == 3 else None      # the capture is of the cfg3 workload
     except Exception:
         pass
     sm_hz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
@@ -451,10 +454,10 @@ def run_b200(args):
            "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "u8/i32 (ORB, match), f32 (Harris/angle/blur), f64 (RANSAC, pose)",
            "data": "synthetic",
-           "config": {"workload": "cfg3: synthetic 1280x720 pair batch, ORB 5000 features (sf 1.1, 12 levels, FAST 15, "
-                                  "HARRIS), BF-Hamming knn2 + ratio 0.75, max_matches 500, RANSAC 5-pt 2000 iters",
+           "config": {"workload": workload_name(),
                       "pairs_per_gpu_per_step": B, "image_bytes_per_step": int(2 * B * H * W),
-                      "l2_policy": "inputs larger than L2 (236 MB of frames + 1.2 GB of pyramids per step)",
+                      "l2_policy": f"inputs larger than L2 ({2 * B * H * W / 1e6:.0f} MB of frames + "
+                                   f"{2 * B * sum(level_pixels()) / 1e9:.1f} GB of pyramids per step)",
                       "parallelism": f"{world} independent shards, no collective",
                       "pipeline": {"handles": len(engines), "batches_pending_per_handle": max(1, min(2, args.depth)),
                                    "chunk_pairs": args.chunk, "streams": args.streams},
@@ -468,8 +471,21 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def workload_name():
+    return (f"cfg{CFG['synth_cfg']}: synthetic {CFG['W']}x{CFG['H']} pair batch, ORB {CFG['nfeatures']} features (sf 1.1, "
+            f"{CFG['nlevels']} levels, FAST 15, HARRIS), BF-Hamming knn2 + ratio 0.75, max_matches {CFG['max_matches']}, "
+            f"RANSAC 5-pt {CFG['ransac_max_iters']} iters")
+
+
 def main():
+    global METRIC
     args = parse()
+    if args.config == 4:
+        CFG.update(W=3840, H=2160, nfeatures=20000, nlevels=8, synth_cfg=4)
+        METRIC = METRIC.replace("ORB 5k", "ORB 20k").replace("1280x720", "3840x2160")
+        args.no_stream = True
+    if args.batch is None:
+        args.batch = 128 if args.config == 3 else 16
     if args.impl == "reference":
         run_reference(args)
     else:
