@@ -186,6 +186,13 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
     for (int x = 0; x < w[l]; ++x)
       if (xt[x].x - xt[x & ~3].x > 6) g.resize_strip_ok = 0;
   }
+  // source rows an 8-row output strip needs: rows y0[first] .. y0[last] + 1
+  g.resize_span = 0;
+  for (int l = 1; l < c.nlevels; ++l) {
+    const int2* yt = G.taps.data() + g.lv[l].ytab;
+    for (int y = 0; y < h[l]; y += 8)
+      g.resize_span = std::max(g.resize_span, yt[std::min(y + 7, h[l] - 1)].x + 2 - yt[y].x);
+  }
   g.total_tiles = tile0;
   g.total_ftiles = ftile0;
   g.total_bitems = (int)G.btab.size();

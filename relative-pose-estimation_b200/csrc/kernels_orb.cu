@@ -3,6 +3,7 @@
 // cv2.ORB.detectAndCompute as the reference calls it (src/core/pose_estimator.py:85-91, :108).
 // Every launch covers the whole batch (grid.y / grid.z = image slot); the dense kernels
 // (FAST, blur) cover all pyramid levels in one launch through a flat tile table.
+#include <cstdlib>
 #include "rpe_device.cuh"
 #include "orb_math.cuh"
 #include "tma.cuh"
@@ -138,10 +139,100 @@ k_resize_strip(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, con
   }
 }
 
+
+// Same strip, source rows staged first: the thread requests ALL source rows of its strip (<= kResizeSrcRows rows x
+// three words) with 4-byte cp.async into its own shared-memory column and only then walks down the strip, reading
+// rows back with LDS.  k_resize_strip keeps one row in flight per thread and waits on it row after row (ncu:
+// 37 % of its stall samples on the row-advance); here one round trip covers the strip.  A thread reads only what it
+// staged itself, so cp.async.wait_group is the only synchronisation.  Chosen on the host when every strip of the
+// level chain spans <= kResizeSrcRows source rows (scale <= ~1.25), else k_resize_strip.
+constexpr int kResizeSrcRows = 11;
+constexpr int kResizeStageBytes = kResizeSrcRows * 3 * 256 * 4;
+
+__global__ void __launch_bounds__(256)
+k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,
+                int level) {
+  extern __shared__ uint32_t s_rows[];   // [kResizeSrcRows][3][256 threads]
+  const LevelGeom& d = g.lv[level];
+  const LevelGeom& s = g.lv[level - 1];
+  const int img = blockIdx.z;
+  const int tid = threadIdx.y * 32 + threadIdx.x;
+  const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int y_first = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
+  if (y_first >= d.h || x4 >= d.pitch) return;
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + s.off;
+  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
+  const int y_end = min(y_first + kResizeRows, d.h);
+  int2 ty = __ldg(&taps[d.ytab + y_first]);
+  const int ra0 = ty.x;
+  const int n_src = __ldg(&taps[d.ytab + y_end - 1]).x + 2 - ra0;      // <= kResizeSrcRows (host-checked)
+  const int xbase = __ldg(&taps[d.xtab + min(x4, d.w - 1)]).x;
+  const int abase = xbase & ~3, sh8 = (xbase & 3) * 8;
+  const int sp = s.pitch, last_row = s.h - 1;
+  {
+    const uint32_t sdst = smem_u32(s_rows + tid);
+#pragma unroll
+    for (int i = 0; i < kResizeSrcRows; ++i) {
+      if (i < n_src) {
+        const uint8_t* p = src + (size_t)min(ra0 + i, last_row) * sp + abase;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + (uint32_t)((i * 3 + k) * 256 * 4)), "l"(p + 4 * k) : "memory");
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  // horizontal taps of the four columns (while the rows are in flight)
+  uint32_t sel[4], wgt[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int2 t = __ldg(&taps[d.xtab + min(x4 + k, d.w - 1)]);
+    const uint32_t r = (uint32_t)(t.x - xbase);          // 0 .. 6 (checked on the host)
+    sel[k] = r | ((r + 1u) << 4) | 0x8800u;
+    wgt[k] = (256u - (uint32_t)t.y) | ((uint32_t)t.y << 16);
+  }
+  auto hpass = [&](int i, uint32_t* h) {                 // staged row i of this thread
+    const uint32_t* r = s_rows + i * 3 * 256 + tid;
+    const uint32_t r0 = r[0], r1 = r[256], r2 = r[512];
+    const uint32_t lo = __funnelshift_r(r0, r1, sh8), hi = __funnelshift_r(r1, r2, sh8);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = __dp2a_lo(wgt[k], __byte_perm(lo, hi, sel[k]), 0u);
+  };
+  // straight-line: the row index into the staged rows is free to be dynamic, so every output row takes its own two
+  // source rows (no walk, no register moves, no data-dependent loop); the vertical taps are loaded up front
+  int2 tys[kResizeRows];
+#pragma unroll
+  for (int j = 0; j < kResizeRows; ++j) tys[j] = __ldg(&taps[d.ytab + min(y_first + j, d.h - 1)]);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  uint8_t* out = dst + (size_t)y_first * d.pitch + x4;
+#pragma unroll
+  for (int j = 0; j < kResizeRows; ++j) {
+    if (y_first + j < y_end) {
+      uint32_t hA[4], hB[4];
+      const int rel = tys[j].x - ra0;
+      hpass(rel, hA);
+      hpass(rel + 1, hB);
+      const uint32_t cy1 = (uint32_t)tys[j].y, cy0 = 256u - cy1;
+      uint32_t v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = cy0 * hA[k] + (cy1 * hB[k] + 32768u);
+      *reinterpret_cast<uint32_t*>(out + (size_t)j * d.pitch) =
+          __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+    }
+  }
+}
+
 void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   for (int l = 1; l < g.nlevels; ++l) {
     const LevelGeom& d = g.lv[l];
-    if (g.resize_strip_ok) {
+    // first level built by k_resize_staged (0 = never).  Measured on B200, 128 pairs: from level 1: 0.95 ms, but the
+    // end-to-end rate (uploads of the next batch running beside it) drops 13.1k -> 12.9k pairs/s; from level 2:
+    // 0.99 ms and 13.3k end to end; never: 1.10 ms
+    static const int staged_from = getenv("RPE_RESIZE_STAGED") ? atoi(getenv("RPE_RESIZE_STAGED")) : 2;
+    if (g.resize_strip_ok && g.resize_span <= kResizeSrcRows && staged_from > 0 && l >= staged_from) {
+      dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
+      k_resize_staged<<<grid, block, kResizeStageBytes, s>>>(g, b.pyr, b.taps, l);
+    } else if (g.resize_strip_ok) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
       k_resize_strip<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
     } else {

@@ -42,6 +42,7 @@ struct OrbGeom {
   int cand_stride;
   int kp_stride;
   int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)
+  int resize_span;         // most source rows any 8-row output strip needs (k_resize_staged stages them all)
   int resize_strip_ok;     // every aligned group of 4 output columns taps <= 8 consecutive source bytes
   size_t pyr_stride;
   LevelGeom lv[RPE_MAX_LEVELS];
