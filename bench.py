@@ -260,6 +260,13 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: the CUDA library has no CPU fallback")
     torch.cuda.set_device(local)
+    numa_cpus = []
+    if world > 1 and os.environ.get("RPE_NUMA_BIND", "1") != "0":
+        # one process per GPU: run on, and allocate the pinned frame buffers from, the GPU's own NUMA node
+        try:
+            numa_cpus = rpe_b200.sharding.bind_host_to_gpu(rpe_b200.sharding.gpu_pci_bus_id(local))
+        except Exception:
+            numa_cpus = []
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch
@@ -459,6 +466,7 @@ def run_b200(args):
                       "l2_policy": f"inputs larger than L2 ({2 * B * H * W / 1e6:.0f} MB of frames + "
                                    f"{2 * B * sum(level_pixels()) / 1e9:.1f} GB of pyramids per step)",
                       "parallelism": f"{world} independent shards, no collective",
+                      "host_numa_binding": f"{len(numa_cpus)} cpus of the GPU's node" if numa_cpus else "none",
                       "pipeline": {"handles": len(engines), "batches_pending_per_handle": max(1, min(2, args.depth)),
                                    "chunk_pairs": args.chunk, "streams": args.streams},
                       "mean_keypoints_per_image": nkp, "ok_fraction": ok_frac},

@@ -14,6 +14,41 @@ import numpy as np
 RESULT_WIDTH = 16   # R (9) | t (3) | euler yaw,pitch,roll (3) | status (1)
 
 
+def _parse_cpulist(text: str) -> set[int]:
+    cpus: set[int] = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        a, _, b = part.partition("-")
+        cpus.update(range(int(a), int(b or a) + 1))
+    return cpus
+
+
+def bind_host_to_gpu(pci_bus_id: str) -> list[int]:
+    """Pin the calling process to the CPUs of the NUMA node its GPU hangs off (``/sys/bus/pci/devices/<id>/
+    local_cpulist``), so that the pinned frame buffers it allocates next are first-touched in node-local memory and
+    every rank's H2D stream reads its own socket's DRAM.  With one process per GPU and ~20 GB/s of uploads per rank
+    this is what keeps 8 ranks from sharing one socket's memory bandwidth.  Returns the CPU list ([] = left alone:
+    unknown device, single node, or no permission)."""
+    import os
+    try:
+        path = f"/sys/bus/pci/devices/{pci_bus_id.lower()}/local_cpulist"
+        cpus = _parse_cpulist(open(path).read()) & set(os.sched_getaffinity(0))
+        if not cpus or cpus == set(os.sched_getaffinity(0)):
+            return []
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except (OSError, ValueError, AttributeError):
+        return []
+
+
+def gpu_pci_bus_id(device: int) -> str:
+    """'dddd:bb:dd.0' of a CUDA device, as sysfs names it."""
+    import torch
+    p = torch.cuda.get_device_properties(device)
+    return f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+
+
 def shard_range(n_pairs: int, world: int, rank: int) -> tuple[int, int]:
     """Contiguous block [lo, hi) of pair indices owned by ``rank``: [r*n/G, (r+1)*n/G)."""
     if world < 1 or not 0 <= rank < world:
