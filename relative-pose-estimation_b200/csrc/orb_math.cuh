@@ -327,8 +327,15 @@ static __device__ __constant__ int8_t kBriefPattern_dev[1024] = {
 // angle in radians and cos / sin evaluated in double, as computeOrbDescriptors does
 RPE_HD void brief_steer(float angle_deg, float* a, float* b) {
   const float theta = f32_mul(angle_deg, 0.017453292519943295f);  // (float)(CV_PI/180)
+#if defined(__CUDA_ARCH__)
+  double sn, cs;                       // one range reduction for both (same polynomials as sin() / cos())
+  sincos((double)theta, &sn, &cs);
+  *a = (float)cs;
+  *b = (float)sn;
+#else
   *a = (float)cos((double)theta);
   *b = (float)sin((double)theta);
+#endif
 }
 
 // one test; t = (xa, ya, xb, yb) as four int8 packed little-endian; c = blurred level at the keypoint centre
