@@ -36,7 +36,15 @@ void launch_normalize(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, i
   ++*launches;
 }
 
-constexpr int kChunk = 64;            // hypotheses per round
+// Hypotheses per round.  The five-point solver keeps 2.5 KB of per-thread scratch in local memory (the 10 x 20
+// elimination matrix), interleaved by lane: 16 solver threads in the lower half-warp touch 40 KB, which stays in L1
+// next to the dense kernels sharing the SM; 24 and more spill out of it (B200, 128 pairs per step: 0.38 / 0.44 / 1.08 /
+// 1.11 / 1.24 / 3.2 ms for 8 / 16 / 24 / 32 / 64 / 128).  Small rounds also solve fewer hypotheses past the adaptive
+// stop.  The result does not depend on it (same RNG stream, sequential update rule replayed per round).
+#ifndef RPE_RANSAC_CHUNK
+#define RPE_RANSAC_CHUNK 16
+#endif
+constexpr int kChunk = RPE_RANSAC_CHUNK;   // hypotheses per round
 constexpr int kRansacThreads = 128;
 
 struct RansacShared {
@@ -88,13 +96,14 @@ k_ransac(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ n
     const int it0 = S.it0;
     const int nh = min(kChunk, S.niters - it0);   // hypotheses that can still matter
     // (b) minimal solver, one hypothesis per thread
-    if (tid < nh) {
+    const int hyp = tid;
+    if (hyp < nh) {
       double x1[10], x2[10];
       for (int k = 0; k < 5; ++k) {
-        const double4 p = P[S.subset[tid][k]];
+        const double4 p = P[S.subset[hyp][k]];
         x1[2 * k] = p.x; x1[2 * k + 1] = p.y; x2[2 * k] = p.z; x2[2 * k + 1] = p.w;
       }
-      S.nmodels[tid] = five_point_solve(x1, x2, &S.models[tid][0][0]);
+      S.nmodels[hyp] = five_point_solve(x1, x2, &S.models[hyp][0][0]);
     }
     __syncthreads();
     solved += nh;
