@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=None, help="pairs per GPU per step (default 128; config 4: 16)")
+    ap.add_argument("--batch", type=int, default=None, help="pairs per GPU per step (default 256, as SURVEY 8d suggests for config 3; config 4: 16)")
     ap.add_argument("--config", type=int, default=3, choices=[3, 4],
                     help="BASELINE.json config: 3 = 1280x720 / 5000 features (the headline workload, default); "
                          "4 = 3840x2160 / 20000 features / 8 levels (stress line item, not the bench line)")
@@ -493,7 +493,7 @@ def main():
         METRIC = METRIC.replace("ORB 5k", "ORB 20k").replace("1280x720", "3840x2160")
         args.no_stream = True
     if args.batch is None:
-        args.batch = 128 if args.config == 3 else 16
+        args.batch = 256 if args.config == 3 else 16
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -317,7 +317,10 @@ __device__ __forceinline__ void fast_issue(const OrbGeom& g, const FastTile& T, 
 
 constexpr int kFastTilesPerCta = 4;   // consecutive tiles of one image per CTA, TMA double-buffered
 
-__global__ void __launch_bounds__(256, 6)
+#ifndef RPE_FAST_MINB
+#define RPE_FAST_MINB 6
+#endif
+__global__ void __launch_bounds__(256, RPE_FAST_MINB)
 k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
        int n_img, uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
   __shared__ __align__(128) uint8_t simg2[2][kFastIH * kFastIP];
