@@ -899,11 +899,19 @@ k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, c
       }
     }
   }
-  __syncthreads();
-  // (2) steering coefficients
-  if (tid < nk) brief_steer(s_angle[tid], &s_a[tid], &s_b[tid]);
-  __syncthreads();
+  // a warp only ever touches its own keypoints (k = warp, warp + 4, ...): warp-level synchronisation from here on,
+  // so the four warps of the CTA drift through the phases independently
+  __syncwarp();
+  // (2) steering coefficients of this warp's keypoints, one per lane
+  if (lane < kDescKp / 4) {
+    const int k = warp + 4 * lane;
+    if (k < nk) brief_steer(s_angle[k], &s_a[k], &s_b[k]);
+  }
+  __syncwarp();
   // (3) descriptor
+#ifdef RPE_DESC_UNROLL
+#pragma unroll RPE_DESC_UNROLL
+#endif
   for (int k = warp; k < nk; k += 4) {
     const LevelGeom& L = g.lv[s_level[k]];
     const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];
