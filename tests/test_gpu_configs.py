@@ -101,3 +101,42 @@ def test_cfg4_4k_20000_features_8_levels():
         _check_pair(eng, c, 0, 0, out)
     finally:
         eng.close()
+
+
+def test_cfg3_full_bench_batch_properties():
+    """The batch size bench.py times (256 pairs per step, 512 images): size-independent properties.
+    16 distinct synthetic pairs are tiled 16 times in a fixed shuffled order; every copy of a pair must give
+    bit-identical R / t / euler / status / info wherever it sits in the batch, the same bits as a 16-pair batch
+    (batch-size independence), the same bits through the asynchronous two-batches-pending path, and a pose within
+    2 deg of the generator's ground-truth rotation for at least three pairs in four (planar scene, see below)."""
+    from rpe_b200.synth import synth_K, synth_batch, synth_pair
+    c = CFG3
+    U, T = 16, 16
+    B = U * T
+    K = synth_K(c["W"], c["H"])
+    uniq = synth_batch(c["synth_cfg"], 200, U, c["W"], c["H"]).reshape(U, 2, c["H"], c["W"])
+    order = np.random.default_rng(0).permutation(B) % U
+    eng = _engine(c, B)
+    try:
+        small = eng.estimate_batch_interleaved(np.ascontiguousarray(uniq.reshape(2 * U, c["H"], c["W"])), K)
+        assert (small["status"] == 0).all(), small["status"]
+        frames = np.ascontiguousarray(uniq[order].reshape(2 * B, c["H"], c["W"]))
+        big = eng.estimate_batch_interleaved(frames, K)
+        for k in ("R", "t", "euler", "status", "info"):
+            assert np.array_equal(big[k], small[k][order]), k
+        # two batches pending on one handle (the bench's submit / wait pipeline) == the blocking call
+        rev = np.ascontiguousarray(uniq[order[::-1]].reshape(2 * B, c["H"], c["W"]))     # the same pairs, reversed order
+        eng.submit_interleaved(frames, K)
+        eng.submit_interleaved(rev, K)
+        o1 = eng.wait()
+        o2 = eng.wait()
+        for k in ("R", "t", "euler", "status"):
+            assert np.array_equal(o1[k], big[k]), k
+            assert np.array_equal(o2[k], big[k][::-1]), k
+        # ground-truth sanity of the whole batch.  The synthetic scene is a plane, for which the essential matrix
+        # is ambiguous: now and then RANSAC (cv2's as well, on the same points) settles on the mirrored solution
+        errs = np.array([og.rotation_angle_deg(small["R"][u], synth_pair(c["synth_cfg"], 200 + u, c["W"], c["H"])[3])
+                         for u in range(U)])
+        assert (errs < 2.0).sum() >= 0.75 * U, errs
+    finally:
+        eng.close()

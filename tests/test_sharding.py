@@ -127,3 +127,15 @@ def test_batch_processor_twin(tmp_path, monkeypatch):
         proc.process_sequence([0])
     with pytest.raises(RuntimeError, match="Insufficient matches: 3"):
         BatchProcessor(tmp_path, _FakeEstimator(fail_at=2), gt).process_at_interval(15)
+
+
+def test_numa_binding_helper_is_safe_without_a_gpu(tmp_path):
+    """sharding.bind_host_to_gpu: cpulist parsing, and a no-op ([]) for an unknown PCI device or a node that
+    already covers the whole affinity mask."""
+    from rpe_b200 import sharding
+    assert sharding._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert sharding._parse_cpulist("") == set()
+    import os
+    before = os.sched_getaffinity(0)
+    assert sharding.bind_host_to_gpu("ffff:ff:1f.0") == []
+    assert os.sched_getaffinity(0) == before
