@@ -45,7 +45,11 @@ void launch_normalize(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, i
 #define RPE_RANSAC_CHUNK 16
 #endif
 constexpr int kChunk = RPE_RANSAC_CHUNK;   // hypotheses per round
-constexpr int kRansacThreads = 128;
+#ifndef RPE_RANSAC_THREADS
+#define RPE_RANSAC_THREADS 128
+#endif
+constexpr int kRansacThreads = RPE_RANSAC_THREADS;
+static_assert(kRansacThreads >= kChunk && kRansacThreads % 32 == 0, "one solver thread per hypothesis of a round");
 
 struct RansacShared {
   double models[kChunk][10][9];
