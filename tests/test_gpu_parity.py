@@ -388,3 +388,24 @@ def test_bgr_ingest_bit_exact_and_equal_to_host_gray(engine):
     # back to gray input on the same handle
     again = engine.estimate_sequence(grays, K)
     assert np.array_equal(again["R"], want["R"])
+
+
+@pytest.mark.parametrize("size", [(637, 475), (333, 251), (129, 97), (70, 70), (62, 200), (40, 40)])
+def test_orb_ragged_sizes_bit_exact(engine, size):
+    """Widths / heights that are not multiples of 4 or 16 (row pitch padding, partial tiles, partial quads), levels
+    that shrink below ORB's 63-px minimum on the way up the pyramid, and images too small for any keypoint: the
+    keypoint set, every field and the descriptors must equal the oracle's (= cv2's) for each size."""
+    w, h = size
+    img = np.ascontiguousarray(load_gray("sim_000015.png")[37:37 + h, 101:101 + w])
+    if h > 480 - 37:      # taller than the crop allows: tile the fixture
+        img = np.ascontiguousarray(np.tile(load_gray("sim_000015.png"), (2, 1))[37:37 + h, 101:101 + w])
+    res = engine.orb_detect(img)
+    ref = oo.orb_detect_and_compute(img, oo.OrbParams())
+    kps, desc = cv2.ORB_create(nfeatures=4000, scaleFactor=1.1, nlevels=12, fastThreshold=15,
+                               scoreType=cv2.ORB_HARRIS_SCORE).detectAndCompute(img, None)
+    assert len(ref) == len(kps)                      # the oracle itself against live cv2 at this size
+    d = _orb_diff(res, ref)
+    assert res["flags"] == 0 and d["n_gpu"] == d["n_ref"], (size, d)
+    assert all(v == 0 for k, v in d.items() if k not in ("n_gpu", "n_ref")), (size, d)
+    if min(w, h) < 63:
+        assert d["n_gpu"] == 0
