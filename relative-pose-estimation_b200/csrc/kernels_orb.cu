@@ -141,14 +141,15 @@ k_resize_strip(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, con
 
 
 // Same strip, source rows staged first: the thread requests ALL source rows of its strip (<= kResizeSrcRows rows x
-// three words) with 4-byte cp.async into its own shared-memory column and only then walks down the strip, reading
-// rows back with LDS.  k_resize_strip keeps one row in flight per thread and waits on it row after row (ncu:
+// three words) into its own shared-memory column (through registers, or with 4-byte cp.async: kViaRegs) and only
+// then walks down the strip, reading rows back with LDS.  k_resize_strip keeps one row in flight per thread and waits on it row after row (ncu:
 // 37 % of its stall samples on the row-advance); here one round trip covers the strip.  A thread reads only what it
 // staged itself, so cp.async.wait_group is the only synchronisation.  Chosen on the host when every strip of the
 // level chain spans <= kResizeSrcRows source rows (scale <= ~1.25), else k_resize_strip.
 constexpr int kResizeSrcRows = 11;
 constexpr int kResizeStageBytes = kResizeSrcRows * 3 * 256 * 4;
 
+template <bool kViaRegs>
 __global__ void __launch_bounds__(256)
 k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,
                 int level) {
@@ -169,7 +170,20 @@ k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, co
   const int xbase = __ldg(&taps[d.xtab + min(x4, d.w - 1)]).x;
   const int abase = xbase & ~3, sh8 = (xbase & 3) * 8;
   const int sp = s.pitch, last_row = s.h - 1;
-  {
+  if (kViaRegs) {
+    // the same rows through registers (LDG then STS) instead of LDGSTS
+    uint32_t rr[kResizeSrcRows][3];
+#pragma unroll
+    for (int i = 0; i < kResizeSrcRows; ++i) {
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (size_t)min(ra0 + min(i, n_src - 1), last_row) * sp + abase);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) rr[i][k] = __ldg(p + k);
+    }
+#pragma unroll
+    for (int i = 0; i < kResizeSrcRows; ++i)
+#pragma unroll
+      for (int k = 0; k < 3; ++k) s_rows[(i * 3 + k) * 256 + tid] = rr[i][k];
+  } else {
     const uint32_t sdst = smem_u32(s_rows + tid);
 #pragma unroll
     for (int i = 0; i < kResizeSrcRows; ++i) {
@@ -225,13 +239,16 @@ k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, co
 void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   for (int l = 1; l < g.nlevels; ++l) {
     const LevelGeom& d = g.lv[l];
-    // first level built by k_resize_staged (0 = never).  Measured on B200, 128 pairs: from level 1: 0.95 ms, but the
-    // end-to-end rate (uploads of the next batch running beside it) drops 13.1k -> 12.9k pairs/s; from level 2:
-    // 0.99 ms and 13.3k end to end; never: 1.10 ms
-    static const int staged_from = getenv("RPE_RESIZE_STAGED") ? atoi(getenv("RPE_RESIZE_STAGED")) : 2;
+    // tuning knobs: first level built by k_resize_staged (0 = never) and the levels below which the rows are staged
+    // through registers (LDG + STS) rather than LDGSTS.  B200, 256 pairs: never staged 2.20 ms; LDGSTS from level 2
+    // 1.89 ms (from level 1 the end-to-end rate, with the next batch uploading beside it, DROPS 3 %); registers
+    // on every level 1.81 ms with no end-to-end penalty -> the default
+    static const int staged_from = getenv("RPE_RESIZE_STAGED") ? atoi(getenv("RPE_RESIZE_STAGED")) : 1;
+    static const int via_regs = getenv("RPE_RESIZE_REGS") ? atoi(getenv("RPE_RESIZE_REGS")) : 99;
     if (g.resize_strip_ok && g.resize_span <= kResizeSrcRows && staged_from > 0 && l >= staged_from) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
-      k_resize_staged<<<grid, block, kResizeStageBytes, s>>>(g, b.pyr, b.taps, l);
+      if (l < via_regs) k_resize_staged<true><<<grid, block, kResizeStageBytes, s>>>(g, b.pyr, b.taps, l);
+      else k_resize_staged<false><<<grid, block, kResizeStageBytes, s>>>(g, b.pyr, b.taps, l);
     } else if (g.resize_strip_ok) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
       k_resize_strip<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
