@@ -200,6 +200,18 @@ RPE_HD uint32_t fast_compass4(uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t U, 
 }
 
 // ------------------------------------------------------------------ A.5 Harris response
+// response from the three integer sums over the 7x7 block (non-fused f32, A.5)
+RPE_HD float harris_from_sums(int a, int b, int cc) {
+  const float s = f32_div(1.0f, f32_mul(28.0f, 255.0f));   // 1.f/(4*7*255.f)
+  const float s4 = f32_mul(f32_mul(f32_mul(s, s), s), s);
+  const float fa = (float)a, fb = (float)b, fc = (float)cc;
+  const float apb = f32_add(fa, fb);
+  const float t1 = f32_mul(fa, fb);
+  const float t2 = f32_mul(fc, fc);
+  const float t3 = f32_mul(f32_mul(0.04f, apb), apb);
+  return f32_mul(f32_sub(f32_sub(t1, t2), t3), s4);
+}
+
 RPE_HD float harris_response(const uint8_t* c, int pitch) {
   int a = 0, b = 0, cc = 0;
   // 9x9 neighbourhood, rows -4..4; three-row sliding window
@@ -224,14 +236,7 @@ RPE_HD float harris_response(const uint8_t* c, int pitch) {
 #pragma unroll
     for (int i = 0; i < 9; ++i) { r0[i] = r1[i]; r1[i] = r2[i]; }
   }
-  const float s = f32_div(1.0f, f32_mul(28.0f, 255.0f));   // 1.f/(4*7*255.f)
-  const float s4 = f32_mul(f32_mul(f32_mul(s, s), s), s);
-  const float fa = (float)a, fb = (float)b, fc = (float)cc;
-  const float apb = f32_add(fa, fb);
-  const float t1 = f32_mul(fa, fb);
-  const float t2 = f32_mul(fc, fc);
-  const float t3 = f32_mul(f32_mul(0.04f, apb), apb);
-  return f32_mul(f32_sub(f32_sub(t1, t2), t3), s4);
+  return harris_from_sums(a, b, cc);
 }
 
 // ------------------------------------------------------------------ A.6 orientation
