@@ -872,7 +872,7 @@ k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, c
            float* __restrict__ kp_size, float* __restrict__ kp_angle, float* __restrict__ kp_resp,
            int32_t* __restrict__ kp_oct, uint8_t* __restrict__ desc, int32_t* __restrict__ kp_n) {
   __shared__ int s_level[kDescKp], s_x[kDescKp], s_y[kDescKp], s_cx[kDescKp], s_cy[kDescKp];
-  __shared__ float s_angle[kDescKp], s_a[kDescKp], s_b[kDescKp];
+  __shared__ float s_a[kDescKp], s_b[kDescKp];
   __shared__ int s_total;
   const int img = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int i0 = blockIdx.x * kDescKp;
@@ -922,48 +922,65 @@ k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, c
   //     row: 10 words cover columns x-15 .. x+15 at any alignment, 3 rows per warp instruction, 11 steps for the
   //     31 rows; the per-byte column weights u (zero outside the disc) and the 0/1 disc mask come from a table
   //     indexed by (alignment, row, word), so a step is one LDG.32, one table load, two DP4A and one IMAD
-  //     (the byte-per-lane form spent 47 % of the kernel's instructions here)
+  //     (the byte-per-lane form spent 47 % of the kernel's instructions here).
+  //     Two keypoints per iteration (both sets of loads in flight together); lane j keeps the sums of the warp's
+  //     j-th keypoint, so that the angle (fastAtan2: two divisions, a polynomial) and the steering coefficients
+  //     (double-precision sincos) of all eight keypoints of the warp are computed ONCE, in eight lanes side by side
   {
     const int rsub = lane / 10, w = lane - 10 * rsub;      // lanes 30, 31 idle
-    for (int k = warp; k < nk; k += 4) {
-      const LevelGeom& L = g.lv[s_level[k]];
-      const int x = s_x[k], y = s_y[k];
-      const int xa = (x - 15) & ~3, sh = (x - 15) & 3;
-      const uint8_t* c = pyr + (size_t)img * g.pyr_stride + L.off + (size_t)(y - 15 + rsub) * L.pitch + xa + 4 * w;
-      const uint2* tab = kOriTab_dev + (sh * 31 + rsub) * 10 + w;
-      int m10 = 0, m01 = 0;
+    int my_m10 = 0, my_m01 = 0;
+    for (int k = warp, j = 0; k < nk; k += 8, j += 2) {
+      const int kb = (k + 4 < nk) ? k + 4 : k;              // second keypoint (or the first again: result unused)
+      const LevelGeom& La = g.lv[s_level[k]];
+      const LevelGeom& Lb = g.lv[s_level[kb]];
+      const int xA = s_x[k], xB = s_x[kb];
+      const uint8_t* ca = pyr + (size_t)img * g.pyr_stride + La.off + (size_t)(s_y[k] - 15 + rsub) * La.pitch + ((xA - 15) & ~3) + 4 * w;
+      const uint8_t* cb = pyr + (size_t)img * g.pyr_stride + Lb.off + (size_t)(s_y[kb] - 15 + rsub) * Lb.pitch + ((xB - 15) & ~3) + 4 * w;
+      const uint2* ta = kOriTab_dev + (((xA - 15) & 3) * 31 + rsub) * 10 + w;
+      const uint2* tb = kOriTab_dev + (((xB - 15) & 3) * 31 + rsub) * 10 + w;
+      int a10 = 0, a01 = 0, b10 = 0, b01 = 0;
       if (lane < 30) {
+        uint32_t pa[11], pb[11];
+#pragma unroll
+        for (int it = 0; it < 11; ++it) {
+          const bool ok = it < 10 || rsub == 0;             // row 3 it + rsub <= 30
+          pa[it] = ok ? __ldg(reinterpret_cast<const uint32_t*>(ca + (size_t)(3 * it) * La.pitch)) : 0u;
+          pb[it] = ok ? __ldg(reinterpret_cast<const uint32_t*>(cb + (size_t)(3 * it) * Lb.pitch)) : 0u;
+        }
 #pragma unroll
         for (int it = 0; it < 11; ++it) {
           const int r = 3 * it + rsub;
-          if (it < 10 || r < 31) {
-            const uint32_t px = __ldg(reinterpret_cast<const uint32_t*>(c + (size_t)(3 * it) * L.pitch));
-            const uint2 t = __ldg(tab + 30 * it);
-            m10 = dp4a_u8s8(px, t.x, m10);                         // u8 pixels x s8 column offsets
-            m01 += (r - 15) * (int)__dp4a(px, t.y, 0u);            // row offset x masked row sum
+          if (it < 10 || rsub == 0) {
+            const uint2 t = __ldg(ta + 30 * it), u = __ldg(tb + 30 * it);
+            a10 = dp4a_u8s8(pa[it], t.x, a10);                     // u8 pixels x s8 column offsets
+            a01 += (r - 15) * (int)__dp4a(pa[it], t.y, 0u);        // row offset x masked row sum
+            b10 = dp4a_u8s8(pb[it], u.x, b10);
+            b01 += (r - 15) * (int)__dp4a(pb[it], u.y, 0u);
           }
         }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+        a10 += __shfl_xor_sync(0xffffffffu, a10, o);
+        a01 += __shfl_xor_sync(0xffffffffu, a01, o);
+        b10 += __shfl_xor_sync(0xffffffffu, b10, o);
+        b01 += __shfl_xor_sync(0xffffffffu, b01, o);
       }
-      if (lane == 0) {
-        const float ang = fast_atan2_deg((float)m01, (float)m10);
-        s_angle[k] = ang;
+      if (lane == j) { my_m10 = a10; my_m01 = a01; }
+      if (lane == j + 1) { my_m10 = b10; my_m01 = b01; }
+    }
+    // (2) angle + steering coefficients of the warp's keypoints, one per lane
+    if (lane < kDescKp / 4) {
+      const int k = warp + 4 * lane;
+      if (k < nk) {
+        const float ang = fast_atan2_deg((float)my_m01, (float)my_m10);
         kp_angle[(size_t)img * g.kp_stride + i0 + k] = ang;
+        brief_steer(ang, &s_a[k], &s_b[k]);
       }
     }
   }
-  // a warp only ever touches its own keypoints (k = warp, warp + 4, ...): warp-level synchronisation from here on,
-  // so the four warps of the CTA drift through the phases independently
-  __syncwarp();
-  // (2) steering coefficients of this warp's keypoints, one per lane
-  if (lane < kDescKp / 4) {
-    const int k = warp + 4 * lane;
-    if (k < nk) brief_steer(s_angle[k], &s_a[k], &s_b[k]);
-  }
+  // a warp only ever touches its own keypoints (k = warp, warp + 4, ...): warp-level synchronisation is enough, and
+  // the four warps of the CTA drift through the phases independently
   __syncwarp();
   // (3) descriptor
 #ifdef RPE_DESC_UNROLL
