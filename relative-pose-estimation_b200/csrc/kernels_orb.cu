@@ -332,7 +332,10 @@ __device__ __forceinline__ void fast_issue(const OrbGeom& g, const FastTile& T, 
 #endif
 }
 
-constexpr int kFastTilesPerCta = 4;   // consecutive tiles of one image per CTA, TMA double-buffered
+#ifndef RPE_FAST_TILES
+#define RPE_FAST_TILES 4
+#endif
+constexpr int kFastTilesPerCta = RPE_FAST_TILES;   // consecutive tiles of one image per CTA, TMA double-buffered
 
 #ifndef RPE_FAST_MINB
 #define RPE_FAST_MINB 6
