@@ -163,6 +163,11 @@ def five_point_models(x1: np.ndarray, x2: np.ndarray, roots_fn=None) -> list[np.
     each with ||E||_F = 1.  x1, x2: (5, 2) float64."""
     x1 = np.asarray(x1, dtype=np.float64)
     x2 = np.asarray(x2, dtype=np.float64)
+    if np.array_equal(x1, x2):
+        # static sample (no camera motion): the system is rank deficient and cv2 4.13 returns this skew-symmetric
+        # matrix (R = I) for ANY such sample — pinned against live cv2 in tests/test_oracle_geometry.py
+        a = 1.0 / np.sqrt(6.0)
+        return [np.array([[0.0, -a, -a], [a, 0.0, -a], [a, a, 0.0]])]
     Q = np.stack([x2[:, 0] * x1[:, 0], x2[:, 0] * x1[:, 1], x2[:, 0],
                   x2[:, 1] * x1[:, 0], x2[:, 1] * x1[:, 1], x2[:, 1],
                   x1[:, 0], x1[:, 1], np.ones(5)], axis=1)

@@ -157,6 +157,22 @@ RPE_HDN void solve_poly10(const double* c, Cplx* roots, int max_iters) {
 // All real essential matrices through five normalised correspondences (x2' E x1 = 0), each
 // with Frobenius norm 1.  x1, x2: 5 x (x, y).  Eout: up to 10 x 9 (row-major).  Returns count.
 RPE_HDN int five_point_solve(const double* x1, const double* x2, double* Eout) {
+  // --- 0. static sample (x2 == x1 for all five points: the camera did not move, e.g. the last 5 pairs of the
+  // reference's simulator sequence).  Every skew-symmetric matrix then satisfies the constraints, the polynomial
+  // system is rank deficient and its numerical solution is noise; cv2 4.13 (LAPACK build) returns
+  // E = [[0,-1,-1],[1,0,-1],[1,1,0]] / sqrt(6) for ANY such sample, whatever the points and K
+  // (tests/test_oracle_geometry.py pins this against live cv2), i.e. R = I exactly.  Same here.
+  {
+    bool is_static = true;
+    for (int i = 0; i < 10; ++i) is_static = is_static && (x1[i] == x2[i]);
+    if (is_static) {
+      const double a = 0.40824829046386302;   // 1 / sqrt(6)
+      Eout[0] = 0.0; Eout[1] = -a;  Eout[2] = -a;
+      Eout[3] = a;   Eout[4] = 0.0; Eout[5] = -a;
+      Eout[6] = a;   Eout[7] = a;   Eout[8] = 0.0;
+      return 1;
+    }
+  }
   // --- 1. null space of the 5x9 epipolar system, in the SAME basis OpenCV gets from LAPACK.
   // cv2 (built with LAPACK) calls dgesdd(FULL_UV) on the 5x9 matrix; for that shape dgesdd takes
   // the "LQ first" path, so rows 5..8 of Vt are rows 5..8 of the full Householder Q of A = L Q.
@@ -366,6 +382,20 @@ RPE_HD void jacobi_cols(double* a, double* v) {
 // decomposeEssentialMat: E -> R1, R2, t (unit).  Candidate order used downstream:
 // (R1,t) (R2,t) (R1,-t) (R2,-t), as cv2.recoverPose.
 RPE_HDN void decompose_essential(const double* E, double* R1, double* R2, double* t) {
+  {
+    // the static-pair matrix of five_point_solve step 0 has two equal singular values, so U and V are not unique;
+    // cv2.recoverPose on it returns R = I, t = (1, -1, 1) / sqrt(3) (count 0): R1 = I makes candidate 0 win
+    const double a0 = 0.40824829046386302;
+    if (E[0] == 0.0 && E[4] == 0.0 && E[8] == 0.0 && E[1] == -a0 && E[2] == -a0 && E[5] == -a0 && E[3] == a0 &&
+        E[6] == a0 && E[7] == a0) {
+      const double q = 0.57735026918962576;      // 1 / sqrt(3)
+      t[0] = q; t[1] = -q; t[2] = q;
+      for (int i = 0; i < 9; ++i) R1[i] = (i % 4 == 0) ? 1.0 : 0.0;
+      for (int i = 0; i < 3; ++i)                // R2 = 2 t t' - I: the half-turn about t (the twisted candidate)
+        for (int j = 0; j < 3; ++j) R2[3 * i + j] = 2.0 * t[i] * t[j] - (i == j ? 1.0 : 0.0);
+      return;
+    }
+  }
   double a[9], v[9];
   for (int i = 0; i < 9; ++i) a[i] = E[i];
   jacobi_cols<3, 3>(a, v);

@@ -140,3 +140,74 @@ def test_cfg3_full_bench_batch_properties():
         assert (errs < 2.0).sum() >= 0.75 * U, errs
     finally:
         eng.close()
+
+
+CFG2_DIR = __import__("os").path.join(__import__("os").path.dirname(__import__("os").path.dirname(
+    __import__("os").path.abspath(__file__))), "baseline", "_ref", "simulator-data")
+
+
+class _TableGT:
+    """The two GroundTruthLoader methods the sequence driver and the evaluator use (reference:
+    src/core/ground_truth_loader.py:43-80), over the staged camera_poses.txt."""
+    def __init__(self, path):
+        rows = [l.split() for l in open(path).read().strip().splitlines()[1:]]
+        self.rows = {int(r[0]): [float(v) for v in r[1:]] for r in rows}
+
+    def get_pose(self, f):
+        x, y, z, roll, pitch, yaw = self.rows[int(f)]
+        return {"x": x, "y": y, "z": z, "roll": roll, "pitch": pitch, "yaw": yaw}
+
+    def get_frame_indices(self, step=1):
+        return [f for f in sorted(self.rows) if f % step == 0]
+
+
+def test_cfg2_simulator_sequence():
+    """BASELINE config 2: the reference's simulator sequence at step 15 — 59 frames, all 58 consecutive pairs in ONE
+    sequence call on one B200 (ORB once per frame), loaded as the pipeline loads them (imread + cvtColor), reference
+    parameters (4000 features, cross-check, 500 matches, RANSAC 1000).  Every pair against the reference's own cv2
+    call sequence on the canonically ordered features: R within 0.1 deg, t within 0.5 deg; then the BatchProcessor
+    and PoseEvaluator twins end to end against the oracle's evaluator on the same estimates.
+    The frames are reference DATA staged by tests/golden/stage_cfg2.py into baseline/_ref (git-ignored)."""
+    import os
+    if not os.path.isdir(os.path.join(CFG2_DIR, "images")):
+        pytest.skip("config-2 frames not staged (python tests/golden/stage_cfg2.py in the build container)")
+    import rpe_b200
+    from conftest import default_K
+    from oracle import evaluator as oe
+    gt = _TableGT(os.path.join(CFG2_DIR, "camera_poses.txt"))
+    idx = [f for f in gt.get_frame_indices(step=15) if os.path.exists(os.path.join(CFG2_DIR, "images", f"{f:06d}.png"))]
+    assert len(idx) == 59
+    frames = [cv2.cvtColor(cv2.imread(os.path.join(CFG2_DIR, "images", f"{f:06d}.png")), cv2.COLOR_BGR2GRAY) for f in idx]
+    K = default_K(640, 480)
+    est = rpe_b200.PoseEstimator(K, nfeatures=4000, max_matches=500)
+    R, t, status = est.estimate_sequence(frames)
+    assert R.shape == (58, 3, 3) and (status == 0).all(), status
+    ref = ReferencePath(K, PathConfig(), canonical=True)
+    worst_r = worst_t = 0.0
+    n_static = 0
+    for p in range(58):
+        Rr, tr = ref.estimate(frames[p], frames[p + 1])
+        worst_r = max(worst_r, og.rotation_angle_deg(R[p], Rr))
+        worst_t = max(worst_t, og.direction_angle_deg(t[p], tr))
+        if np.array_equal(frames[p], frames[p + 1]):
+            # the camera stands still at the end of the sequence: the static-pair convention (R = I exactly, as cv2)
+            n_static += 1
+            assert np.array_equal(R[p], np.eye(3)) and og.rotation_angle_deg(Rr, np.eye(3)) < 1e-6
+    assert worst_r < 0.1 and worst_t < 0.5, (worst_r, worst_t)
+    assert n_static == 5
+    # the callers: BatchProcessor twin (GPU gray ingest from the decoded BGR frames) and PoseEvaluator twin
+    bp = rpe_b200.BatchProcessor(os.path.join(CFG2_DIR, "images"), est, gt, chunk_pairs=58)
+    res = bp.process_at_interval(step=15)
+    assert res["frames"] == idx[1:] and len(res["R"]) == 58
+    ev = rpe_b200.PoseEvaluator(gt, engine=est.engine)
+    out = ev.evaluate_sequence(res)
+    gt_e = np.array([[gt.get_pose(f)[k] for k in ("yaw", "pitch", "roll")] for f in res["frames"]])
+    gt_p = np.array([[gt.get_pose(f)[k] for k in ("x", "y", "z")] for f in res["frames"]])
+    want = oe.evaluate_sequence(res["R"], res["t"], np.stack([res["yaw"], res["pitch"], res["roll"]], axis=1), gt_e, gt_p)
+    for k, m in enumerate(oe.METRICS):
+        # (the ground-truth position does not change over the last frames: 0 / 0 = NaN in the reference's
+        # translation_direction_error, and here)
+        assert np.allclose(out[m], want[:, k], rtol=0, atol=2e-6, equal_nan=True), m
+    assert np.isnan(want[:, 4]).sum() >= 5 and not np.isnan(want[:, :4]).any()
+    stats = ev.compute_summary_statistics(out)
+    assert abs(stats["rotation_error_mean"] - want[:, 3].mean()) < 1e-6

@@ -98,3 +98,27 @@ def test_euler_equals_reference_helpers():
         R = np.array(p["reference"]["R"])
         assert np.allclose(og.rotation_to_euler_yup(R), p["reference"]["euler_yup"], atol=1e-10)
         assert np.allclose(og.rotation_to_euler_zyx(R), p["reference"]["euler_zyx"], atol=1e-10)
+
+
+def test_static_pair_convention_matches_cv2():
+    """Identical point sets (a camera that did not move: the last five pairs of the reference's simulator sequence).
+    The five-point system is rank deficient; cv2 4.13 returns E = [[0,-1,-1],[1,0,-1],[1,1,0]] / sqrt(6) for any such
+    input, whatever the points, their number and K, with every point an inlier.  The oracle
+    (and the CUDA solver, geom_math.cuh step 0) reproduce exactly that."""
+    import cv2
+    from oracle import geometry as og
+    rng = np.random.default_rng(0)
+    E0 = np.array([[0, -1, -1], [1, 0, -1], [1, 1, 0]]) / np.sqrt(6.0)
+    for _ in range(6):
+        M = int(rng.integers(6, 600))
+        K = np.array([[rng.uniform(300, 1200), 0, rng.uniform(200, 700)], [0, rng.uniform(300, 1200), rng.uniform(150, 500)],
+                      [0, 0, 1.0]])
+        p = np.c_[rng.uniform(0, 1280, M), rng.uniform(0, 720, M)].astype(np.float32)
+        E, mask = cv2.findEssentialMat(p, p.copy(), K, method=cv2.RANSAC, prob=0.999, threshold=1.0, maxIters=1000)
+        assert E.shape == (3, 3) and np.abs(E - E0).max() < 1e-12 and int(mask.sum()) == M
+        Eo, mo = og.find_essential_ransac(p, p.copy(), K)
+        assert np.abs(np.asarray(Eo) - E0).max() < 1e-15 and int(np.asarray(mo).sum()) == M
+        # recoverPose on it is itself ill-defined: two equal singular values and no point in front of any of the
+        # four candidates (count 0), so cv2 returns R = I or the 180-degree twisted rotation depending on 1e-17 noise
+        n, R, _, _ = cv2.recoverPose(E, p, p.copy(), K)
+        assert n == 0 and min(og.rotation_angle_deg(R, np.eye(3)), abs(180.0 - og.rotation_angle_deg(R, np.eye(3)))) < 1e-4
