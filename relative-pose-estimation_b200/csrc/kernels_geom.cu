@@ -38,13 +38,23 @@ void launch_normalize(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, i
 
 // Hypotheses per round.  The five-point solver keeps 2.5 KB of per-thread scratch in local memory (the 10 x 20
 // elimination matrix), interleaved by lane: 16 solver threads in the lower half-warp touch 40 KB, which stays in L1
-// next to the dense kernels sharing the SM; 24 and more spill out of it (B200, 128 pairs per step: 0.38 / 0.44 / 1.08 /
-// 1.11 / 1.24 / 3.2 ms for 8 / 16 / 24 / 32 / 64 / 128).  Small rounds also solve fewer hypotheses past the adaptive
-// stop.  The result does not depend on it (same RNG stream, sequential update rule replayed per round).
+// next to the dense kernels sharing the SM; 24 and more spill out of it (B200, 128 easy pairs per step: 0.38 / 0.44 /
+// 1.08 / 1.11 / 1.24 / 3.2 ms for rounds of 8 / 16 / 24 / 32 / 64 / 128), and small rounds solve fewer hypotheses
+// past the adaptive stop.  A round costs one solver latency (~0.3 ms) whatever its size, though, so a pair that still
+// needs many iterations (low inlier ratio: the reference's simulator frames run to the 1000-iteration cap) takes
+// rounds of kChunkMax instead: 58 such pairs 22 ms -> 10 ms.  The result does not depend on the round sizes (same
+// RNG stream, exactly the drawn subsets consumed, sequential update rule replayed per round).
 #ifndef RPE_RANSAC_CHUNK
 #define RPE_RANSAC_CHUNK 16
 #endif
-constexpr int kChunk = RPE_RANSAC_CHUNK;   // hypotheses per round
+constexpr int kChunkSmall = RPE_RANSAC_CHUNK;   // first round, and while few iterations remain
+constexpr int kChunkMax = 64;                   // later rounds while more than kChunkSwitch iterations remain
+#ifndef RPE_RANSAC_SWITCH
+#define RPE_RANSAC_SWITCH 48
+#endif
+constexpr int kChunkSwitch = RPE_RANSAC_SWITCH;
+constexpr int kChunk = kChunkMax;               // array sizes
+static_assert(kChunkSmall <= kChunkMax, "round sizes");
 #ifndef RPE_RANSAC_THREADS
 #define RPE_RANSAC_THREADS 128
 #endif
@@ -58,7 +68,7 @@ struct RansacShared {
   int subset[kChunk][5];
   double best_model[9];
   unsigned long long rng_state;
-  int best, niters, it0, done, have_best;
+  int best, niters, it0, done, have_best, nh;
 };
 
 __global__ void __launch_bounds__(kRansacThreads)
@@ -89,8 +99,12 @@ k_ransac(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ n
   while (true) {
     // (a) subsets for this chunk, sequentially from the shared RNG stream
     if (tid == 0) {
+      const int remaining = S.niters - S.it0;
+      // the first round is always small: it is what brings niters down from max_iters for an easy pair
+      const int nh_round = min((S.it0 > 0 && remaining > kChunkSwitch) ? kChunkMax : kChunkSmall, remaining);
+      S.nh = nh_round;                              // hypotheses that can still matter
       CvRng rng{S.rng_state};
-      for (int h = 0; h < kChunk; ++h) {
+      for (int h = 0; h < nh_round; ++h) {
         if (M == 5) { for (int k = 0; k < 5; ++k) S.subset[h][k] = k; }
         else draw_subset5(rng, M, S.subset[h]);
       }
@@ -98,7 +112,7 @@ k_ransac(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ n
     }
     __syncthreads();
     const int it0 = S.it0;
-    const int nh = min(kChunk, S.niters - it0);   // hypotheses that can still matter
+    const int nh = S.nh;
     // (b) minimal solver, one hypothesis per thread
     const int hyp = tid;
     if (hyp < nh) {
