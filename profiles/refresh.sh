@@ -1,5 +1,5 @@
 #!/bin/bash
-# usage: profiles/refresh.sh vN   -- copy the artefacts of the last `gpu_round.sh ncu` run from gpurun_out/ into profiles/ as round-1 vN
+# usage: profiles/refresh.sh vN   -- copy the artefacts of the last `tools/gpu_round.sh ncu` run from gpurun_out/ into profiles/ as round-1 vN
 V=$1
 cp gpurun_out/bench.json profiles/r01_bench_b256_$V.json
 cp gpurun_out/launches.csv profiles/r01_launches_b256_$V.csv

@@ -2,7 +2,7 @@
 host frames in / poses out, against the reference's cv2 call sequence on the same frames (all host threads)."""
 import os, sys, time, json
 import numpy as np, cv2
-ROOT = os.path.dirname(os.path.abspath(__file__)); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import rpe_b200
 from conftest import default_K
 from oracle.reference_path import PathConfig, ReferencePath

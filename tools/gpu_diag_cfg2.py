@@ -1,7 +1,7 @@
 """Stage-by-stage diagnosis of config 2 (simulator sequence) against the reference's cv2 call sequence."""
 import os, sys
 import numpy as np, cv2
-ROOT = os.path.dirname(os.path.abspath(__file__)); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import rpe_b200
 from rpe_b200 import _lib as L
 from conftest import default_K

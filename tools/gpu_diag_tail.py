@@ -1,5 +1,6 @@
 import sys, json
 sys.argv = ["bench.py", "--no-cpu-baseline", "--no-stream", "--steps", "20"]
+sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
 import bench
 bench.CFG["ransac_max_iters"] = int(sys.stdin.readline() or 2000)
 import io, contextlib
