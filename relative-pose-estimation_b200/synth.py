@@ -95,18 +95,19 @@ def stream_pose(cfg: int, stream_idx: int, k: int, W: int, H: int):
     return R, t
 
 
-def stream_relative_pose(cfg: int, stream_idx: int, k: int, W: int, H: int):
-    """Ground-truth relative pose of the pair (frame k, frame k+1): R_rel, unit t_rel."""
+def stream_relative_pose(cfg: int, stream_idx: int, k: int, W: int, H: int, step: int = 1):
+    """Ground-truth relative pose of the pair (frame k, frame k+step): R_rel, unit t_rel."""
     R0, t0 = stream_pose(cfg, stream_idx, k, W, H)
-    R1, t1 = stream_pose(cfg, stream_idx, k + 1, W, H)
+    R1, t1 = stream_pose(cfg, stream_idx, k + step, W, H)
     Rr = R1 @ R0.T
     tr = t1 - Rr @ t0
     return Rr, tr / max(np.linalg.norm(tr), 1e-300)
 
 
 def synth_stream(cfg: int, first_frame: int, n_frames: int, W: int, H: int, stream_idx: int = 0,
-                 out: np.ndarray | None = None):
-    """(n_frames, H, W) uint8: frames first_frame .. first_frame + n_frames - 1 of stream ``stream_idx``."""
+                 out: np.ndarray | None = None, step: int = 1):
+    """(n_frames, H, W) uint8: frames first_frame, first_frame + step, ... of stream ``stream_idx``
+    (``step`` > 1 = the stream sampled at a lower frame rate: proportionally larger motion per pair)."""
     base, _ = _stream_state(cfg, stream_idx, W, H)
     K = synth_K(W, H)
     Ki = np.linalg.inv(K)
@@ -114,7 +115,7 @@ def synth_stream(cfg: int, first_frame: int, n_frames: int, W: int, H: int, stre
     if out is None:
         out = np.empty((n_frames, H, W), np.uint8)
     for i in range(n_frames):
-        R, t = stream_pose(cfg, stream_idx, first_frame + i, W, H)
+        R, t = stream_pose(cfg, stream_idx, first_frame + i * step, W, H)
         Hm = K @ (R + np.outer(t, n) / 5.0) @ Ki
         cv2.warpPerspective(base, Hm, (W, H), dst=out[i], flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
     return out
