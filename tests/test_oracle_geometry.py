@@ -122,3 +122,28 @@ def test_static_pair_convention_matches_cv2():
         # four candidates (count 0), so cv2 returns R = I or the 180-degree twisted rotation depending on 1e-17 noise
         n, R, _, _ = cv2.recoverPose(E, p, p.copy(), K)
         assert n == 0 and min(og.rotation_angle_deg(R, np.eye(3)), abs(180.0 - og.rotation_angle_deg(R, np.eye(3)))) < 1e-4
+
+
+def test_cv2_tie_order_is_rounding_noise():
+    """Why the engine does not reproduce cv2.recoverPose's pick when all four candidates tie:
+    the order of {R1, R2} out of cv2.decomposeEssentialMat on a rank-2 E follows the rounding residue of its SVD -
+    a 1e-13 perturbation of E swaps them - while the candidate SET is stable."""
+    rng = np.random.default_rng(2)
+    swapped = 0
+    for _ in range(40):
+        r, _ = cv2.Rodrigues(rng.uniform(-1, 1, 3))
+        t = rng.normal(size=3)
+        t /= np.linalg.norm(t)
+        tx = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]])
+        E = tx @ r
+        E /= np.linalg.norm(E)
+        R1, R2, _ = cv2.decomposeEssentialMat(E)
+        for _ in range(8):
+            Q1, Q2, _ = cv2.decomposeEssentialMat(E + rng.normal(size=(3, 3)) * 1e-13)
+            same = np.allclose(Q1, R1, atol=1e-6) and np.allclose(Q2, R2, atol=1e-6)
+            swap = np.allclose(Q1, R2, atol=1e-6) and np.allclose(Q2, R1, atol=1e-6)
+            assert same or swap                      # the set {R1, R2} never changes
+            if swap:
+                swapped += 1
+                break
+    assert swapped >= 30, swapped
