@@ -197,7 +197,18 @@ def cpu_reference_rate_sharded(steps: int, n_per_proc: int):
     ps = [ctx.Process(target=_shard_worker, args=(w, steps, n_per_proc, barrier, q), daemon=True) for w in range(procs)]
     for p_ in ps:
         p_.start()
-    res = [q.get(timeout=600) for _ in ps]
+    import queue as _queue
+    res, t_end = [], time.perf_counter() + 300
+    while len(res) < procs:
+        try:
+            res.append(q.get(timeout=2))
+        except _queue.Empty:
+            dead = [p_.exitcode for p_ in ps if p_.exitcode not in (None, 0)]
+            if dead or time.perf_counter() > t_end:      # a worker died (or hangs): do not wait for it
+                for p_ in ps:
+                    if p_.is_alive():
+                        p_.terminate()
+                raise RuntimeError(f"process-per-core CPU sample failed (exit codes {dead})")
     for p_ in ps:
         p_.join(timeout=60)
     wall = sum(max(r[1][s] for r in res) for s in range(steps))     # per step: until the slowest core is done
@@ -448,11 +459,11 @@ def run_b200(args):
                "sample": f"{args.cpu_pairs} synthetic 1280x720 cfg3 pairs in {dt:.1f}s, cv2 {threads} threads "
                          f"(same cv2 calls as PoseEstimator.estimate)", "modes": {"cv2_threads": rate}}
         try:        # the CPU's other mode: one single-threaded process per core (SURVEY 8d ii); the better one is reported
-            r2, procs, wall2 = cpu_reference_rate_sharded(1, 3)
+            r2, procs, wall2 = cpu_reference_rate_sharded(1, 8)
             cpu["modes"]["process_per_core"] = r2
             if r2 > rate:
                 cpu.update(value=r2, cores=procs,
-                           sample=f"{procs} single-threaded processes x 3 synthetic 1280x720 cfg3 pairs in {wall2:.1f}s "
+                           sample=f"{procs} single-threaded processes x 8 synthetic 1280x720 cfg3 pairs in {wall2:.1f}s "
                                   f"(same cv2 calls as PoseEstimator.estimate); cv2's own {threads} threads: {rate:.1f} pairs/s")
         except Exception as e:
             cpu["modes"]["process_per_core_error"] = repr(e)[:200]
