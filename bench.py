@@ -105,7 +105,7 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------------------ data
 def make_batch(rank: int, B: int):
-    from rpe_b200.synth import synth_batch, synth_K   # input generator (host), not the checker
+    from bench_support.synth import synth_batch, synth_K   # input generator (host), not the checker
     frames = synth_batch(CFG["synth_cfg"], rank * 100000, B, CFG["W"], CFG["H"])
     return frames, synth_K(CFG["W"], CFG["H"])
 
@@ -141,7 +141,7 @@ def cpu_reference_rate(n_pairs: int, first_pair: int = 900000):
     """The reference's CPU path (cv2, all host threads) on a bounded sample of the same workload."""
     import cv2
     from oracle.reference_path import PathConfig, ReferencePath
-    from rpe_b200.synth import synth_K, synth_pair
+    from bench_support.synth import synth_K, synth_pair
     cv2.setNumThreads(-1)
     K = synth_K(CFG["W"], CFG["H"])
     ref = ReferencePath(K, PathConfig(nfeatures=CFG["nfeatures"], nlevels=CFG["nlevels"], match_mode=CFG["match_mode"],
@@ -166,7 +166,7 @@ def _shard_worker(wid, steps, n, barrier, q):
     started together on a barrier."""
     import cv2
     from oracle.reference_path import PathConfig, ReferencePath
-    from rpe_b200.synth import synth_K, synth_pair
+    from bench_support.synth import synth_K, synth_pair
     cv2.setNumThreads(1)
     K = synth_K(CFG["W"], CFG["H"])
     ref = ReferencePath(K, PathConfig(nfeatures=CFG["nfeatures"], nlevels=CFG["nlevels"], match_mode=CFG["match_mode"],
@@ -375,7 +375,7 @@ def run_b200(args):
     # chains steps by starting at the previous step's last frame, so the steady-state rate is B pairs / step.
     stream = None
     if not args.no_stream:
-        from rpe_b200.synth import synth_stream
+        from bench_support.synth import synth_stream
         F = B + 1
         shost = torch.from_numpy(synth_stream(5, rank * 100000, F, W, H)).pin_memory()
         sdev = shost.cuda(non_blocking=False)

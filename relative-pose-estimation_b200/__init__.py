@@ -7,7 +7,7 @@ from .pose_estimator import PoseEstimator
 from .geometry import rotation_to_euler, euler_to_rotation, rotation_to_euler_yup, rotation_to_euler_zyx
 from .batch_processor import BatchProcessor
 from .pose_evaluator import PoseEvaluator
-from . import _lib, sharding, synth
+from . import _lib, sharding
 
 __all__ = ["Engine", "EngineConfig", "PoseEstimator", "BatchProcessor", "PoseEvaluator", "sharding", "rotation_to_euler", "euler_to_rotation",
            "rotation_to_euler_yup", "rotation_to_euler_zyx"]

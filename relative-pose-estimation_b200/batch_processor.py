@@ -50,6 +50,10 @@ class BatchProcessor:
         for c0 in range(0, n_pairs, self.chunk_pairs):
             c1 = min(c0 + self.chunk_pairs, n_pairs)
             frames = [load_image(self.get_image_path(f), to_gray=not self.gpu_gray) for f in frame_indices[c0:c1 + 1]]
+            # the reference hands R_prev to estimate() on every pair (:82-92), which arms its VP branch
+            note = getattr(self.pose_estimator, "_note_vp", None)
+            if note is not None:
+                note(True)
             R_rel, t_rel, status = self.pose_estimator.estimate_sequence(frames)
             for k in range(c1 - c0):
                 self.pose_estimator._raise_for(status[k], self.pose_estimator.last["info"][k, 0])

@@ -826,6 +826,8 @@ int rpe_submit_sequence(rpe_handle* h, const uint8_t* const* frames, int32_t F, 
 
 int rpe_estimate_sequence(rpe_handle* h, const uint8_t* const* frames, int32_t F, int32_t H, int32_t W, size_t pitch,
                           const double K[9], double* R, double* t, double* euler, int32_t* status, int32_t* info) {
+  // blocking form: nothing else may be pending, so that the results waited for are this call's (as run_batch)
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   RPE_TRY(rpe_submit_sequence(h, frames, F, H, W, pitch, K, R, t, euler, status, info));
   return wait_batch(h);
 }
@@ -843,6 +845,7 @@ int rpe_submit_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t im
 int rpe_estimate_sequence_device(rpe_handle* h, const uint8_t* d_frames, size_t img_stride, int32_t F, int32_t H,
                                  int32_t W, size_t pitch, const double K[9], double* R, double* t, double* euler,
                                  int32_t* status, int32_t* info) {
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
   RPE_TRY(rpe_submit_sequence_device(h, d_frames, img_stride, F, H, W, pitch, K, R, t, euler, status, info));
   return wait_batch(h);
 }

@@ -13,7 +13,9 @@ CONVENTION_ZYX = "zyx"
 
 
 def rotation_to_euler_yup(R):
-    pitch = math.asin(R[2, 1])
+    # np.arcsin as the reference (geometry.py:60): rounding in R_prev @ R_rel can leave |R[2,1]| a hair above 1 near
+    # gimbal lock; numpy then yields nan with a RuntimeWarning and the sequence goes on, math.asin would raise
+    pitch = float(np.arcsin(R[2, 1]))
     if abs(R[2, 1]) > 0.9999:
         roll, yaw = math.atan2(-R[1, 2], R[1, 1]), 0.0
     else:

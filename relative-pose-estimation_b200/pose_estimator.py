@@ -3,16 +3,26 @@
 RuntimeErrors, computed by hand-written sm_100a kernels through librpe_b200.so instead of cv2 on
 the CPU.  Adds ``estimate_batch`` (one launch sequence for many pairs) and stage accessors.
 
-Not implemented (documented scope): SIFT / L2 raise NotImplementedError;
-VP refinement is accepted as a constructor argument but never applied (it never fires on the
-reference's own data and is outside the hot path north_star names).
+Not implemented (documented scope): SIFT / L2 raise NotImplementedError.
+VP refinement (reference :155-481, applied at :535-567) is not built: run with the unmodified reference over
+its three datasets at the runners' steps (tools/vp_gate_count.py -> profiles/r02_vp_gate_count.json) its two
+reliability gates (:545-550) pass on 0 of 58 (simulator), 0 of 9 (phone) and 0 of 80 (salah) pairs and R_rel is
+bit-identical with the refinement on and off on all 147.  The constructor accepts the ``vp_*`` arguments; the
+first ``estimate*`` call that would have entered the branch (``use_vp_refinement`` and ``R_prev`` given) warns
+once (``VPRefinementNotApplied``) instead of dropping it silently.
 """
 from __future__ import annotations
+
+import warnings
 
 import numpy as np
 
 from . import _lib as L
 from .engine import Engine, EngineConfig
+
+
+class VPRefinementNotApplied(UserWarning):
+    """use_vp_refinement=True and R_prev were given: the reference would run its VP branch here."""
 
 _MESSAGES = {
     L.STATUS_NO_DESCRIPTORS: "Could not compute descriptors for one of the images.",
@@ -48,6 +58,7 @@ class PoseEstimator:
                         euler_convention=euler_convention)
         self._engine = None
         self._size = (0, 0)
+        self._vp_warned = False
         if max_image_size is not None:
             self._ensure_engine(max_image_size[0], max_image_size[1], max_pairs)
 
@@ -106,14 +117,26 @@ class PoseEstimator:
         if code != L.STATUS_OK:
             raise RuntimeError(_MESSAGES[code])
 
+    def _note_vp(self, R_prev):
+        """The reference enters its VP branch when ``use_vp_refinement and R_prev is not None`` (:536).  That branch
+        is not built here (see the module docstring: its gates pass on none of the reference's 147 dataset pairs)."""
+        if self.use_vp_refinement and R_prev is not None and not self._vp_warned:
+            self._vp_warned = True
+            warnings.warn("use_vp_refinement=True: VP refinement is not implemented in the B200 engine and is NOT "
+                          "applied; results equal the reference's whenever its VP reliability gates fail (all 147 "
+                          "pairs of the reference's own datasets, profiles/r02_vp_gate_count.json)",
+                          VPRefinementNotApplied, stacklevel=3)
+
     def estimate(self, img1, img2, R_prev=None):
         """reference: src/core/pose_estimator.py:487-569 -> (R 3x3, t 3x1)."""
+        self._note_vp(R_prev)
         R, t, st = self.estimate_batch([img1], [img2])
         self._raise_for(st[0], self.last["info"][0, 0])
         return R[0], t[0]
 
     def estimate_with_debug(self, img1, img2, R_prev=None):
         """reference: src/core/pose_estimator.py:571-688 (same dict keys)."""
+        self._note_vp(R_prev)
         R, t, st = self.estimate_batch([img1], [img2])
         info = self.last["info"][0]
         self._raise_for(st[0], info[0])

@@ -62,3 +62,40 @@ class PoseEvaluator:
             errors = np.stack([np.asarray(evaluation_results[m], np.float64) for m in _METRICS], axis=1)
             summary = self._get_engine().summarize_errors(errors) if n else np.full((5, 5), np.nan)
         return {f"{m}_{s}": summary[i, j] for i, m in enumerate(_METRICS) for j, s in enumerate(_STATS)}
+
+    # ------------------------------------------------------------------ host-side reporting (no arithmetic of the path)
+    # The shipped pipeline calls these two right after evaluate_sequence (reference: src/pipeline.py:160, :163), so a
+    # drop-in evaluator needs them; they only format what the device kernels returned.
+    _FRAME_COLUMNS = ("gt_roll", "gt_pitch", "gt_yaw", "est_roll", "est_pitch", "est_yaw") + _METRICS
+
+    def create_comparison_dataframe(self, evaluation_results):
+        """reference: pose_evaluator.py:159-184 — one row per frame: frame, GT / estimated angles, the five errors."""
+        import pandas as pd
+        cols = {"frame": evaluation_results["frames"]}
+        cols.update({c: evaluation_results[c] for c in self._FRAME_COLUMNS})
+        return pd.DataFrame(cols)
+
+    @staticmethod
+    def _wrap_angle_error(error_deg):
+        """reference: pose_evaluator.py:186-198 — |error| after wrapping to [-180, 180)."""
+        return abs(((error_deg + 180) % 360) - 180)
+
+    # (title, metric, statistics shown) in the order the reference prints them (pose_evaluator.py:214-238)
+    _SUMMARY_LAYOUT = (("Rotation Errors (degrees):", "rotation_error", ("mean", "std", "median", "max", "min")),
+                       ("Roll Errors (degrees):", "roll_error", ("mean", "std")),
+                       ("Pitch Errors (degrees):", "pitch_error", ("mean", "std")),
+                       ("Yaw Errors (degrees):", "yaw_error", ("mean", "std")),
+                       ("Translation Direction Errors (degrees):", "translation_dir_error", ("mean", "std")))
+
+    def print_summary(self, evaluation_results):
+        """reference: pose_evaluator.py:200-240 — same console text, from the device-reduced statistics."""
+        stats = self.compute_summary_statistics(evaluation_results)
+        bar = "=" * 60
+        lines = ["\n" + bar, "POSE ESTIMATION EVALUATION SUMMARY", bar,
+                 f"\nNumber of frames evaluated: {len(evaluation_results['frames'])}"]
+        for title, metric, shown in self._SUMMARY_LAYOUT:
+            lines.append("\n" + title)
+            for s in shown:
+                lines.append(f"  {(s.capitalize() + ':'):<7} {stats[f'{metric}_{s}']:.2f}")
+        lines.append("\n" + bar + "\n")
+        print("\n".join(lines))

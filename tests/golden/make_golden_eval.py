@@ -49,7 +49,7 @@ def make_case(seed, n, convention, geometry):
 
 
 def main():
-    for name in ("plotly", "plotly.graph_objects"):
+    for name in ("plotly", "plotly.graph_objects", "plotly.subplots"):
         sys.modules.setdefault(name, types.ModuleType(name))
     sys.path.insert(0, REF)
     from src.core.pose_evaluator import PoseEvaluator
@@ -69,6 +69,18 @@ def main():
         out[p + "est_R"] = est_R; out[p + "est_t"] = est_t
         out[p + "errors"] = np.stack([res[m] for m in metrics], axis=1)
         out[p + "summary"] = np.array([[stats[f"{m}_{s}"] for s in ("mean", "std", "median", "max", "min")] for m in metrics])
+        if ci == 0:
+            # what the shipped pipeline does next (src/pipeline.py:160, :163): the console summary and the comparison table
+            import contextlib
+            import io
+            buf = io.StringIO()
+            with contextlib.redirect_stdout(buf):
+                ev.print_summary(res)
+            df = ev.create_comparison_dataframe(res)
+            with open(os.path.join(HERE, "eval_report_c0.txt"), "w") as f:
+                f.write(buf.getvalue())
+            with open(os.path.join(HERE, "eval_report_c0_columns.txt"), "w") as f:
+                f.write(",".join(df.columns) + "\n")
     np.savez_compressed(os.path.join(HERE, "eval_golden.npz"), **out)
     print("wrote eval_golden.npz:", {k: v.shape for k, v in out.items() if k.endswith("errors")})
 

@@ -35,7 +35,7 @@ def _cv2_canonical(img, c):
 
 def _check_pair(eng, c, pair_idx, slot, out):
     from rpe_b200 import _lib as L
-    from rpe_b200.synth import synth_K, synth_pair
+    from bench_support.synth import synth_K, synth_pair
     a, b = synth_pair(c["synth_cfg"], pair_idx, c["W"], c["H"])[:2]
     K = synth_K(c["W"], c["H"])
     assert out["status"][slot] == 0, out["status"][slot]          # ok, and no capacity overflow flag
@@ -69,7 +69,7 @@ def _check_pair(eng, c, pair_idx, slot, out):
 
 
 def test_cfg3_720p_5000_features_ratio_batch():
-    from rpe_b200.synth import synth_K, synth_batch
+    from bench_support.synth import synth_K, synth_batch
     c = CFG3
     eng = _engine(c, 3)
     try:
@@ -92,7 +92,7 @@ def test_cfg3_720p_5000_features_ratio_batch():
 
 
 def test_cfg4_4k_20000_features_8_levels():
-    from rpe_b200.synth import synth_K, synth_batch
+    from bench_support.synth import synth_K, synth_batch
     c = CFG4
     eng = _engine(c, 1)
     try:
@@ -109,7 +109,7 @@ def test_cfg3_full_bench_batch_properties():
     bit-identical R / t / euler / status / info wherever it sits in the batch, the same bits as a 16-pair batch
     (batch-size independence), the same bits through the asynchronous two-batches-pending path, and a pose within
     2 deg of the generator's ground-truth rotation for at least three pairs in four (planar scene, see below)."""
-    from rpe_b200.synth import synth_K, synth_batch, synth_pair
+    from bench_support.synth import synth_K, synth_batch, synth_pair
     c = CFG3
     U, T = 16, 16
     B = U * T
@@ -226,7 +226,7 @@ def test_cfg5_stream_shards_and_subsample_vs_cv2():
     nothing determinate to compare with; tools/gpu_diag_cfg5.py prints the stage-wise comparison at any stride
     (matches are bit-identical at every stride; pose within tolerance on 5 / 18 / 24 of 24 pairs at stride 1 / 8 / 16)."""
     from rpe_b200.sharding import shard_frames, shard_range
-    from rpe_b200.synth import stream_relative_pose, synth_K, synth_stream
+    from bench_support.synth import stream_relative_pose, synth_K, synth_stream
     c = CFG3
     F = 25
     K = synth_K(c["W"], c["H"])

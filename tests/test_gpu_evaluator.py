@@ -112,3 +112,14 @@ def test_stream_length_and_nan_propagation(engine):
     gt_pos[501] = gt_pos[500]
     errors2, summary2 = engine.evaluate_sequence(est_R, est_t, est_euler, gt_euler, gt_pos)
     assert np.isnan(errors2[501, 4]) and np.isnan(summary2[4]).all() and not np.isnan(summary2[:4]).any()
+
+
+def test_pipeline_call_sequence_on_the_twin(engine, capsys):
+    """INTEGRATION.md swaps the twin in where src/pipeline.py constructs PoseEvaluator; the pipeline then calls
+    print_summary (:160) and create_comparison_dataframe (:163).  Same text / columns as the unmodified reference."""
+    import rpe_b200
+    from test_oracle_evaluator import _TableGT, _pipeline_call_sequence, check_report_against_reference
+    c = list(_cases())[0]
+    ev = rpe_b200.PoseEvaluator(_TableGT(c), euler_convention="yup", engine=engine)
+    text, df, res = _pipeline_call_sequence(ev, c, capsys)
+    check_report_against_reference(text, df, res)

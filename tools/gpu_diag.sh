@@ -4,7 +4,7 @@ sys.path.insert(0, os.getcwd())
 import numpy as np, torch
 import bench
 import rpe_b200
-from rpe_b200.synth import synth_batch, synth_K
+from bench_support.synth import synth_batch, synth_K
 B,W,H=128,1280,720
 frames=synth_batch(3,0,B,W,H); K=synth_K(W,H)
 host=torch.from_numpy(frames).pin_memory(); dev=host.cuda()

@@ -4,7 +4,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import rpe_b200
 from rpe_b200 import _lib as L
-from rpe_b200.synth import synth_K, synth_stream, stream_relative_pose
+from bench_support.synth import synth_K, synth_stream, stream_relative_pose
 from oracle import geometry as og
 from oracle.reference_path import PathConfig, ReferencePath
 W, H, F = 1280, 720, int(os.environ.get("F", "25"))
