@@ -10,9 +10,12 @@ induced by a small random motion (rvec ~ U(-0.03,0.03)^3, t ~ U(-0.1,0.1)^3) of 
 looking at the plane z = 5; K = [[0.9W,0,W/2],[0,0.9W,H/2],[0,0,1]].
 
 Stream (config 5): ONE base texture per stream (seed = 1000*cfg + stream_idx) seen by a camera whose pose
-is a smooth bounded function of the frame index (three sinusoids per axis, random phase); frame k =
-the base texture warped by the plane homography of pose k, so consecutive frames differ by a small
-motion and any frame can be generated independently (shards need no state).
+is a smooth bounded function of the frame index (one sinusoid per axis, random phase); frame k =
+the base texture warped by the plane homography of pose k, so any frame can be generated independently
+(shards need no state).  The motion between CONSECUTIVE frames is sized like a config-3 pair's
+(|dt| ~ 0.03-0.2 per axis at scene depth 5, |dr| ~ 0.01-0.04 rad per axis: periods of 8-20 frames), so that
+stride-1 pairs have a determinate pose.  (Round 1 used periods of 40-120 frames: a per-frame baseline of ~1/400 of
+the depth, for which recoverPose's answer - cv2's too - is rounding noise)
 """
 from __future__ import annotations
 
@@ -77,10 +80,10 @@ def _stream_state(cfg: int, stream_idx: int, W: int, H: int):
     if key not in _STREAM_CACHE:
         rng = np.random.default_rng(1000 * cfg + stream_idx)
         base = synth_texture(rng, W, H)
-        # per axis: amplitude, angular frequency (periods of 40 .. 120 frames), phase
-        par = {"r_amp": rng.uniform(0.02, 0.05, 3), "r_w": 2 * np.pi / rng.uniform(40, 120, 3),
-               "r_ph": rng.uniform(0, 2 * np.pi, 3), "t_amp": rng.uniform(0.08, 0.2, 3),
-               "t_w": 2 * np.pi / rng.uniform(40, 120, 3), "t_ph": rng.uniform(0, 2 * np.pi, 3)}
+        # per axis: amplitude, angular frequency (periods of 8 .. 20 frames), phase
+        par = {"r_amp": rng.uniform(0.02, 0.05, 3), "r_w": 2 * np.pi / rng.uniform(8, 20, 3),
+               "r_ph": rng.uniform(0, 2 * np.pi, 3), "t_amp": rng.uniform(0.5, 0.9, 3),
+               "t_w": 2 * np.pi / rng.uniform(8, 20, 3), "t_ph": rng.uniform(0, 2 * np.pi, 3)}
         _STREAM_CACHE.clear()
         _STREAM_CACHE[key] = (base, par)
     return _STREAM_CACHE[key]

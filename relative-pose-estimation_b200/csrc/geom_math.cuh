@@ -48,16 +48,18 @@ RPE_HD int ransac_update_iters(double p, double ep, int model_points, int max_it
   return (denom >= 0 || -num >= max_iters * (-denom)) ? max_iters : f64_rint(num / denom);
 }
 
-// EMEstimatorCallback::computeError for one correspondence (f64 Sampson, stored as f32)
+// EMEstimatorCallback::computeError for one correspondence (f64 Sampson, stored as f32).  Every product and sum is
+// rounded on its own, in cv2's order (Matx row times vector left to right, then the dot product, then a + b + c + d):
+// given the same E and points the error is cv2's to the last bit, so `err <= threshold` decides as cv2 does.
 RPE_HD float sampson_err_f32(const double* E, double x1, double y1, double x2, double y2) {
-  const double Ex0 = E[0] * x1 + E[1] * y1 + E[2];
-  const double Ex1 = E[3] * x1 + E[4] * y1 + E[5];
-  const double Ex2 = E[6] * x1 + E[7] * y1 + E[8];
-  const double Et0 = E[0] * x2 + E[3] * y2 + E[6];
-  const double Et1 = E[1] * x2 + E[4] * y2 + E[7];
-  const double x2tEx1 = x2 * Ex0 + y2 * Ex1 + Ex2;
-  const double den = Ex0 * Ex0 + Ex1 * Ex1 + Et0 * Et0 + Et1 * Et1;
-  return (float)(x2tEx1 * x2tEx1 / den);
+  const double Ex0 = f64_add(f64_add(f64_mul(E[0], x1), f64_mul(E[1], y1)), E[2]);
+  const double Ex1 = f64_add(f64_add(f64_mul(E[3], x1), f64_mul(E[4], y1)), E[5]);
+  const double Ex2 = f64_add(f64_add(f64_mul(E[6], x1), f64_mul(E[7], y1)), E[8]);
+  const double Et0 = f64_add(f64_add(f64_mul(E[0], x2), f64_mul(E[3], y2)), E[6]);
+  const double Et1 = f64_add(f64_add(f64_mul(E[1], x2), f64_mul(E[4], y2)), E[7]);
+  const double x2tEx1 = f64_add(f64_add(f64_mul(x2, Ex0), f64_mul(y2, Ex1)), Ex2);
+  const double den = f64_add(f64_add(f64_add(f64_mul(Ex0, Ex0), f64_mul(Ex1, Ex1)), f64_mul(Et0, Et0)), f64_mul(Et1, Et1));
+  return (float)(f64_mul(x2tEx1, x2tEx1) / den);
 }
 
 // ------------------------------------------------------------------ five-point solver

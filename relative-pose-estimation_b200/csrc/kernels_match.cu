@@ -4,13 +4,15 @@
 // knnMatch(k=2) + ratio test.
 //
 // k_hamming: bound by the XU pipe (POPC, 16 lanes/clk/SM) and the ALU pipe (LOP3, 64 lanes/clk/SM) together,
-// not by HBM; carry-save adders on the ALU pipe (match_math.cuh) cut the POPCs per 256-bit distance from 8
-// to 5 or 4, the key arithmetic runs on the FMA pipe (IMAD), and the default variant alternates the 5- and
-// 4-POPC forms so that both pipes sit near 18/64 clk per distance.  Each thread keeps kQPT query
-// descriptors (8 x u32 each) in registers, train descriptors stream through a shared-memory
-// tile read with 128-bit broadcast loads; nearest / second nearest are tracked as packed
+// not by HBM.  Operands are linearly pre-combined (match_math.cuh: hamming_mix) so that three carry-save adders
+// cost one XOR (sum) + one LOP3 (carry) each; even train descriptors take the 11 LOP3 + 5 POPC form, odd ones the
+// 13 LOP3 + 4 POPC form, which balances the two pipes; the key arithmetic runs on the FMA pipe (IMAD).  Each
+// thread keeps kQPT query descriptors (8 x u32 each) in registers, train descriptors stream through a
+// shared-memory tile read with 128-bit broadcast loads; nearest / second nearest are tracked as packed
 // (dist << 20 | index) keys, which reproduces OpenCV's tie rule (lowest index) for free.
-#include <cstdlib>
+// Measured alternatives (B200, 128 pairs x 5000 x 5000, round 1): plain 8 XOR + 8 POPC 4.14 ms; three / four
+// adders 4.25 / 3.96 ms; + FMA-pipe keys and paired top-2 update 3.95 / 3.84 ms; pre-combined operands with four
+// adders 3.60, alternating 3.58 (this kernel), three adders 3.92 ms.
 #include "rpe_device.cuh"
 #include "match_math.cuh"
 
@@ -25,21 +27,22 @@ __device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) {
   return __vimin3_u32(a, b, c);   // VIMNMX3 on sm_100
 }
 
-// kFma: keys built with multiply-adds (FMA pipe) and two train descriptors folded per top-2 update;
-// kMix (with kFma): the even train descriptor of each pair uses three carry-save adders + five POPCs, the odd
-// one four adders + four POPCs, which balances the ALU pipe (LOP3) against the XU pipe (POPC)
-// kLin (with kFma): operands in the linearly pre-combined layout of match_math.cuh (hamming_mix): queries are
-// rewritten in registers, train descriptors when a thread stages them in shared memory (one descriptor per
-// thread); 13 LOP3 + 4 POPC per distance
-template <bool kTop2, bool kCsa4, bool kFma, bool kMix = false, bool kLin = false>
+// kTop2 (ratio mode, knnMatch k = 2): nearest and second nearest train descriptor of every query, view 1 -> view 2.
+// !kTop2 (cross-check mode): every distance D[q][t] is computed ONCE and feeds both directions: the row minimum
+// (nearest train descriptor of query q, key dist<<20|t) stays in the thread's registers as above; the column
+// minimum (nearest query of train descriptor t, key dist<<20|q) is the minimum over the warp's 64 queries - one
+// REDUX.MIN per warp and train descriptor - kept by lane t % 32, folded into a shared-memory minimum per tile slot
+// (one atomicMin per lane and 32 train descriptors) and flushed to bwd1 with one global atomicMin per CTA and train
+// descriptor.  Keys carry the index in the low bits, so ties go to the lowest index in both directions, as cv2's.
+template <bool kTop2>
 __global__ void __launch_bounds__(kMatchThreads)
 k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride, int pstep, uint32_t m20,
           int nsplit, uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
   __shared__ uint4 s_train[kTrainTile * 2];
+  __shared__ uint32_t s_col[kTrainTile];
   const int pair = blockIdx.y;
-  const int dir = blockIdx.z;                  // 0: view1 -> view2, 1: view2 -> view1
   // image slots of the two views: pstep = 2 (pair batch: 2p, 2p+1) or 1 (consecutive frames: p, p+1)
-  const int qi = pstep * pair + dir, ti = pstep * pair + 1 - dir;
+  const int qi = pstep * pair, ti = pstep * pair + 1;
   const int nq = kp_n[qi], nt_all = kp_n[ti];
   // blockIdx.x = query block * nsplit + split: each CTA scans one slice of the train set (finer work units: the
   // last wave of a launch stays full); slices are merged with atomicMin on the packed keys, see below
@@ -51,17 +54,20 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
   if (tbeg >= nt && nsplit > 1) return;
   const uint4* dq = reinterpret_cast<const uint4*>(desc + (size_t)qi * kp_stride * 32);
   const uint4* dt = reinterpret_cast<const uint4*>(desc + (size_t)ti * kp_stride * 32);
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
 
   uint32_t q[kQPT][8];
   uint32_t best1[kQPT], best2[kQPT];
+  int qidx[kQPT];
 #pragma unroll
   for (int k = 0; k < kQPT; ++k) {
+    // queries past the end repeat the last one: same keys, so they change neither a row nor a column minimum
     const int qq = min(q0 + tid + k * kMatchThreads, nq - 1);
+    qidx[k] = qq;
     const uint4 a = dq[2 * qq], b = dq[2 * qq + 1];
     q[k][0] = a.x; q[k][1] = a.y; q[k][2] = a.z; q[k][3] = a.w;
     q[k][4] = b.x; q[k][5] = b.y; q[k][6] = b.z; q[k][7] = b.w;
-    if (kLin) hamming_mix(q[k]);
+    hamming_mix(q[k]);
     best1[k] = 0xffffffffu;
     best2[k] = 0xffffffffu;
   }
@@ -69,19 +75,20 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
   for (int t0 = tbeg; t0 < nt; t0 += kTrainTile) {
     const int tn = min(kTrainTile, nt - t0);
     __syncthreads();
-    if (kLin) {
-      if (tid < tn) {
-        const uint4 a = dt[2 * (t0 + tid)], b = dt[2 * (t0 + tid) + 1];
-        uint32_t d[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-        hamming_mix(d);
-        s_train[2 * tid] = make_uint4(d[0], d[1], d[2], d[3]);
-        s_train[2 * tid + 1] = make_uint4(d[4], d[5], d[6], d[7]);
-      }
-    } else {
-      for (int i = tid; i < tn * 2; i += kMatchThreads) s_train[i] = dt[2 * t0 + i];
+    if (!kTop2 && t0 > tbeg && tid < kTrainTile) {           // flush the previous tile's column minima
+      const uint32_t v = s_col[tid];
+      if (v != 0xffffffffu) atomicMin(&bwd1[(size_t)pair * kp_stride + t0 - kTrainTile + tid], v);
+    }
+    if (!kTop2) s_col[tid] = 0xffffffffu;
+    if (tid < tn) {
+      const uint4 a = dt[2 * (t0 + tid)], b = dt[2 * (t0 + tid) + 1];
+      uint32_t d[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+      hamming_mix(d);
+      s_train[2 * tid] = make_uint4(d[0], d[1], d[2], d[3]);
+      s_train[2 * tid + 1] = make_uint4(d[4], d[5], d[6], d[7]);
     }
     __syncthreads();
-    if (kFma) {
+    if (kTop2) {
       // pairs of train descriptors: with m <= M the two new keys, the two smallest of {best1, best2, m, M}
       // are min(best1, m) and min(max(best1, m), best2, M): five min / max per two distances instead of six
       int j = 0;
@@ -90,44 +97,63 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
         const uint4 a0 = s_train[2 * j], b0 = s_train[2 * j + 1], a1 = s_train[2 * j + 2], b1 = s_train[2 * j + 3];
 #pragma unroll
         for (int k = 0; k < kQPT; ++k) {
-          const uint32_t k0 = kLin ? hamming256_mixed_key<kCsa4 && !kMix>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20)
-                                   : hamming256_key<kCsa4 && !kMix>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20);
-          const uint32_t k1 = kLin ? hamming256_mixed_key<kCsa4 || kMix>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20)
-                                   : hamming256_key<kCsa4 || kMix>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20);
-          if (kTop2) {
-            const uint32_t m = min(k0, k1), M = max(k0, k1);
-            best2[k] = umin3(max(best1[k], m), best2[k], M);
-            best1[k] = min(best1[k], m);
-          } else {
-            best1[k] = umin3(best1[k], k0, k1);
-          }
+          const uint32_t k0 = hamming256_mixed_key<false>(q[k], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20);
+          const uint32_t k1 = hamming256_mixed_key<true>(q[k], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20);
+          const uint32_t m = min(k0, k1), M = max(k0, k1);
+          best2[k] = umin3(max(best1[k], m), best2[k], M);
+          best1[k] = min(best1[k], m);
         }
       }
       if (j < tn) {
         const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
 #pragma unroll
         for (int k = 0; k < kQPT; ++k) {
-          const uint32_t key = kLin ? hamming256_mixed_key<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20)
-                                    : hamming256_key<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20);
-          if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
+          const uint32_t key = hamming256_mixed_key<false>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20);
+          best2[k] = min(best2[k], max(best1[k], key));
           best1[k] = min(best1[k], key);
         }
       }
     } else {
-#pragma unroll 4
-      for (int j = 0; j < tn; ++j) {
-        const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
-#pragma unroll
-        for (int k = 0; k < kQPT; ++k) {
-          const uint32_t d = hamming256<kCsa4>(q[k], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w);
-          const uint32_t key = pack_nn(d, (uint32_t)(t0 + j));
-          if (kTop2) best2[k] = min(best2[k], max(best1[k], key));
-          best1[k] = min(best1[k], key);
+      // column key of (q, t) = row key + (q - t): the distance bits are shared
+      const int dq0 = qidx[0] - t0, dq1 = qidx[1] - t0;
+      for (int jb = 0; jb < tn; jb += 32) {
+        uint32_t mine = 0xffffffffu;                         // column minimum of train descriptor t0 + jb + lane
+        const int je = min(jb + 32, tn);
+        int j = jb;
+#pragma unroll 2
+        for (; j + 1 < je; j += 2) {
+          const uint4 a0 = s_train[2 * j], b0 = s_train[2 * j + 1], a1 = s_train[2 * j + 2], b1 = s_train[2 * j + 3];
+          const uint32_t r00 = hamming256_mixed_key<false>(q[0], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20);
+          const uint32_t r10 = hamming256_mixed_key<false>(q[1], a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w, (uint32_t)(t0 + j), m20);
+          const uint32_t r01 = hamming256_mixed_key<true>(q[0], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20);
+          const uint32_t r11 = hamming256_mixed_key<true>(q[1], a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w, (uint32_t)(t0 + j + 1), m20);
+          best1[0] = umin3(best1[0], r00, r01);
+          best1[1] = umin3(best1[1], r10, r11);
+          const uint32_t c0 = __reduce_min_sync(0xffffffffu, min(r00 + (uint32_t)(dq0 - j), r10 + (uint32_t)(dq1 - j)));
+          const uint32_t c1 = __reduce_min_sync(0xffffffffu, min(r01 + (uint32_t)(dq0 - j - 1), r11 + (uint32_t)(dq1 - j - 1)));
+          if (lane == ((j - jb) & 31)) mine = c0;
+          if (lane == ((j + 1 - jb) & 31)) mine = c1;
         }
+        if (j < je) {
+          const uint4 a = s_train[2 * j], b = s_train[2 * j + 1];
+          const uint32_t r0 = hamming256_mixed_key<false>(q[0], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20);
+          const uint32_t r1 = hamming256_mixed_key<false>(q[1], a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, (uint32_t)(t0 + j), m20);
+          best1[0] = min(best1[0], r0);
+          best1[1] = min(best1[1], r1);
+          const uint32_t c = __reduce_min_sync(0xffffffffu, min(r0 + (uint32_t)(dq0 - j), r1 + (uint32_t)(dq1 - j)));
+          if (lane == ((j - jb) & 31)) mine = c;
+        }
+        if (jb + lane < tn) atomicMin(&s_col[jb + lane], mine);
       }
     }
   }
-  uint32_t* o1 = (dir == 0 ? fwd1 : bwd1) + (size_t)pair * kp_stride;
+  if (!kTop2) {                                              // column minima of the last tile
+    __syncthreads();
+    const int t_last = tbeg + ((nt - tbeg - 1) / kTrainTile) * kTrainTile;
+    const uint32_t v = s_col[tid];
+    if (t_last + tid < nt && v != 0xffffffffu) atomicMin(&bwd1[(size_t)pair * kp_stride + t_last + tid], v);
+  }
+  uint32_t* o1 = fwd1 + (size_t)pair * kp_stride;
 #pragma unroll
   for (int k = 0; k < kQPT; ++k) {
     const int qq = q0 + tid + k * kMatchThreads;
@@ -153,38 +179,20 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
 // train-set slices per query block.  Finer work units keep every SM busy to the end of the launch (B200, 128 pairs x
 // 5000 x 5000: 3.58 / 3.41 / 3.38 ms with 1 / 4 / 8 slices); a slice keeps >= ~5 shared-memory tiles of work so
 // that loading the queries and the three atomics per query stay negligible
-static int pick_nsplit(int nfeatures) {
-  static const int forced = getenv("RPE_MATCH_SPLIT") ? atoi(getenv("RPE_MATCH_SPLIT")) : 0;   // tuning knob
-  if (forced > 0) return forced;
-  return max(1, min(32, (nfeatures + 5 * kTrainTile / 2) / (5 * kTrainTile)));
-}
+static int pick_nsplit(int nfeatures) { return max(1, min(32, (nfeatures + 5 * kTrainTile / 2) / (5 * kTrainTile))); }
 
 void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int nfeatures, int n_pairs, int pstep,
                   int mode, cudaStream_t s, int* launches) {
   const int qblocks = (kp_stride + kQPB - 1) / kQPB;
-  static const int variant = getenv("RPE_MATCH_VARIANT") ? atoi(getenv("RPE_MATCH_VARIANT")) : 6;   // tuning knob (B200: 4.14 / 4.25 / 3.96 / 3.95 / 3.84 / 3.60 / 3.58 / 3.92 ms for 0..7)
   const bool top2 = mode == RPE_MATCH_RATIO;
-
-  // 0: CSA3, 1: CSA4, 2: CSA3 + FMA-pipe keys + paired update, 3: CSA4 + FMA-pipe keys + paired update,
-  // 4: as 2 / 3 with CSA3 and CSA4 alternating
-  // 5: pre-combined operands, CSA4 (13 LOP3 + 4 POPC); 6: pre-combined, CSA3 / CSA4 alternating; 7: pre-combined, CSA3
-  auto k = top2 ? (variant == 5 ? k_hamming<true, true, true, false, true> : variant == 6 ? k_hamming<true, false, true, true, true>
-                   : variant == 7 ? k_hamming<true, false, true, false, true> : variant == 1 ? k_hamming<true, true, false> : variant == 2 ? k_hamming<true, false, true>
-                   : variant == 3 ? k_hamming<true, true, true> : variant == 4 ? k_hamming<true, false, true, true>
-                   : k_hamming<true, false, false>)
-                : (variant == 5 ? k_hamming<false, true, true, false, true> : variant == 6 ? k_hamming<false, false, true, true, true>
-                   : variant == 7 ? k_hamming<false, false, true, false, true> : variant == 1 ? k_hamming<false, true, false> : variant == 2 ? k_hamming<false, false, true>
-                   : variant == 3 ? k_hamming<false, true, true> : variant == 4 ? k_hamming<false, false, true, true>
-                   : k_hamming<false, false, false>);
-  const int ndir = top2 ? 1 : 2;
   const int nsplit = pick_nsplit(min(nfeatures, kp_stride));
-  if (nsplit > 1) {
-    const size_t bytes = (size_t)n_pairs * kp_stride * sizeof(uint32_t);
-    cudaMemsetAsync(mb.fwd1, 0xff, bytes, s);
-    cudaMemsetAsync(top2 ? mb.fwd2 : mb.bwd1, 0xff, bytes, s);
-  }
-  dim3 grid(qblocks * nsplit, n_pairs, ndir);
-  k<<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, nsplit, mb.fwd1, mb.fwd2, mb.bwd1);
+  const size_t bytes = (size_t)n_pairs * kp_stride * sizeof(uint32_t);
+  if (nsplit > 1) cudaMemsetAsync(mb.fwd1, 0xff, bytes, s);
+  if (top2 && nsplit > 1) cudaMemsetAsync(mb.fwd2, 0xff, bytes, s);
+  if (!top2) cudaMemsetAsync(mb.bwd1, 0xff, bytes, s);       // column minima always arrive through atomicMin
+  dim3 grid(qblocks * nsplit, n_pairs);
+  if (top2) k_hamming<true><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, nsplit, mb.fwd1, mb.fwd2, mb.bwd1);
+  else k_hamming<false><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, nsplit, mb.fwd1, mb.fwd2, mb.bwd1);
   ++*launches;
 }
 

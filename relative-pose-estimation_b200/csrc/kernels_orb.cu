@@ -141,15 +141,15 @@ k_resize_strip(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, con
 
 
 // Same strip, source rows staged first: the thread requests ALL source rows of its strip (<= kResizeSrcRows rows x
-// three words) into its own shared-memory column (through registers, or with 4-byte cp.async: kViaRegs) and only
-// then walks down the strip, reading rows back with LDS.  k_resize_strip keeps one row in flight per thread and waits on it row after row (ncu:
-// 37 % of its stall samples on the row-advance); here one round trip covers the strip.  A thread reads only what it
-// staged itself, so cp.async.wait_group is the only synchronisation.  Chosen on the host when every strip of the
-// level chain spans <= kResizeSrcRows source rows (scale <= ~1.25), else k_resize_strip.
+// three words) up front, parks them in its own shared-memory column and only then walks down the strip, reading rows
+// back with LDS.  k_resize_strip keeps one row in flight per thread and waits on it row after row (ncu: 37 % of its
+// stall samples on the row-advance); here one round trip covers the strip.  A thread reads only what it staged
+// itself, so no barrier is needed.  Chosen on the host when every strip of the level chain spans <= kResizeSrcRows
+// source rows (scale <= ~1.25), else k_resize_strip.  (Staging with 4-byte cp.async instead of LDG + STS was equally
+// fast alone and 3 % slower end to end with the next batch uploading beside it: B200, 256 pairs, 1.89 vs 1.81 ms.)
 constexpr int kResizeSrcRows = 11;
 constexpr int kResizeStageBytes = kResizeSrcRows * 3 * 256 * 4;
 
-template <bool kViaRegs>
 __global__ void __launch_bounds__(256)
 k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,
                 int level) {
@@ -170,8 +170,7 @@ k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, co
   const int xbase = __ldg(&taps[d.xtab + min(x4, d.w - 1)]).x;
   const int abase = xbase & ~3, sh8 = (xbase & 3) * 8;
   const int sp = s.pitch, last_row = s.h - 1;
-  if (kViaRegs) {
-    // the same rows through registers (LDG then STS) instead of LDGSTS
+  {
     uint32_t rr[kResizeSrcRows][3];
 #pragma unroll
     for (int i = 0; i < kResizeSrcRows; ++i) {
@@ -183,18 +182,6 @@ k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, co
     for (int i = 0; i < kResizeSrcRows; ++i)
 #pragma unroll
       for (int k = 0; k < 3; ++k) s_rows[(i * 3 + k) * 256 + tid] = rr[i][k];
-  } else {
-    const uint32_t sdst = smem_u32(s_rows + tid);
-#pragma unroll
-    for (int i = 0; i < kResizeSrcRows; ++i) {
-      if (i < n_src) {
-        const uint8_t* p = src + (size_t)min(ra0 + i, last_row) * sp + abase;
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + (uint32_t)((i * 3 + k) * 256 * 4)), "l"(p + 4 * k) : "memory");
-      }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
   }
   // horizontal taps of the four columns (while the rows are in flight)
   uint32_t sel[4], wgt[4];
@@ -217,7 +204,6 @@ k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, co
   int2 tys[kResizeRows];
 #pragma unroll
   for (int j = 0; j < kResizeRows; ++j) tys[j] = __ldg(&taps[d.ytab + min(y_first + j, d.h - 1)]);
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
   uint8_t* out = dst + (size_t)y_first * d.pitch + x4;
 #pragma unroll
   for (int j = 0; j < kResizeRows; ++j) {
@@ -239,16 +225,10 @@ k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, co
 void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   for (int l = 1; l < g.nlevels; ++l) {
     const LevelGeom& d = g.lv[l];
-    // tuning knobs: first level built by k_resize_staged (0 = never) and the levels below which the rows are staged
-    // through registers (LDG + STS) rather than LDGSTS.  B200, 256 pairs: never staged 2.20 ms; LDGSTS from level 2
-    // 1.89 ms (from level 1 the end-to-end rate, with the next batch uploading beside it, DROPS 3 %); registers
-    // on every level 1.81 ms with no end-to-end penalty -> the default
-    static const int staged_from = getenv("RPE_RESIZE_STAGED") ? atoi(getenv("RPE_RESIZE_STAGED")) : 1;
-    static const int via_regs = getenv("RPE_RESIZE_REGS") ? atoi(getenv("RPE_RESIZE_REGS")) : 99;
-    if (g.resize_strip_ok && g.resize_span <= kResizeSrcRows && staged_from > 0 && l >= staged_from) {
+    // B200, 256 pairs: k_resize_strip on every level 2.20 ms; k_resize_staged on every level 1.81 ms
+    if (g.resize_strip_ok && g.resize_span <= kResizeSrcRows) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
-      if (l < via_regs) k_resize_staged<true><<<grid, block, kResizeStageBytes, s>>>(g, b.pyr, b.taps, l);
-      else k_resize_staged<false><<<grid, block, kResizeStageBytes, s>>>(g, b.pyr, b.taps, l);
+      k_resize_staged<<<grid, block, kResizeStageBytes, s>>>(g, b.pyr, b.taps, l);
     } else if (g.resize_strip_ok) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
       k_resize_strip<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
@@ -260,15 +240,7 @@ void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream
   }
 }
 
-// flat tile index -> (level, tile x, tile y)
-__device__ __forceinline__ int find_level(const OrbGeom& g, int tile) {
-  int l = 0;
-#pragma unroll 1
-  for (int i = 1; i < g.nlevels; ++i)
-    if (tile >= g.lv[i].tile0) l = i;
-  return l;
-}
-
+namespace fast_v1 {
 // ------------------------------------------------------------------ K2: FAST-9 + 3x3 NMS + border
 // One CTA (8 warps) = one 120x30 tile of one level of one image (tile table: ftab); the scored
 // region (tile + 1) is 32 rows x 32 aligned pixel quads, one warp per row, four rows per warp.
@@ -341,7 +313,7 @@ constexpr int kFastTilesPerCta = RPE_FAST_TILES;   // consecutive tiles of one i
 #define RPE_FAST_MINB 6
 #endif
 __global__ void __launch_bounds__(256, RPE_FAST_MINB)
-k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
+k_fast_v1(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
        int n_img, uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
   __shared__ __align__(128) uint8_t simg2[2][kFastIH * kFastIP];
   __shared__ __align__(16) uint8_t ssc[kFastSH * kFastSP];
@@ -463,10 +435,212 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
   }
 }
 
-void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
+static void launch_fast_v1(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   if (g.total_ftiles == 0) return;
   dim3 grid((g.total_ftiles + kFastTilesPerCta - 1) / kFastTilesPerCta, n_img);
-  k_fast<<<grid, 256, 0, s>>>(g, b.pyr, b.ftab, n_img, b.cand_key, b.cand_cnt, b.hist);
+  k_fast_v1<<<grid, 256, 0, s>>>(g, b.pyr, b.ftab, n_img, b.cand_key, b.cand_cnt, b.hist);
+  ++*launches;
+}
+
+}  // namespace fast_v1
+using fast_v1::launch_fast_v1;
+
+// ------------------------------------------------------------------ K2: FAST-9 + 3x3 NMS + border
+// One WARP = one 120x30 tile of one level of one image (flat tile table: ftab).  Warps are independent: own slice
+// of shared memory, own mbarrier, no CTA-wide barrier.  The scored region (tile + 1 px for the NMS neighbours) is
+// 32 rows x 32 aligned pixel quads: lane = quad column, the warp walks down the 32 rows.
+//  (1) TMA: one bulk copy per image row of the tile (+halo) onto the warp's mbarrier (UBLKCP), issued by the lanes;
+//      the score tile is cleared while the rows are in flight;
+//  (2) packed pre-test, four pixels per lane and row (fast_compass4_unpacked): the unpacked column word of an image
+//      row is kept in a 7-row register window and serves as D, C and U of three score rows.  The pass bits of the
+//      lane's 32 x 4 pixels collect in four registers (one per band of 8 rows);
+//  (3) compaction per CANDIDATE, not per pixel: one warp scan over the lanes' candidate counts, then every lane
+//      expands its own set bits into the warp's queue.  A lane owns 128 pixels (~4 candidates, worst lane ~10), so
+//      the lanes' loops are short and even - with 16 pixels per thread (one CTA per tile, four rows per warp) the
+//      same loop ran to a worst lane of ~6 against a mean of 0.5, and the per-pixel predicated stores that replaced
+//      it cost 133 instructions per thread and tile (9.5 per pixel; ncu, round 1);
+//  (4) one lane per queued pixel: FAST-9 corner test + score in one packed min/max network (fast9_score) -> score
+//      tile; the corners are compacted in place at the head of the queue (ballot);
+//  (5) one lane per corner: strict 3x3 NMS on the score tile, 31-px border filter, append
+//      (score<<24 | y<<12 | x) to the level's candidate list + score histogram.
+// A tile with more candidates than the queue holds (dense noise) is processed band by band and its NMS scans the
+// score tile instead of a corner list.
+constexpr int kFastIP = 160;                 // staged bytes per image row (16-B aligned start)
+constexpr int kFastIH = kFastTH + 8;         // image rows y0-4 .. y0+TH+3
+constexpr int kFastSP = 128;                 // score tile pitch: x0-4 .. x0+123
+constexpr int kFastSH = kFastTH + 2;         // score rows y0-1 .. y0+TH
+constexpr int kFastIPW = kFastIP / 4;
+static_assert(kFastSH == 32 && kFastTW + 8 == kFastSP, "32 score rows in four bands of 8, 32 quads per row");
+// unpack a column word into its two u16x2 halves ONCE: volatile keeps ptxas from re-deriving them from the raw word
+// at each of the three rows that use them (it prefers the PRMTs to the registers: 7.7 instead of 6 per row)
+__device__ __forceinline__ void fast_unpack_keep(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  asm volatile("prmt.b32 %0, %1, 0, 0x4140;" : "=r"(lo) : "r"(w));
+  asm volatile("prmt.b32 %0, %1, 0, 0x4342;" : "=r"(hi) : "r"(w));
+}
+constexpr int kFastWarps = 4;                // independent warps (tiles) per CTA
+constexpr int kFastQueue = 1024;             // queue entries per warp; a band of 8 rows x 128 px always fits
+
+struct __align__(16) FastWarpSmem {
+  uint8_t img[kFastIH * kFastIP];
+  uint8_t score[kFastSH * kFastSP];
+  uint16_t queue[kFastQueue];
+  uint64_t bar;
+  uint64_t pad;
+};
+static_assert(sizeof(FastWarpSmem) % 16 == 0, "warp slices stay 16-byte aligned");
+
+__global__ void __launch_bounds__(kFastWarps * 32, 4)
+k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
+       uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
+  extern __shared__ __align__(128) uint8_t s_fast[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int item = blockIdx.x * kFastWarps + warp, img = blockIdx.y;
+  if (item >= g.total_ftiles) return;                       // warps are independent: no CTA-wide barrier below
+  FastWarpSmem& S = *reinterpret_cast<FastWarpSmem*>(s_fast + warp * sizeof(FastWarpSmem));
+  const uint32_t te = __ldg(ftab + item);                   // level<<24 | ty<<12 | tx
+  const int level = te >> 24;
+  const LevelGeom& L = g.lv[level];
+  const int x0 = kFastOrigin + (int)(te & 0xfff) * kFastTW, y0 = kFastOrigin + (int)((te >> 12) & 0xfff) * kFastTH;
+  const int astart = (x0 - 8) & ~15;
+  const int pitch = L.pitch, lw = L.w, lh = L.h;
+  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off + (size_t)(y0 - 4) * pitch + astart;
+
+  // (1) rows y0-4 .. y0+TH+3, columns astart .. astart+159, clipped to the level buffer.  Bytes outside the level
+  //     are never read for a pixel that can become a candidate
+  const uint32_t row_bytes = (uint32_t)min(kFastIP, pitch - astart);
+  const int n_rows = min(kFastIH, lh - (y0 - 4));
+  if (lane == 0) {
+    mbar_init(&S.bar, 1);
+    mbar_arrive_expect_tx(&S.bar, row_bytes * (uint32_t)n_rows);
+  }
+  __syncwarp();
+  for (int r = lane; r < n_rows; r += 32) bulk_copy_g2s(S.img + r * kFastIP, src + (size_t)r * pitch, row_bytes, &S.bar);
+#pragma unroll
+  for (int i = 0; i < kFastSH * kFastSP / (16 * 32); ++i) reinterpret_cast<uint4*>(S.score)[i * 32 + lane] = make_uint4(0, 0, 0, 0);
+  const int thr = g.fast_threshold;
+  const uint32_t t4 = (uint32_t)min(thr, 127) * 0x01010101u;
+  // scores are only ever needed for x in [30, w-30), y in [30, h-30)
+  const int xlo = max(30, x0 - 1), xhi = min(lw - 30, x0 + kFastTW + 1);
+  const int ylo = max(30, y0 - 1), yhi = min(lh - 30, y0 + kFastTH + 1);
+  const int ib = x0 - 4 - astart;                            // staged byte column of score column 0 (4 or 12)
+  const int xq = x0 - 4 + 4 * lane;                          // first pixel of this lane's quad
+  const int lo = min(max(xlo - xq, 0), 4), hi = min(max(xhi - xq, 0), 4);
+  const uint32_t vmask = (uint32_t)(0x80808080ull << (8 * lo)) & (uint32_t)(0x80808080ull >> (8 * (4 - hi)));
+  const uint32_t* wimg = reinterpret_cast<const uint32_t*>(S.img) + (ib >> 2) + lane;   // this lane's word of image row 0
+  mbar_wait(&S.bar, 0);
+
+  // (2) score row sr = image rows sr (U), sr + 3 (C), sr + 6 (D); window slot of image row r = r % 7.  Straight
+  //     line: rows outside [ylo, yhi) (first / last tile row of a level only) are computed and masked out
+  uint32_t wl[7], wh[7];
+#pragma unroll
+  for (int r = 0; r < 6; ++r) fast_unpack_keep(wimg[r * kFastIPW], wl[r], wh[r]);
+  const uint32_t kt = fast_compass_kt(t4);
+  const int sr_lo = ylo - (y0 - 1), sr_n = yhi - ylo;       // valid score rows: sr_lo <= sr < sr_lo + sr_n
+  uint32_t m[4] = {0u, 0u, 0u, 0u};                          // bit 7 - k of byte j of m[b] = score row 8 b + k, pixel j of the quad
+#pragma unroll
+  for (int sr = 0; sr < kFastSH; ++sr) {
+    fast_unpack_keep(wimg[(sr + 6) * kFastIPW], wl[(sr + 6) % 7], wh[(sr + 6) % 7]);
+    const uint32_t* row = wimg + (sr + 3) * kFastIPW;
+    const uint32_t rmask = (uint32_t)(sr - sr_lo) < (uint32_t)sr_n ? vmask : 0u;
+    const uint32_t cw = fast_compass4_unpacked(wl[(sr + 3) % 7], wh[(sr + 3) % 7], wl[sr % 7], wh[sr % 7],
+                                               wl[(sr + 6) % 7], wh[(sr + 6) % 7], row[-1], row[0], row[1], kt) & rmask;
+    m[sr >> 3] |= cw >> (sr & 7);
+  }
+
+  const uint32_t lt = (1u << lane) - 1u;
+  // queue the set bits of the bands in mm[] (all four, or one with the others zero); returns the warp's total
+  auto push = [&](const uint32_t* mm) -> int {
+    const int c = __popc(mm[0]) + __popc(mm[1]) + __popc(mm[2]) + __popc(mm[3]);
+    int inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
+    }
+    uint16_t* out = S.queue + (inc - c);
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      uint32_t bits = mm[b];
+      while (bits) {
+        const int p = __ffs(bits) - 1;                       // bit p: pixel p >> 3 of the quad, row 8 b + 7 - (p & 7)
+        bits &= bits - 1u;
+        *out++ = (uint16_t)(((8 * b + 7 - (p & 7)) << 7) | (4 * lane + (p >> 3)));
+      }
+    }
+    __syncwarp();
+    return __shfl_sync(0xffffffffu, inc, 31);
+  };
+  // (4) corner test + score of the queued pixels; corners are compacted in place (they never outrun the reads:
+  //     n_corner <= entries consumed, and a round's entries are in registers before its ballot)
+  auto score = [&](int total) -> int {
+    int n_corner = 0;
+    for (int base = 0; base < total; base += 32) {
+      const int i = base + lane;
+      int e = 0, sc = 0;
+      if (i < total) {
+        e = S.queue[i];
+        sc = fast9_score(&S.img[((e >> 7) + 3) * kFastIP + ib + (e & 127)], kFastIP, thr);
+      }
+      const uint32_t bal = __ballot_sync(0xffffffffu, sc > 0);
+      if (sc > 0) {
+        S.score[e] = (uint8_t)sc;
+        S.queue[n_corner + __popc(bal & lt)] = (uint16_t)e;
+      }
+      n_corner += __popc(bal);
+    }
+    __syncwarp();
+    return n_corner;
+  };
+  // (5) NMS + border filter + append, for the corner at score-tile offset e
+  uint32_t* cnt = cand_cnt + img * g.nlevels + level;
+  uint32_t* hst = hist + (size_t)(img * g.nlevels + level) * 256;
+  uint32_t* out_key = cand_key + (size_t)img * g.cand_stride + L.cand_off;
+  const uint32_t cap = (uint32_t)L.cand_cap;
+  auto nms = [&](int e) {
+    const int sr = e >> 7, c = e & 127;
+    if (sr < 1 || sr > kFastTH || c < 4 || c >= 4 + kFastTW) return;
+    const int x = x0 - 4 + c, y = y0 - 1 + sr;
+    if (x < 31 || x >= lw - 31 || y < 31 || y >= lh - 31) return;
+    const uint8_t* p = &S.score[e];
+    const int s = p[0];
+    const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
+                      s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
+    if (!keep) return;
+    const uint32_t pos = atomicAdd(cnt, 1u);
+    if (pos < cap) out_key[pos] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+    atomicAdd(&hst[s], 1u);
+  };
+
+  int all = __popc(m[0]) + __popc(m[1]) + __popc(m[2]) + __popc(m[3]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) all += __shfl_xor_sync(0xffffffffu, all, o);
+  if (all == 0) return;
+  if (all <= kFastQueue) {
+    const int n_corner = score(push(m));
+    for (int i = lane; i < n_corner; i += 32) nms(S.queue[i]);
+  } else {
+    // dense tile: band by band (a band is at most 8 x 128 = kFastQueue pixels), then NMS over the score tile
+#pragma unroll 1
+    for (int b = 0; b < 4; ++b) {
+      // (selects instead of a dynamic register index)
+      const uint32_t one[4] = {b == 0 ? m[0] : 0u, b == 1 ? m[1] : 0u, b == 2 ? m[2] : 0u, b == 3 ? m[3] : 0u};
+      score(push(one));
+    }
+    for (int sr = 1; sr <= kFastTH; ++sr) {
+      const uint32_t w = reinterpret_cast<const uint32_t*>(S.score)[sr * (kFastSP / 4) + lane];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if ((w >> (8 * j)) & 0xffu) nms(sr * kFastSP + 4 * lane + j);
+    }
+  }
+}
+
+void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
+  if (g.total_ftiles == 0) return;
+  static const bool v1 = getenv("RPE_FAST_V1") != nullptr;   // TEMPORARY A/B against the round-1 kernel
+  if (v1) { launch_fast_v1(g, b, n_img, s, launches); return; }
+  dim3 grid((g.total_ftiles + kFastWarps - 1) / kFastWarps, n_img);
+  k_fast<<<grid, kFastWarps * 32, kFastWarps * sizeof(FastWarpSmem), s>>>(g, b.pyr, b.ftab, b.cand_key, b.cand_cnt, b.hist);
   ++*launches;
 }
 
@@ -1012,6 +1186,8 @@ int setup_orb_attributes(int sort_cap) {
   build_ori_table(ori);
   if (cudaMemcpyToSymbol(kOriTab_dev, ori, sizeof ori) != cudaSuccess) return 1;
   if (cudaFuncSetAttribute(k_blur, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kBlurWarpBytes) != cudaSuccess) return 1;
+  if (cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kFastWarps * sizeof(FastWarpSmem))) != cudaSuccess) return 1;
+  if (cudaFuncSetAttribute(k_fast, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) != cudaSuccess) return 1;
   return (int)cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_cap * 8);
 }
 

@@ -188,15 +188,23 @@ RPE_HD uint32_t fast_compass2(uint32_t c, uint32_t n, uint32_t s, uint32_t e, ui
   const uint32_t dark = umax16x2(umin16x2(n, s), umin16x2(e, w));
   return (bright + (kt - c)) | ((kt + c) - dark);
 }
-RPE_HD uint32_t fast_compass4(uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t U, uint32_t D, uint32_t t4) {
+// The same test with the column words already unpacked (k_fast keeps the unpacked words of the rows above / below in
+// a register window while it walks down a tile: the word of a row serves as D, C and U of three output rows).
+// clo / chi = bytes {0, 1} / {2, 3} of the centre word as u16 lanes (fast_unpack_lo / _hi), same for U and D.
+RPE_HD uint32_t fast_unpack_lo(uint32_t w) { return prmt(w, 0, 0x4140); }
+RPE_HD uint32_t fast_unpack_hi(uint32_t w) { return prmt(w, 0, 0x4342); }
+RPE_HD uint32_t fast_compass_kt(uint32_t t4) { return 0x7fff7fffu - (t4 & 0x00ff00ffu); }
+RPE_HD uint32_t fast_compass4_unpacked(uint32_t clo, uint32_t chi, uint32_t ulo, uint32_t uhi, uint32_t dlo, uint32_t dhi,
+                                       uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t kt) {
   const uint32_t E = (C >> 24) | (Rw << 8);                // pixels x+3 .. x+6
   const uint32_t W = (Lw >> 8) | (C << 24);                // pixels x-3 .. x
-  const uint32_t kt = 0x7fff7fffu - (t4 & 0x00ff00ffu);
-  const uint32_t lo = fast_compass2(prmt(C, 0, 0x4140), prmt(U, 0, 0x4140), prmt(D, 0, 0x4140), prmt(E, 0, 0x4140),
-                                    prmt(W, 0, 0x4140), kt);
-  const uint32_t hi = fast_compass2(prmt(C, 0, 0x4342), prmt(U, 0, 0x4342), prmt(D, 0, 0x4342), prmt(E, 0, 0x4342),
-                                    prmt(W, 0, 0x4342), kt);
+  const uint32_t lo = fast_compass2(clo, ulo, dlo, fast_unpack_lo(E), fast_unpack_lo(W), kt);
+  const uint32_t hi = fast_compass2(chi, uhi, dhi, fast_unpack_hi(E), fast_unpack_hi(W), kt);
   return prmt(lo, hi, 0x7531) & 0x80808080u;
+}
+RPE_HD uint32_t fast_compass4(uint32_t Lw, uint32_t C, uint32_t Rw, uint32_t U, uint32_t D, uint32_t t4) {
+  return fast_compass4_unpacked(fast_unpack_lo(C), fast_unpack_hi(C), fast_unpack_lo(U), fast_unpack_hi(U),
+                                fast_unpack_lo(D), fast_unpack_hi(D), Lw, C, Rw, fast_compass_kt(t4));
 }
 
 // ------------------------------------------------------------------ A.5 Harris response

@@ -60,6 +60,22 @@ RPE_HD float f32_div(float a, float b) {
 #endif
 }
 RPE_HD float f32_fma(float a, float b, float c) { return fmaf(a, b, c); }
+// individually rounded f64 operations, for the places where a discrete decision of the reference hangs on the last
+// bit (cv2 is built without FMA contraction; nvcc contracts a*b+c by default)
+RPE_HD double f64_mul(double a, double b) {
+#if defined(__CUDA_ARCH__)
+  return __dmul_rn(a, b);
+#else
+  return a * b;
+#endif
+}
+RPE_HD double f64_add(double a, double b) {
+#if defined(__CUDA_ARCH__)
+  return __dadd_rn(a, b);
+#else
+  return a + b;
+#endif
+}
 // round half to even (cvRound)
 RPE_HD int f32_rint(float a) {
 #if defined(__CUDA_ARCH__)

@@ -91,16 +91,52 @@ def test_cfg3_720p_5000_features_ratio_batch():
         eng.close()
 
 
-def test_cfg4_4k_20000_features_8_levels():
+def _check_many(c, first_pair, n, name, max_pairs=None):
+    """n consecutive synthetic pairs, starting at pair index first_pair, as ONE batch; every pair through _check_pair.
+    Records which data-dependent paths the pairs exercised (gpurun_out/<name>.json): RANSAC iterations per pair (more
+    than 16 = more than one round; more than 64 = the large-round path of k_ransac), keypoint counts above nfeatures
+    (retainBest ties kept in the head-room), pairs at the max_matches cut."""
+    import json
+    import os
     from bench_support.synth import synth_K, synth_batch
-    c = CFG4
-    eng = _engine(c, 1)
+    from conftest import ROOT
+    eng = _engine(c, max_pairs or n)
     try:
-        frames = synth_batch(c["synth_cfg"], 0, 1, c["W"], c["H"])
+        frames = synth_batch(c["synth_cfg"], first_pair, n, c["W"], c["H"])
         out = eng.estimate_batch_interleaved(frames, synth_K(c["W"], c["H"]))
-        _check_pair(eng, c, 0, 0, out)
+        failures = []
+        nkp = []
+        for i in range(n):
+            nkp.append([len(eng.keypoints(i, v)["x"]) for v in (0, 1)])
+            try:
+                _check_pair(eng, c, first_pair + i, i, out)
+            except AssertionError as e:
+                failures.append((first_pair + i, str(e)[:300]))
+        iters = out["info"][:, 3].tolist()
+        stats = {"first_pair": first_pair, "pairs": n, "failures": failures, "ransac_iterations": iters,
+                 "pairs_with_more_than_one_ransac_round": int(sum(i > 16 for i in iters)),
+                 "pairs_on_the_large_round_path": int(sum(i > 64 for i in iters)),
+                 "images_with_retainbest_ties_kept": int(sum(k > c["nfeatures"] for kk in nkp for k in kk)),
+                 "pairs_at_the_match_cut": int((out["info"][:, 0] == 500).sum()),
+                 "keypoints_min_max": [int(np.min(nkp)), int(np.max(nkp))]}
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        json.dump(stats, open(os.path.join(ROOT, "gpurun_out", name + ".json"), "w"), indent=1)
+        print(name, {k: v for k, v in stats.items() if k != "ransac_iterations"})
+        assert not failures, failures
+        return stats
     finally:
         eng.close()
+
+
+def test_cfg3_parity_on_the_pairs_the_bench_times():
+    """bench.py times synth_batch(3, rank * 100000, 256): the first 64 pairs of rank 0's batch and 8 of rank 7's,
+    each against live cv2 (ORB and matches bit-exact, pose within 0.1 / 0.5 deg, inlier IoU >= 0.95)."""
+    _check_many(CFG3, 0, 64, "r02_cfg3_parity_rank0")
+    _check_many(CFG3, 700000, 8, "r02_cfg3_parity_rank7")
+
+
+def test_cfg4_parity_four_pairs():
+    _check_many(CFG4, 0, 4, "r02_cfg4_parity")
 
 
 def test_cfg3_full_bench_batch_properties():
@@ -214,35 +250,34 @@ def test_cfg2_simulator_sequence():
 
 
 def test_cfg5_stream_shards_and_subsample_vs_cv2():
-    """BASELINE config 5 at test size: a synthetic 1280x720 video stream with cfg3 parameters, consecutive frame pairs
-    through the sequence call (ORB once per frame).  (i) EVERY pair against the reference's cv2 call sequence on the
-    canonically ordered features (R within 0.1 deg, t within 0.5 deg), (ii) the stream cut into the per-rank frame
-    blocks of SURVEY 8(e) (boundary frame duplicated, no exchange) gives bit-identical results in pair order for 2, 3
-    and 4 ranks, (iii) the sequence call equals the pair-batch call on the same frames, and (iv) most pairs land within
-    2 deg of the generator's ground-truth rotation.
-    The stream is sampled every 16th frame: at stride 1 the baseline of a pair is ~1/400 of the scene depth, every
-    triangulated point fails recoverPose's depth < 50 gate (count 0), nearly every hypothesis has 500 / 500 inliers,
-    and cv2's own answer is decided by rounding noise (180 deg from the ground truth on 10 of 24 pairs) - there is
-    nothing determinate to compare with; tools/gpu_diag_cfg5.py prints the stage-wise comparison at any stride
-    (matches are bit-identical at every stride; pose within tolerance on 5 / 18 / 24 of 24 pairs at stride 1 / 8 / 16)."""
-    from rpe_b200.sharding import shard_frames, shard_range
+    """BASELINE config 5 at test size: a synthetic 1280x720 video stream with cfg3 parameters, CONSECUTIVE frames
+    (stride 1, exactly what bench.py's config-5 line item times) through the sequence call (ORB once per frame).
+    (i) EVERY pair against the reference's cv2 call sequence on the canonically ordered features (R within 0.1 deg,
+    t within 0.5 deg), (ii) the stream cut into the per-rank frame blocks of SURVEY 8(e) (boundary frame duplicated,
+    no exchange) gives bit-identical results in pair order for 2, 3 and 4 ranks, (iii) the sequence call equals the
+    pair-batch call on the same frames, (iv) chained calls (the next call starts at the previous call's last frame)
+    equal one long call, and (v) most pairs land within 5 deg of the generator's ground-truth rotation (the scene is
+    a plane: the essential matrix has a second, twisted solution that RANSAC - cv2's as well - sometimes takes)."""
     from bench_support.synth import stream_relative_pose, synth_K, synth_stream
+    from rpe_b200.sharding import shard_frames, shard_range
     c = CFG3
-    F = 25
+    F = 49
     K = synth_K(c["W"], c["H"])
-    STEP = 16
-    frames = synth_stream(5, 1000, F, c["W"], c["H"], step=STEP)
+    frames = synth_stream(5, 1000, F, c["W"], c["H"])
     eng = _engine(c, F - 1)
     try:
         out = eng.estimate_sequence(frames, K)
         assert out["R"].shape == (F - 1, 3, 3) and (out["status"] == 0).all(), out["status"]
         ref = ReferencePath(K, PathConfig(nfeatures=c["nfeatures"], nlevels=c["nlevels"], match_mode="ratio",
                                           ratio=0.75, max_matches=500, ransac_max_iters=2000), canonical=True)
+        bad = []
         for p in range(F - 1):
             Rr, tr = ref.estimate(frames[p], frames[p + 1])
             rot = og.rotation_angle_deg(out["R"][p], Rr)
             tdir = og.direction_angle_deg(out["t"][p], tr)
-            assert rot < 0.1 and tdir < 0.5, (p, rot, tdir)
+            if not (rot < 0.1 and tdir < 0.5):
+                bad.append((p, rot, tdir, out["info"][p].tolist()))
+        assert not bad, bad
         for world in (2, 3, 4):
             parts = {k: [] for k in ("R", "t", "euler", "status", "info")}
             for rank in range(world):
@@ -260,8 +295,20 @@ def test_cfg5_stream_shards_and_subsample_vs_cv2():
         ob = eng.estimate_batch_interleaved(pairs, K)
         for k in ("R", "t", "euler", "status", "info"):
             assert np.array_equal(ob[k], out[k]), k
-        gt_rot = [og.rotation_angle_deg(out["R"][p], stream_relative_pose(5, 0, 1000 + p * STEP, c["W"], c["H"], STEP)[0])
+        # chained asynchronous calls, two pending, as the config-5 bench line submits them
+        spans = [(0, 17), (17, 30), (30, F - 1)]
+        done = []
+        for a, b in spans:
+            eng.submit_sequence(np.ascontiguousarray(frames[a:b + 1]), K)
+            if len(eng._pending) == 2:
+                done.append(eng.wait())
+        while eng._pending:
+            done.append(eng.wait())
+        for (a, b), got in zip(spans, done):
+            for k in ("R", "t", "euler", "status", "info"):
+                assert np.array_equal(got[k], out[k][a:b]), (a, b, k)
+        gt_rot = [og.rotation_angle_deg(out["R"][p], stream_relative_pose(5, 0, 1000 + p, c["W"], c["H"])[0])
                   for p in range(F - 1)]
-        assert np.mean(np.array(gt_rot) < 2.0) >= 0.75, gt_rot
+        assert np.mean(np.array(gt_rot) < 5.0) >= 0.75, gt_rot
     finally:
         eng.close()

@@ -1,0 +1,181 @@
+"""GPU tests of the failure contract and of the ABI corners the round-1 suite left out (a9 on the
+device, overflow flag, device Euler 'zyx', host rows with pitch > W, the pending-batch guard of the blocking
+sequence calls, max_matches=None at 720p), all through the C ABI."""
+import numpy as np
+import pytest
+
+import cv2
+from conftest import default_K, load_gray
+
+from oracle import geometry as og
+from oracle import matcher as om
+from oracle import orb as oo
+from oracle.reference_path import PathConfig, ReferencePath
+
+pytestmark = pytest.mark.gpu
+
+
+def _dots(points, val=200, shape=(240, 320)):
+    a = np.full(shape, 100, np.uint8)
+    for x, y in points:
+        a[y, x] = val
+    return a
+
+
+@pytest.mark.parametrize("n_dots,expected", [(1, 2), (2, 4)])
+def test_insufficient_matches_status_and_message(n_dots, expected):
+    """reference: src/core/pose_estimator.py:514-515 — fewer than 5 matches raise
+    "Insufficient matches: n (minimum 5 required)" with the match count n; the batch call reports
+    RPE_STATUS_INSUFFICIENT_MATCHES and n in info[0].  Isolated bright pixels give a handful of keypoints each
+    (one per pyramid level while the contrast lasts); the expected n is what the reference's cv2 path counts."""
+    import rpe_b200
+    from rpe_b200 import _lib as L
+    K = np.array([[300.0, 0, 160], [0, 300, 120], [0, 0, 1]])
+    dots = [(60 + 40 * i, 80 + 17 * i) for i in range(n_dots)]
+    a = _dots(dots + [(250, 200), (280, 60)])
+    b = _dots([(x + 2, y + 1) for x, y in dots])
+    with pytest.raises(RuntimeError) as ref_err:
+        ReferencePath(K, PathConfig(), canonical=True).estimate(a, b)
+    assert str(ref_err.value) == f"Insufficient matches: {expected} (minimum 5 required)"
+    est = rpe_b200.PoseEstimator(K)
+    with pytest.raises(RuntimeError) as err:
+        est.estimate(a, b)
+    assert str(err.value) == str(ref_err.value)
+    with pytest.raises(RuntimeError, match=f"Insufficient matches: {expected} "):
+        est.estimate_with_debug(a, b)
+    # batched: no exception, status code + count; a good pair in the same batch is unaffected
+    s1, s2 = load_gray("sim_000000.png")[:240, :320].copy(), load_gray("sim_000015.png")[:240, :320].copy()
+    R, t, status = est.estimate_batch([a, s1], [b, s2])
+    assert status[0] == L.STATUS_INSUFFICIENT_MATCHES and est.last["info"][0, 0] == expected
+    assert not R[0].any() and not t[0].any()
+    assert status[1] == L.STATUS_OK and abs(np.linalg.det(R[1]) - 1) < 1e-9
+
+
+def test_candidate_overflow_sets_the_flag():
+    """RPE_STATUS_FLAG_OVERFLOW (include/rpe.h): a level whose FAST + NMS corners outnumber the candidate capacity
+    (w*h/16) is truncated and flagged — per image (rpe_orb_detect flags) and per pair (status bit 0x100).
+    Isolated bright pixels on a staggered 4 x 3 grid: every one is a FAST corner and an NMS maximum (density 1/12)."""
+    import rpe_b200
+    from rpe_b200 import _lib as L
+    img = np.full((480, 640), 60, np.uint8)
+    img[0::6, 0::4] = 200
+    img[3::6, 2::4] = 200
+    n_corners = int((oo.nms_3x3(oo.fast_score_map(img, 15))[31:-31, 31:-31] > 0).sum())
+    assert n_corners > 640 * 480 // 16                      # more than level 0's capacity
+    est = rpe_b200.PoseEstimator(default_K())
+    res = est._detect_and_compute(img)
+    assert res["flags"] & 1
+    R, t, status = est.estimate_batch([img, load_gray("sim_000000.png")], [img, load_gray("sim_000015.png")])
+    assert status[0] & L.STATUS_FLAG_OVERFLOW
+    assert status[1] == L.STATUS_OK
+    # the wrapper raises only for the status CODE; the flag alone is not an error
+    code = int(status[0]) & 0xFF
+    assert code in (L.STATUS_OK, L.STATUS_INSUFFICIENT_MATCHES, L.STATUS_E_FAILED)
+
+
+def test_device_euler_zyx():
+    """euler_convention='zyx' (the reference's phone / salah runs): the Euler angles computed in k_pose against
+    rotation_to_euler_zyx of the returned R (reference: src/utils/geometry.py:181-205), plus the host twin."""
+    import rpe_b200
+    a, b, c = load_gray("phone_000000.png"), load_gray("phone_000005.png"), load_gray("sim_000000.png")
+    K = default_K(a.shape[1], a.shape[0])
+    for conv, fn in (("zyx", og.rotation_to_euler_zyx), ("yup", og.rotation_to_euler_yup)):
+        eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=a.shape[1], max_height=a.shape[0], max_pairs=2,
+                                                     euler_convention=conv))
+        try:
+            out = eng.estimate_batch([a, b], [b, a], K)
+            assert (out["status"] == 0).all()
+            for i in range(2):
+                assert np.allclose(out["euler"][i], fn(out["R"][i]), atol=1e-9), conv
+                assert np.allclose(rpe_b200.rotation_to_euler(out["R"][i], conv), out["euler"][i], atol=1e-9)
+        finally:
+            eng.close()
+    assert not np.allclose(og.rotation_to_euler_zyx(out["R"][0]), og.rotation_to_euler_yup(out["R"][0]), atol=1e-3)
+    del c
+
+
+def test_host_rows_with_pitch_larger_than_width():
+    """The ABI takes a row pitch: frames that sit in a wider host buffer (pitch = W + 48, and an odd W whose device
+    pitch is padded) give bit-identical results to tight copies."""
+    import rpe_b200
+    a, b = load_gray("sim_000000.png"), load_gray("sim_000015.png")
+    K = default_K()
+    for W in (640, 601):
+        H = 480
+        tight = np.ascontiguousarray(np.stack([a[:, :W], b[:, :W]]))
+        wide = np.full((2, H, W + 48), 255, np.uint8)
+        wide[:, :, :W] = tight
+        view = wide[:, :, :W]
+        assert view.strides[1] == W + 48
+        eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=W, max_height=H, max_pairs=1))
+        try:
+            want = eng.estimate_batch_interleaved(tight, K)
+            kp_want = eng.keypoints(0, 1)
+            got = eng.estimate_batch_interleaved(view, K)
+            kp_got = eng.keypoints(0, 1)
+            assert want["status"][0] == 0
+            for k in ("R", "t", "euler", "status", "info"):
+                assert np.array_equal(got[k], want[k]), (W, k)
+            for k in kp_want:
+                assert np.array_equal(kp_got[k], kp_want[k]), (W, k)
+        finally:
+            eng.close()
+
+
+def test_blocking_calls_are_refused_while_a_batch_is_pending():
+    """include/rpe.h: while a submitted batch is pending every other call fails with RPE_ERR_INVALID — including the
+    blocking sequence calls, which would otherwise wait for the OLDER batch and return zeros."""
+    import rpe_b200
+    from rpe_b200._lib import RpeError
+    a, b, c = load_gray("sim_000000.png"), load_gray("sim_000015.png"), load_gray("sim_000030.png")
+    K = default_K()
+    eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=640, max_height=480, max_pairs=2))
+    try:
+        pair = np.ascontiguousarray(np.stack([a, b]))
+        want = eng.estimate_batch_interleaved(pair, K)
+        seq = np.ascontiguousarray(np.stack([a, b, c]))
+        want_seq = eng.estimate_sequence(seq, K)
+        eng.submit_interleaved(pair, K)
+        with pytest.raises(RpeError, match="pending"):
+            eng.estimate_sequence(seq, K)
+        with pytest.raises(RpeError, match="pending"):
+            eng.estimate_batch_interleaved(pair, K)
+        with pytest.raises(RpeError, match="pending"):
+            eng.orb_detect(a)
+        assert len(eng._pending) == 1                      # the host-side queue stayed in step with the C side
+        got = eng.wait()
+        for k in ("R", "t", "euler", "status", "info"):
+            assert np.array_equal(got[k], want[k]), k
+        with pytest.raises(RpeError):
+            eng.wait()                                      # nothing pending any more
+        assert len(eng._pending) == 0
+        again = eng.estimate_sequence(seq, K)               # and the handle is usable
+        for k in ("R", "t", "status"):
+            assert np.array_equal(again[k], want_seq[k]), k
+    finally:
+        eng.close()
+
+
+def test_no_cut_cross_check_at_720p():
+    """max_matches=None (no cut) on a 1280x720 pair with 5000 features, cross-check mode (the reference's matcher):
+    the whole match list equals cv2 BFMatcher(crossCheck=True) + the reference's stable sort."""
+    import rpe_b200
+    from bench_support.synth import synth_K, synth_pair
+    from rpe_b200 import _lib as L
+    a, b = synth_pair(3, 5, 1280, 720)[:2]
+    K = synth_K(1280, 720)
+    eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=1280, max_height=720, max_pairs=1, nfeatures=5000,
+                                                 match_mode="crosscheck", max_matches=None))
+    try:
+        out = eng.estimate_batch([a], [b], K)
+        assert out["status"][0] == 0
+        kp1, kp2 = eng.keypoints(0, 0), eng.keypoints(0, 1)
+        got = eng.get_stage(0, 0, L.STAGE_MATCHES, 0, np.int32).reshape(-1, 3)
+        bf = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True)
+        ms = sorted(bf.match(kp1["desc"], kp2["desc"]), key=lambda m: m.distance)
+        want = np.array([[m.queryIdx, m.trainIdx, int(m.distance)] for m in ms], np.int32)
+        assert len(want) > 2500 and np.array_equal(got, want)
+        assert np.array_equal(got, om.sort_and_cut(om.match_crosscheck(kp1["desc"], kp2["desc"]), None))
+        assert out["info"][0, 0] == len(want)
+    finally:
+        eng.close()
