@@ -187,6 +187,16 @@ int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const 
                      int32_t m, const double K[9], double* R, double* t, double* euler,
                      int32_t* count, uint8_t* mask);
 
+/* the geometry half of the path over a batch of pairs whose matched points are already known: replaces
+ * cv2.findEssentialMat(pts1, pts2, K, RANSAC, prob, thr, maxIters) + cv2.recoverPose(E, pts1, pts2, K) +
+ * rotation_to_euler (reference: src/core/pose_estimator.py:518-533, src/utils/geometry.py:14-27) for B pairs in one
+ * launch sequence.  pts1 / pts2: B x cap x 2 float32 (pair p at element offset p*cap*2), counts[B] = matches of
+ * pair p (<= cap <= match capacity).  Outputs as rpe_estimate_batch; a pair with fewer than 5 matches gets
+ * RPE_STATUS_INSUFFICIENT_MATCHES.  Blocking.  rpe_get_stage (E, masks) then refers to this call. */
+int rpe_estimate_from_matches(rpe_handle* h, const float* pts1, const float* pts2, const int32_t* counts,
+                              int32_t B, int32_t cap, const double K[9], double* R, double* t, double* euler,
+                              int32_t* status, int32_t* info);
+
 /* replaces PoseEvaluator.evaluate_sequence + compute_summary_statistics (reference:
  * src/core/pose_evaluator.py:32-134, :136-157) with rotation_error / translation_direction_error /
  * euler_to_rotation (reference: src/utils/geometry.py:128-174, :82-125, :208-236), on the device.

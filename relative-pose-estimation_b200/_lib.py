@@ -65,6 +65,7 @@ _SIGNATURES = [
     ("rpe_find_essential", C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P, _P]),
     ("rpe_ransac_trace", C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P]),
     ("rpe_recover_pose", C.c_int, [_P, _P, _P, _P, C.c_int32, _P, _P, _P, _P, _P, _P]),
+    ("rpe_estimate_from_matches", C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P]),
     ("rpe_evaluate_sequence", C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P, C.c_int32, _P, _P]),
     ("rpe_summarize_errors", C.c_int, [_P, C.c_int32, _P, _P]),
     ("rpe_get_stage", C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, C.POINTER(C.c_size_t)]),

@@ -1016,6 +1016,47 @@ int rpe_recover_pose(rpe_handle* h, const double E[9], const float* pts1, const 
   return RPE_OK;
 }
 
+int rpe_estimate_from_matches(rpe_handle* h, const float* pts1, const float* pts2, const int32_t* counts, int32_t B,
+                              int32_t cap, const double K[9], double* R, double* t, double* euler, int32_t* status,
+                              int32_t* info) {
+  if (h && h->n_pending) return fail(RPE_ERR_INVALID, "a submitted batch is pending: call rpe_wait_batch first");
+  if (!h || !pts1 || !pts2 || !counts || !K || B < 1 || cap < 1) return fail(RPE_ERR_INVALID, "bad argument");
+  if (B > h->NP) return fail(RPE_ERR_CAPACITY, "batch larger than max_pairs");
+  if (cap > h->mcap) return fail(RPE_ERR_CAPACITY, "more points per pair than the handle's match capacity");
+  for (int i = 0; i < B; ++i)
+    if (counts[i] < 0 || counts[i] > cap) return fail(RPE_ERR_INVALID, "counts[i] outside [0, cap]");
+  RPE_CK(cudaSetDevice(h->device));
+  reset_profile(h);
+  const bool prof = h->profiling;
+  const int set = 0;
+  cudaStream_t s = h->stream;
+  const MatchBuffers& mb = h->mb[set];
+  const size_t row = (size_t)cap * 2 * sizeof(float), dpitch = (size_t)h->mcap * 2 * sizeof(float);
+  RPE_CK(cudaMemcpy2DAsync(mb.pts1, dpitch, pts1, row, row, B, cudaMemcpyHostToDevice, s));
+  RPE_CK(cudaMemcpy2DAsync(mb.pts2, dpitch, pts2, row, row, B, cudaMemcpyHostToDevice, s));
+  RPE_CK(cudaMemcpyAsync(mb.m_n, counts, (size_t)B * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+  RPE_CK(cudaMemsetAsync(mb.pstat, 0, (size_t)B * sizeof(int32_t), s));
+  RPE_TRY(upload_K(h, set, K));
+  RPE_TRY(run_geometry(h, set, 0, B, s, prof));
+  if (prof) cudaEventRecord(h->ev[RPE_T_D2H], s);
+  RPE_TRY(download_async(h, set, 0, B, s));
+  RPE_CK(cudaEventRecord(h->ev_done_call[set], s));
+  h->last_pairs = B;
+  h->last_pstep = 2;
+  rpe_handle::Pending p;
+  p.B = B; p.set = set; p.R = R; p.t = t; p.euler = euler; p.status = status; p.info = info;
+  const bool keep_prof = h->profiling;
+  h->profiling = false;                       // only the two geometry stages carry events here
+  const int rc = finish_results(h, p);
+  h->profiling = keep_prof;
+  if (rc != RPE_OK) return rc;
+  if (prof) {
+    RPE_CK(cudaEventElapsedTime(&h->ms[RPE_T_RANSAC], h->ev[RPE_T_RANSAC], h->ev[RPE_T_POSE]));
+    RPE_CK(cudaEventElapsedTime(&h->ms[RPE_T_POSE], h->ev[RPE_T_POSE], h->ev[RPE_T_D2H]));
+  }
+  return RPE_OK;
+}
+
 int rpe_evaluate_sequence(rpe_handle* h, int32_t n, const double* est_R, const double* est_t, const double* est_euler,
                           const double* gt_euler, const double* gt_pos, int32_t euler_convention, double* errors,
                           double* summary) {

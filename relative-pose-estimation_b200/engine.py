@@ -310,6 +310,22 @@ class Engine:
                                            _ptr(e), C.byref(cnt), _ptr(mask)), "rpe_recover_pose")
         return {"R": R, "t": t, "euler": e, "count": cnt.value, "mask": mask[:m]}
 
+    def estimate_from_matches(self, pts1, pts2, counts, K):
+        """rpe_estimate_from_matches: findEssentialMat + recoverPose + Euler for B pairs of already matched points.
+        pts1 / pts2: (B, cap, 2) float32, counts: (B,) matches per pair.  Same dict as estimate_batch."""
+        pts1 = np.ascontiguousarray(pts1, dtype=np.float32)
+        pts2 = np.ascontiguousarray(pts2, dtype=np.float32)
+        counts = np.ascontiguousarray(counts, dtype=np.int32)
+        B, cap = pts1.shape[0], pts1.shape[1]
+        if pts1.shape != (B, cap, 2) or pts2.shape != pts1.shape or counts.shape != (B,):
+            raise ValueError("pts1 / pts2 must be (B, cap, 2) and counts (B,)")
+        K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
+        R, t, e, st, info = self._outputs(B)
+        L.check(self._lib.rpe_estimate_from_matches(self._h, _ptr(pts1), _ptr(pts2), _ptr(counts), B, cap, _ptr(K),
+                                                    _ptr(R), _ptr(t), _ptr(e), _ptr(st), _ptr(info)),
+                "rpe_estimate_from_matches")
+        return {"R": R, "t": t, "euler": e, "status": st, "info": info}
+
     def evaluate_sequence(self, est_R, est_t, est_euler, gt_euler, gt_pos, euler_convention: int = L.EULER_YUP):
         """rpe_evaluate_sequence: per-frame errors (n, 5) = roll, pitch, yaw, rotation, translation-direction (deg)
         and summary (5, 5) = per metric mean, std, median, max, min.  Angles are (yaw, pitch, roll) degrees."""

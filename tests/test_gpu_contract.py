@@ -179,3 +179,62 @@ def test_no_cut_cross_check_at_720p():
         assert out["info"][0, 0] == len(want)
     finally:
         eng.close()
+
+
+def _corrupt(pts2, frac, seed, W, H):
+    """replace a fraction of the correspondences by uniform random points (gross outliers)"""
+    rng = np.random.default_rng(seed)
+    out = pts2.copy()
+    idx = rng.permutation(len(out))[:int(round(frac * len(out)))]
+    out[idx] = np.stack([rng.uniform(0, W, len(idx)), rng.uniform(0, H, len(idx))], axis=1).astype(np.float32)
+    return out
+
+
+def test_estimate_from_matches_batch_and_hard_ransac():
+    """rpe_estimate_from_matches = findEssentialMat + recoverPose over a batch of matched point sets (reference:
+    src/core/pose_estimator.py:518-533).  (i) equals the single-pair stage calls bit for bit, (ii) a short point set
+    reports INSUFFICIENT_MATCHES without disturbing its neighbours, (iii) on correspondences with 30 / 50 / 70 % gross
+    outliers - where cv2 and the engine run tens to thousands of RANSAC iterations instead of the dozen of clean data
+    - every pair agrees with cv2 on the same points: same iteration count path, R within 0.1 deg, t within 0.5 deg,
+    inlier IoU >= 0.95."""
+    import rpe_b200
+    from rpe_b200 import _lib as L
+    from test_gpu_parity import _matched_points
+    K = default_K()
+    pts1, pts2 = _matched_points()
+    M = len(pts1)
+    eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=640, max_height=480, max_pairs=8, ransac_max_iters=2000))
+    try:
+        cases = [(pts1, pts2), (pts1[:300], pts2[:300]), (pts1[:4], pts2[:4])]
+        for k, frac in enumerate((0.3, 0.5, 0.5, 0.7, 0.7)):
+            cases.append((pts1, _corrupt(pts2, frac, 100 + k, 640, 480)))
+        B = len(cases)
+        P1 = np.zeros((B, M, 2), np.float32); P2 = np.zeros((B, M, 2), np.float32)
+        counts = np.array([len(c[0]) for c in cases], np.int32)
+        for i, (a, b) in enumerate(cases):
+            P1[i, :len(a)] = a; P2[i, :len(b)] = b
+        out = eng.estimate_from_matches(P1, P2, counts, K)
+        assert out["status"][2] == L.STATUS_INSUFFICIENT_MATCHES and not out["R"][2].any()
+        ok = [i for i in range(B) if i != 2]
+        assert (out["status"][ok] == 0).all(), out["status"]
+        masks = {i: eng.get_stage(i, 0, L.STAGE_RANSAC_MASK, 0, np.uint8).astype(bool).copy() for i in ok}
+        iters = out["info"][:, 3]
+        assert iters[0] <= 64 and iters[3:].min() > 16 and iters[6:].min() == 2000, iters      # clean vs hard: cap reached at 70 %
+        for i in ok:
+            a, b = cases[i]
+            # (i) the single-pair stage entry points run the same kernels
+            one = eng.find_essential(a, b, K)
+            assert one["iters"] == iters[i] and one["best"] == out["info"][i, 2]
+            rp = eng.recover_pose(one["E"], a, b, K)
+            assert np.array_equal(rp["R"], out["R"][i]) and np.array_equal(rp["t"], out["t"][i])
+            assert np.array_equal(one["mask"].astype(bool), masks[i])
+            # (iii) cv2 on the same points
+            E_cv, m_cv = cv2.findEssentialMat(a, b, K, method=cv2.RANSAC, prob=0.999, threshold=1.0, maxIters=2000)
+            n_cv, R_cv, t_cv, _ = cv2.recoverPose(E_cv, a, b, K)
+            m_cv = m_cv.ravel().astype(bool)
+            iou = (masks[i] & m_cv).sum() / max(1, (masks[i] | m_cv).sum())
+            rot, tdir = og.rotation_angle_deg(out["R"][i], R_cv), og.direction_angle_deg(out["t"][i], t_cv)
+            assert rot < 0.1 and tdir < 0.5 and iou >= 0.95, (i, rot, tdir, iou, int(iters[i]))
+            assert abs(int(out["info"][i, 1]) - n_cv) <= 2
+    finally:
+        eng.close()
