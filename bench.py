@@ -53,7 +53,7 @@ def metric_name(cfg):
 
 
 def workload_name(cfg):
-    return (f"cfg{cfg['synth_cfg']}: synthetic {cfg['W']}x{cfg['H']} pair batch, ORB {cfg['nfeatures']} features (sf 1.1, "
+    return (f"cfg{cfg['synth_cfg']}: synthetic {cfg['W']}x{cfg['H']} pair batch (two-plane scene, generator v2), ORB {cfg['nfeatures']} features (sf 1.1, "
             f"{cfg['nlevels']} levels, FAST 15, HARRIS), BF-Hamming knn2 + ratio 0.75, max_matches {cfg['max_matches']}, "
             f"RANSAC 5-pt {cfg['ransac_max_iters']} iters")
 
@@ -488,7 +488,7 @@ def run_stream(ctx: Ctx, cfg):
     R_again = np.concatenate([o["R"] for o in outs[:lap]])
     deterministic = bool(np.array_equal(R_first, R_again))
     total = per_rank * ctx.world
-    item = {"workload": "cfg5: synthetic 1280x720 video stream, consecutive frame pairs (stride 1), cfg3 parameters, "
+    item = {"workload": "cfg5: synthetic 1280x720 video stream (two-plane scene, generator v2), consecutive frame pairs (stride 1), cfg3 parameters, "
                         "frame-level feature cache (ORB once per frame), chained sequence calls",
             "pairs_total": total, "pairs_per_rank": per_rank, "ranks": ctx.world,
             "value": total / (ms_dev * 1e-3), "e2e": total / (ms_e2e * 1e-3), "unit": "pairs/s",

@@ -1,21 +1,31 @@
-"""Deterministic synthetic image pairs for BASELINE configs 3-5.
+"""Deterministic synthetic image pairs for BASELINE configs 3-5, generator version 2.
 
 BENCH / TEST INPUT GENERATOR (host-side; not on the hot path; uses cv2 on the host for the texture upsampling
-and the homography warp).  The reference has no synthetic data; this is the generator the
-survey defines so that the CPU baseline and the GPU engine see byte-identical inputs.
+and the homography warps).  The reference has no synthetic data; this is the generator the survey defines so that
+the CPU baseline and the GPU engine see byte-identical inputs - with TWO changes to the geometry it prescribes,
+both needed for the pose of a pair to be DETERMINATE (for cv2 itself, not only for the engine):
+
+  * the scene is two planes meeting in a ridge instead of one plane.  Left of the image centre the camera of view 1
+    sees the plane z = 5; right of it a plane through the same vertical line (x = 0, z = 5) tilted by 35 deg, receding
+    to z ~ 8 at the right image border.  A single plane is the degenerate case of the five-point problem: the
+    essential matrix has a second, "twisted" solution with the same support, and which of the two RANSAC holds is
+    decided by one borderline inlier (measured in round 2: 15 of the first 64 config-3 pairs and 29 of 1000 stream
+    pairs changed solution between cv2 and the engine, while keypoints, descriptors and matches were bit-identical);
+  * the baseline is 0.3 - 0.6 instead of U(-0.1, 0.1) per axis: cv2.recoverPose only counts points nearer than 50
+    baselines (distanceThresh), and at depth 5 - 8 a baseline of ~0.1 puts every point at the gate: the counts of
+    the four (R, t) candidates are then 0 - 50 of 500 and their order - cv2's answer - is rounding noise.
 
 Per pair: seed = 1000*cfg + pair_idx.  View 1 = multi-octave noise texture scaled to [40, 200]
-plus floor(W*H/1500) filled axis-aligned rectangles; view 2 = view 1 warped by the homography
-induced by a small random motion (rvec ~ U(-0.03,0.03)^3, t ~ U(-0.1,0.1)^3) of a camera
-looking at the plane z = 5; K = [[0.9W,0,W/2],[0,0.9W,H/2],[0,0,1]].
+plus floor(W*H/1500) filled axis-aligned rectangles; view 2 = view 1 re-projected through the two plane
+homographies of a small random motion (rvec ~ U(-0.03,0.03)^3, t = random direction x U(0.3, 0.6));
+K = [[0.9W,0,W/2],[0,0.9W,H/2],[0,0,1]].
 
 Stream (config 5): ONE base texture per stream (seed = 1000*cfg + stream_idx) seen by a camera whose pose
 is a smooth bounded function of the frame index (one sinusoid per axis, random phase); frame k =
-the base texture warped by the plane homography of pose k, so any frame can be generated independently
-(shards need no state).  The motion between CONSECUTIVE frames is sized like a config-3 pair's
-(|dt| ~ 0.03-0.2 per axis at scene depth 5, |dr| ~ 0.01-0.04 rad per axis: periods of 8-20 frames), so that
-stride-1 pairs have a determinate pose.  (Round 1 used periods of 40-120 frames: a per-frame baseline of ~1/400 of
-the depth, for which recoverPose's answer - cv2's too - is rounding noise)
+the base view re-projected by pose k, so any frame can be generated independently (shards need no state).
+The motion between CONSECUTIVE frames is sized like a pair's (|dt| ~ 0.15-0.7 per axis, |dr| ~ 0.01-0.04 rad per
+axis: periods of 8-20 frames), so that stride-1 pairs have a determinate pose.  (Round 1 used periods of 40-120
+frames and amplitudes of 0.08-0.2: a per-frame baseline of ~1/400 of the depth.)
 """
 from __future__ import annotations
 
@@ -44,9 +54,42 @@ def synth_texture(rng: np.random.Generator, W: int, H: int) -> np.ndarray:
 
 def synth_motion(rng: np.random.Generator):
     rvec = rng.uniform(-0.03, 0.03, 3)
-    t = rng.uniform(-0.1, 0.1, 3)
+    d = rng.standard_normal(3)
+    t = d / np.linalg.norm(d) * rng.uniform(0.3, 0.6)
     R, _ = cv2.Rodrigues(rvec)
     return R, t
+
+
+# the scene in the coordinates of the reference view: plane A (left of the image centre) z = 5, plane B (right of it)
+# through the line x = 0, z = 5, tilted by SCENE_TILT about the vertical axis
+SCENE_DEPTH = 5.0
+SCENE_TILT = np.deg2rad(-35.0)
+_PLANES = ((np.array([0.0, 0.0, 1.0]), SCENE_DEPTH),
+           (np.array([np.sin(SCENE_TILT), 0.0, np.cos(SCENE_TILT)]), SCENE_DEPTH * np.cos(SCENE_TILT)))
+_MASK_CACHE: dict = {}
+
+
+def render_view(ref_view: np.ndarray, K: np.ndarray, R: np.ndarray, t: np.ndarray, out: np.ndarray | None = None):
+    """The reference view (camera at the origin looking at the two-plane scene) seen from pose (R, t):
+    x_cam = R x_ref + t.  Each plane maps by its homography K (R + t n' / d) K^-1; a pixel of the new view belongs
+    to plane A iff its pre-image under A's homography lies left of the ridge (the planes meet there, so the two
+    homographies agree on the seam)."""
+    H, W = ref_view.shape
+    Ki = np.linalg.inv(K)
+    Hs = [K @ (R + np.outer(t, n) / d) @ Ki for n, d in _PLANES]
+    a = cv2.warpPerspective(ref_view, Hs[0], (W, H), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
+    b = cv2.warpPerspective(ref_view, Hs[1], (W, H), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
+    if (W, H) not in _MASK_CACHE:
+        m = np.zeros((H, W), np.uint8)
+        m[:, :W // 2] = 255
+        _MASK_CACHE.clear()
+        _MASK_CACHE[(W, H)] = m
+    left = cv2.warpPerspective(_MASK_CACHE[(W, H)], Hs[0], (W, H), flags=cv2.INTER_NEAREST, borderMode=cv2.BORDER_REPLICATE)
+    if out is None:
+        out = np.empty((H, W), np.uint8)
+    np.copyto(out, b)
+    np.copyto(out, a, where=left > 0)
+    return out
 
 
 def synth_pair(cfg: int, pair_idx: int, W: int, H: int):
@@ -55,9 +98,7 @@ def synth_pair(cfg: int, pair_idx: int, W: int, H: int):
     img1 = synth_texture(rng, W, H)
     R, t = synth_motion(rng)
     K = synth_K(W, H)
-    n = np.array([0.0, 0.0, 1.0])
-    Hm = K @ (R + np.outer(t, n) / 5.0) @ np.linalg.inv(K)
-    img2 = cv2.warpPerspective(img1, Hm, (W, H), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
+    img2 = render_view(img1, K, R, t)
     return img1, img2, K, R, t / np.linalg.norm(t)
 
 
@@ -113,12 +154,9 @@ def synth_stream(cfg: int, first_frame: int, n_frames: int, W: int, H: int, stre
     (``step`` > 1 = the stream sampled at a lower frame rate: proportionally larger motion per pair)."""
     base, _ = _stream_state(cfg, stream_idx, W, H)
     K = synth_K(W, H)
-    Ki = np.linalg.inv(K)
-    n = np.array([0.0, 0.0, 1.0])
     if out is None:
         out = np.empty((n_frames, H, W), np.uint8)
     for i in range(n_frames):
         R, t = stream_pose(cfg, stream_idx, first_frame + i * step, W, H)
-        Hm = K @ (R + np.outer(t, n) / 5.0) @ Ki
-        cv2.warpPerspective(base, Hm, (W, H), dst=out[i], flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
+        render_view(base, K, R, t, out=out[i])
     return out

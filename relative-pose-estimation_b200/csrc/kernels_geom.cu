@@ -3,11 +3,10 @@
 // cv2.recoverPose(E, pts1, pts2, K) as the reference calls them
 // (src/core/pose_estimator.py:522-527, :533) plus rotation_to_euler (src/utils/geometry.py:14-27).
 //
-// k_ransac: one CTA per pair.  OpenCV's loop is sequential (strict ">" best update, adaptive
-// iteration count); here hypotheses are generated in chunks of kChunk from the SAME RNG stream,
-// solved one per thread, scored one model per warp (Sampson error over all M points), and the
-// sequential update rule is then replayed over the chunk's per-model inlier counts, so the CTA
-// stops at exactly the iteration where OpenCV would have stopped and holds the model it held.
+// RANSAC: hypotheses come from the SAME RNG stream as OpenCV's, are solved one per thread and scored one model per
+// warp (Sampson error over all M points) by many CTAs per pair, and OpenCV's sequential update rule is then
+// replayed over their inlier counts, so every pair stops at exactly the iteration where OpenCV would have stopped
+// and holds the model it held (see k_ransac_* below).
 #include "rpe_device.cuh"
 #include "geom_math.cuh"
 
@@ -36,167 +35,247 @@ void launch_normalize(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, i
   ++*launches;
 }
 
-// Hypotheses per round.  The five-point solver keeps 2.5 KB of per-thread scratch in local memory (the 10 x 20
-// elimination matrix), interleaved by lane: 16 solver threads in the lower half-warp touch 40 KB, which stays in L1
-// next to the dense kernels sharing the SM; 24 and more spill out of it (B200, 128 easy pairs per step: 0.38 / 0.44 /
-// 1.08 / 1.11 / 1.24 / 3.2 ms for rounds of 8 / 16 / 24 / 32 / 64 / 128), and small rounds solve fewer hypotheses
-// past the adaptive stop.  A round costs one solver latency (~0.3 ms) whatever its size, though, so a pair that still
-// needs many iterations (low inlier ratio: the reference's simulator frames run to the 1000-iteration cap) takes
-// rounds of kChunkMax instead: 58 such pairs 22 ms -> 10 ms.  The result does not depend on the round sizes (same
-// RNG stream, exactly the drawn subsets consumed, sequential update rule replayed per round).
-#ifndef RPE_RANSAC_CHUNK
-#define RPE_RANSAC_CHUNK 16
-#endif
-constexpr int kChunkSmall = RPE_RANSAC_CHUNK;   // first round, and while few iterations remain
-constexpr int kChunkMax = 64;                   // later rounds while more than kChunkSwitch iterations remain
-#ifndef RPE_RANSAC_SWITCH
-#define RPE_RANSAC_SWITCH 48
-#endif
-constexpr int kChunkSwitch = RPE_RANSAC_SWITCH;
-constexpr int kChunk = kChunkMax;               // array sizes
-static_assert(kChunkSmall <= kChunkMax, "round sizes");
-#ifndef RPE_RANSAC_THREADS
-#define RPE_RANSAC_THREADS 128
-#endif
-constexpr int kRansacThreads = RPE_RANSAC_THREADS;
-static_assert(kRansacThreads >= kChunk && kRansacThreads % 32 == 0, "one solver thread per hypothesis of a round");
+// RANSAC over a batch, hypotheses in parallel ACROSS CTAs.  OpenCV's loop is sequential (strict ">" best update,
+// adaptive iteration count); here it advances in super-rounds:
+//   k_ransac_begin   thread per pair: state (cv2's RNG seed, niters = maxIters), subsets of the first, small round
+//   k_ransac_solve   CTA per (chunk of kChunk hypotheses, pair): minimal solver one hypothesis per thread, Sampson
+//                    scoring one model per warp, then the chunk's PREFIX MAXIMA (the models whose inlier count beats
+//                    everything before them in the chunk and the best held at the start of the super-round): only
+//                    those can ever win the sequential update, so only they (<= kCandCap, with their E) go to HBM
+//   k_ransac_replay  thread per pair: cv2's sequential rule replayed over the chunks' prefix maxima in hypothesis
+//                    order (stop where cv2 stops: it0 + h >= niters), then the next super-round's subsets from the
+//                    pair's RNG stream
+//   k_ransac_finish  CTA per pair: inlier mask of the held model, E, rinfo
+// [solve, replay] is enqueued a fixed number of times (enough for maxIters); CTAs of finished pairs, and chunks past
+// the iterations still needed, return at once.  Same RNG stream, exactly the drawn subsets consumed in order, same
+// update rule => the same stop iteration and the same held model as the one-CTA-per-pair loop of round 1, whatever
+// the chunking.  What changes is latency: a pair that needs 1000 iterations (the reference's simulator frames) takes
+// 1 + ceil(984 / (chunks * 64)) solver passes instead of 16, with its chunks on different SMs (the five-point solver
+// keeps 2.5 KB of per-thread scratch in local memory: 64 solver threads per SM stay in L1, more spill out of it:
+// B200 round 1, rounds of 16 / 64 / 128 hypotheses on one SM: 0.44 / 1.24 / 3.2 ms per pass).
+constexpr int kChunk = 64;                      // hypotheses per solve CTA
+constexpr int kFirstRound = 16;                 // the first round is small: it brings niters down for an easy pair
+constexpr int kMaxChunks = 8;                   // chunks per pair and super-round
+constexpr int kCandCap = 32;                    // prefix maxima kept per chunk
+constexpr int kRansacThreads = 128;
+static_assert(kRansacThreads >= kChunk && kRansacThreads % 32 == 0, "one solver thread per hypothesis of a chunk");
 
 struct RansacShared {
   double models[kChunk][10][9];
   int nmodels[kChunk];
   int counts[kChunk][10];
   int subset[kChunk][5];
-  double best_model[9];
-  unsigned long long rng_state;
-  int best, niters, it0, done, have_best, nh;
 };
 
+__global__ void __launch_bounds__(128)
+k_ransac_begin(const int32_t* __restrict__ m_n, int n_pairs, RansacParams rp, RansacState* __restrict__ state,
+               int32_t* __restrict__ subsets, int sr_cap) {
+  const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pair >= n_pairs) return;
+  const int M = m_n[pair];
+  RansacState st;
+  st.rng = 0xFFFFFFFFFFFFFFFFull;
+  st.best = 0; st.niters = rp.max_iters; st.it0 = 0; st.have_best = 0; st.solved = 0; st.overflow = 0;
+  st.done = M < 5;                              // run() returns false; the host maps this to INSUFFICIENT_MATCHES / E_FAILED
+  st.nh = st.done ? 0 : min(kFirstRound, st.niters);
+  for (int k = 0; k < 9; ++k) st.best_model[k] = 0.0;
+  int32_t* sub = subsets + (size_t)pair * sr_cap * 5;
+  CvRng rng{st.rng};
+  for (int h = 0; h < st.nh; ++h) {
+    if (M == 5) { for (int k = 0; k < 5; ++k) sub[h * 5 + k] = k; }
+    else draw_subset5(rng, M, sub + h * 5);
+  }
+  st.rng = rng.state;
+  state[pair] = st;
+}
+
 __global__ void __launch_bounds__(kRansacThreads)
-k_ransac(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npts,
-         const double* __restrict__ K, RansacParams rp, double* __restrict__ E_out,
-         uint8_t* __restrict__ rmask, int32_t* __restrict__ rinfo, int32_t* tr_subset, int32_t* tr_nmodels,
-         int32_t* tr_counts, double* tr_models, int tr_cap) {
+k_ransac_solve(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npts, const double* __restrict__ K,
+               RansacParams rp, const RansacState* __restrict__ state, const int32_t* __restrict__ subsets, int sr_cap,
+               RansacCand* __restrict__ cands, int32_t* __restrict__ n_cand, int32_t* tr_subset, int32_t* tr_nmodels,
+               int32_t* tr_counts, double* tr_models, int tr_cap) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   RansacShared& S = *reinterpret_cast<RansacShared*>(s_raw);
-  const int pair = blockIdx.x, tid = threadIdx.x;
+  const int pair = blockIdx.y, chunk = blockIdx.x, tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
+  const RansacState& st = state[pair];
+  if (st.done) return;
+  const int h0 = chunk * kChunk;
+  if (h0 >= st.nh) return;
+  const int nh = min(kChunk, st.nh - h0);
+  const int it0 = st.it0, best0 = st.best;
   const int M = m_n[pair];
   const double4* P = reinterpret_cast<const double4*>(npts) + (size_t)pair * mcap;
-  const bool trace = (tr_subset != nullptr) && pair == 0;
-  if (M < 5) {   // run() returns false; the host maps this to INSUFFICIENT_MATCHES / E_FAILED
+  const double thr = rp.threshold / ((K[0] + K[4]) * 0.5);
+  const float t2 = (float)(thr * thr);
+  const int32_t* sub = subsets + ((size_t)pair * sr_cap + h0) * 5;
+  for (int i = tid; i < nh * 5; i += kRansacThreads) S.subset[i / 5][i % 5] = sub[i];
+  __syncthreads();
+  // (b) minimal solver, one hypothesis per thread
+  if (tid < nh) {
+    double x1[10], x2[10];
+    for (int k = 0; k < 5; ++k) {
+      const double4 p = P[S.subset[tid][k]];
+      x1[2 * k] = p.x; x1[2 * k + 1] = p.y; x2[2 * k] = p.z; x2[2 * k + 1] = p.w;
+    }
+    S.nmodels[tid] = five_point_solve(x1, x2, &S.models[tid][0][0]);
+  }
+  __syncthreads();
+  // (c) Sampson scoring, one model per warp
+  for (int mi = warp; mi < nh * 10; mi += kRansacThreads / 32) {
+    const int h = mi / 10, r = mi % 10;
+    if (r >= S.nmodels[h]) continue;
+    const double* E = S.models[h][r];
+    int cnt = 0;
+    for (int i = lane; i < M; i += 32) {
+      const double4 p = P[i];
+      cnt += (sampson_err_f32(E, p.x, p.y, p.z, p.w) <= t2) ? 1 : 0;
+    }
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) S.counts[h][r] = cnt;
+  }
+  __syncthreads();
+  // (d) prefix maxima of the chunk, in (hypothesis, model) order, above what the pair held when the super-round began
+  if (tid == 0) {
+    RansacCand* out = cands + ((size_t)pair * kMaxChunks + chunk) * kCandCap;
+    int run = max(best0, 4), n = 0;
+    for (int h = 0; h < nh; ++h)
+      for (int r = 0; r < S.nmodels[h]; ++r) {
+        const int c = S.counts[h][r];
+        if (c > run) {
+          run = c;
+          if (n < kCandCap) {
+            out[n].h = h0 + h; out[n].r = r; out[n].count = c; out[n].pad = 0;
+            for (int k = 0; k < 9; ++k) out[n].E[k] = S.models[h][r][k];
+          }
+          ++n;
+        }
+      }
+    n_cand[pair * kMaxChunks + chunk] = n;
+  }
+  if (tr_subset != nullptr && pair == 0) {
+    for (int i = tid; i < nh; i += kRansacThreads) {
+      const int g = it0 + h0 + i;
+      if (g < tr_cap) {
+        tr_nmodels[g] = S.nmodels[i];
+        for (int k = 0; k < 5; ++k) tr_subset[g * 5 + k] = S.subset[i][k];
+        for (int r = 0; r < 10; ++r) {
+          tr_counts[g * 10 + r] = r < S.nmodels[i] ? S.counts[i][r] : -1;
+          for (int k = 0; k < 9; ++k) tr_models[(size_t)g * 90 + r * 9 + k] = r < S.nmodels[i] ? S.models[i][r][k] : 0.0;
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128)
+k_ransac_replay(const int32_t* __restrict__ m_n, int n_pairs, RansacParams rp, RansacState* __restrict__ state,
+                int32_t* __restrict__ subsets, int sr_cap, int chunks, const RansacCand* __restrict__ cands,
+                const int32_t* __restrict__ n_cand) {
+  const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pair >= n_pairs) return;
+  RansacState st = state[pair];
+  if (st.done) return;
+  const int M = m_n[pair];
+  // OpenCV's sequential update rule over the super-round: `for h: if (it0 + h >= niters) break; for every model of h:
+  // if (count > max(best, 4)) take it and shrink niters`.  A model that is not a prefix maximum of its chunk cannot
+  // exceed the best held when it is visited, so visiting the prefix maxima in order is the same loop.
+  bool stop = false;
+  int last_h = -1;
+  const int used_chunks = (st.nh + kChunk - 1) / kChunk;
+  for (int c = 0; c < used_chunks && !stop; ++c) {
+    const RansacCand* in = cands + ((size_t)pair * kMaxChunks + c) * kCandCap;
+    const int n = n_cand[pair * kMaxChunks + c];
+    if (n > kCandCap) st.overflow = 1;
+    for (int i = 0; i < min(n, kCandCap); ++i) {
+      const int h = in[i].h;
+      if (h != last_h && st.it0 + h >= st.niters) { stop = true; break; }   // (models of one hypothesis are all visited)
+      last_h = h;
+      const int cnt = in[i].count;
+      if (cnt > max(st.best, 4)) {
+        st.best = cnt;
+        st.have_best = 1;
+        for (int k = 0; k < 9; ++k) st.best_model[k] = in[i].E[k];
+        st.niters = ransac_update_iters(rp.prob, (double)(M - cnt) / M, 5, st.niters);
+      }
+    }
+  }
+  st.it0 += st.nh;
+  st.solved += st.nh;
+  if (st.it0 >= st.niters || M == 5) {
+    st.done = 1;
+    st.nh = 0;
+  } else {
+    // subsets of the next super-round, sequentially from the pair's RNG stream
+    st.nh = min(chunks * kChunk, st.niters - st.it0);
+    int32_t* sub = subsets + (size_t)pair * sr_cap * 5;
+    CvRng rng{st.rng};
+    for (int h = 0; h < st.nh; ++h) draw_subset5(rng, M, sub + h * 5);
+    st.rng = rng.state;
+  }
+  state[pair] = st;
+}
+
+__global__ void __launch_bounds__(kRansacThreads)
+k_ransac_finish(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npts, const double* __restrict__ K,
+                RansacParams rp, const RansacState* __restrict__ state, double* __restrict__ E_out,
+                uint8_t* __restrict__ rmask, int32_t* __restrict__ rinfo) {
+  __shared__ double sE[9];
+  const int pair = blockIdx.x, tid = threadIdx.x;
+  const RansacState& st = state[pair];
+  const int M = m_n[pair];
+  if (M < 5) {
     if (tid < 9) E_out[pair * 9 + tid] = 0.0;
     if (tid < 4) rinfo[pair * 4 + tid] = 0;
     return;
   }
+  if (tid < 9) sE[tid] = st.best_model[tid];
+  __syncthreads();
+  const double4* P = reinterpret_cast<const double4*>(npts) + (size_t)pair * mcap;
   const double thr = rp.threshold / ((K[0] + K[4]) * 0.5);
   const float t2 = (float)(thr * thr);
-  if (tid == 0) {
-    S.rng_state = 0xFFFFFFFFFFFFFFFFull;
-    S.best = 0; S.niters = rp.max_iters; S.it0 = 0; S.done = 0; S.have_best = 0;
-  }
-  __syncthreads();
-  int solved = 0;
-  while (true) {
-    // (a) subsets for this chunk, sequentially from the shared RNG stream
-    if (tid == 0) {
-      const int remaining = S.niters - S.it0;
-      // the first round is always small: it is what brings niters down from max_iters for an easy pair
-      const int nh_round = min((S.it0 > 0 && remaining > kChunkSwitch) ? kChunkMax : kChunkSmall, remaining);
-      S.nh = nh_round;                              // hypotheses that can still matter
-      CvRng rng{S.rng_state};
-      for (int h = 0; h < nh_round; ++h) {
-        if (M == 5) { for (int k = 0; k < 5; ++k) S.subset[h][k] = k; }
-        else draw_subset5(rng, M, S.subset[h]);
-      }
-      S.rng_state = rng.state;
-    }
-    __syncthreads();
-    const int it0 = S.it0;
-    const int nh = S.nh;
-    // (b) minimal solver, one hypothesis per thread
-    const int hyp = tid;
-    if (hyp < nh) {
-      double x1[10], x2[10];
-      for (int k = 0; k < 5; ++k) {
-        const double4 p = P[S.subset[hyp][k]];
-        x1[2 * k] = p.x; x1[2 * k + 1] = p.y; x2[2 * k] = p.z; x2[2 * k + 1] = p.w;
-      }
-      S.nmodels[hyp] = five_point_solve(x1, x2, &S.models[hyp][0][0]);
-    }
-    __syncthreads();
-    solved += nh;
-    // (c) Sampson scoring, one model per warp
-    for (int mi = warp; mi < nh * 10; mi += kRansacThreads / 32) {
-      const int h = mi / 10, r = mi % 10;
-      if (r >= S.nmodels[h]) continue;
-      const double* E = S.models[h][r];
-      int cnt = 0;
-      for (int i = lane; i < M; i += 32) {
-        const double4 p = P[i];
-        cnt += (sampson_err_f32(E, p.x, p.y, p.z, p.w) <= t2) ? 1 : 0;
-      }
-      for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-      if (lane == 0) S.counts[h][r] = cnt;
-    }
-    __syncthreads();
-    // (d) replay OpenCV's sequential update rule over the chunk
-    if (tid == 0) {
-      int h = 0;
-      for (; h < nh; ++h) {
-        if (it0 + h >= S.niters) break;
-        for (int r = 0; r < S.nmodels[h]; ++r) {
-          const int c = S.counts[h][r];
-          if (c > max(S.best, 4)) {
-            S.best = c;
-            S.have_best = 1;
-            for (int k = 0; k < 9; ++k) S.best_model[k] = S.models[h][r][k];
-            S.niters = ransac_update_iters(rp.prob, (double)(M - c) / M, 5, S.niters);
-          }
-        }
-      }
-      S.it0 = it0 + nh;
-      if (S.it0 >= S.niters || M == 5) S.done = 1;
-    }
-    if (trace) {
-      for (int i = tid; i < nh; i += kRansacThreads) {
-        const int g = it0 + i;
-        if (g < tr_cap) {
-          tr_nmodels[g] = S.nmodels[i];
-          for (int k = 0; k < 5; ++k) tr_subset[g * 5 + k] = S.subset[i][k];
-          for (int r = 0; r < 10; ++r) {
-            tr_counts[g * 10 + r] = r < S.nmodels[i] ? S.counts[i][r] : -1;
-            for (int k = 0; k < 9; ++k) tr_models[(size_t)g * 90 + r * 9 + k] = r < S.nmodels[i] ? S.models[i][r][k] : 0.0;
-          }
-        }
-      }
-    }
-    __syncthreads();
-    if (S.done) break;
-  }
-  // inlier mask of the held model
-  const int ok = S.have_best && M > 5;   // M == 5: cv2 returns stacked roots -> E_FAILED
   for (int i = tid; i < M; i += kRansacThreads) {
     uint8_t v = 0;
-    if (S.have_best) {
+    if (st.have_best) {
       const double4 p = P[i];
-      v = sampson_err_f32(S.best_model, p.x, p.y, p.z, p.w) <= t2;
+      v = sampson_err_f32(sE, p.x, p.y, p.z, p.w) <= t2;
     }
     rmask[(size_t)pair * mcap + i] = v;
   }
-  if (tid < 9) E_out[pair * 9 + tid] = S.have_best ? S.best_model[tid] : 0.0;
+  if (tid < 9) E_out[pair * 9 + tid] = st.have_best ? sE[tid] : 0.0;
   if (tid == 0) {
-    rinfo[pair * 4 + 0] = ok;
-    rinfo[pair * 4 + 1] = S.best;
-    rinfo[pair * 4 + 2] = min(S.it0, S.niters);
-    rinfo[pair * 4 + 3] = solved;
+    rinfo[pair * 4 + 0] = st.have_best && M > 5;   // M == 5: cv2 returns stacked roots -> E_FAILED
+    rinfo[pair * 4 + 1] = st.best;
+    rinfo[pair * 4 + 2] = min(st.it0, st.niters);
+    rinfo[pair * 4 + 3] = st.solved;
   }
+}
+
+int ransac_chunks(int n_pairs, int max_iters) {
+  // enough chunks to put ~2 CTAs on every SM when the batch is small, and to keep the number of solver passes that
+  // maxIters can need at about a dozen; never more than kMaxChunks
+  const int fill = (2 * 148 + n_pairs - 1) / max(n_pairs, 1);
+  const int passes = (max_iters + 12 * kChunk - 1) / (12 * kChunk);
+  return max(1, min(kMaxChunks, max(fill, passes)));
 }
 
 void launch_ransac(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_pairs, const double* dK,
                    RansacParams rp, cudaStream_t s, int* launches) {
-  k_ransac<<<n_pairs, kRansacThreads, sizeof(RansacShared), s>>>(mb.m_n, mcap, gb.npts, dK, rp, gb.E, gb.rmask,
-                                                                 gb.rinfo, gb.tr_subset, gb.tr_nmodels,
-                                                                 gb.tr_counts, gb.tr_models, gb.tr_cap);
+  const int chunks = ransac_chunks(n_pairs, rp.max_iters);
+  const int sr_cap = kMaxChunks * kChunk;
+  const int tb = (n_pairs + 127) / 128;
+  k_ransac_begin<<<tb, 128, 0, s>>>(mb.m_n, n_pairs, rp, gb.rstate, gb.rsubsets, sr_cap);
+  ++*launches;
+  const int rounds = 1 + (max(rp.max_iters - kFirstRound, 0) + chunks * kChunk - 1) / (chunks * kChunk);
+  for (int r = 0; r < rounds; ++r) {
+    dim3 grid(r == 0 ? 1 : chunks, n_pairs);
+    k_ransac_solve<<<grid, kRansacThreads, sizeof(RansacShared), s>>>(mb.m_n, mcap, gb.npts, dK, rp, gb.rstate, gb.rsubsets,
+                                                                      sr_cap, gb.rcands, gb.rncand, gb.tr_subset,
+                                                                      gb.tr_nmodels, gb.tr_counts, gb.tr_models, gb.tr_cap);
+    k_ransac_replay<<<tb, 128, 0, s>>>(mb.m_n, n_pairs, rp, gb.rstate, gb.rsubsets, sr_cap, chunks, gb.rcands, gb.rncand);
+    *launches += 2;
+  }
+  k_ransac_finish<<<n_pairs, kRansacThreads, 0, s>>>(mb.m_n, mcap, gb.npts, dK, rp, gb.rstate, gb.E, gb.rmask, gb.rinfo);
   ++*launches;
 }
 
@@ -284,7 +363,7 @@ void launch_pose(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_
 }
 
 int setup_geom_attributes() {
-  return (int)cudaFuncSetAttribute(k_ransac, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  return (int)cudaFuncSetAttribute(k_ransac_solve, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)sizeof(RansacShared));
 }
 

@@ -3,7 +3,6 @@
 // cv2.ORB.detectAndCompute as the reference calls it (src/core/pose_estimator.py:85-91, :108).
 // Every launch covers the whole batch (grid.y / grid.z = image slot); the dense kernels
 // (FAST, blur) cover all pyramid levels in one launch through a flat tile table.
-#include <cstdlib>
 #include "rpe_device.cuh"
 #include "orb_math.cuh"
 #include "tma.cuh"
@@ -240,256 +239,56 @@ void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream
   }
 }
 
-namespace fast_v1 {
 // ------------------------------------------------------------------ K2: FAST-9 + 3x3 NMS + border
-// One CTA (8 warps) = one 120x30 tile of one level of one image (tile table: ftab); the scored
-// region (tile + 1) is 32 rows x 32 aligned pixel quads, one warp per row, four rows per warp.
-//  (1) TMA: one bulk copy per image row of the tile (+halo) into shared memory (UBLKCP);
-//  (2) branch-free packed pre-test, four pixels per thread (fast_compass4); the ~3 % of pixels
-//      that pass are compacted into a shared-memory queue;
-//  (3) one thread per queued pixel: FAST-9 corner test + score in one packed min/max network
-//      (fast9_score) -> score tile in shared memory + corner queue;
-//  (4) one thread per corner: strict 3x3 NMS on the score tile, 31-px border filter,
-//      append (score<<24 | y<<12 | x) to the level's candidate list + score histogram.
-constexpr int kFastIP = 160;                 // staged bytes per image row (16-B aligned start)
-constexpr int kFastIH = kFastTH + 8;         // image rows y0-4 .. y0+TH+3
-constexpr int kFastSP = 128;                 // score tile pitch: x0-4 .. x0+123
-constexpr int kFastSH = kFastTH + 2;         // score rows y0-1 .. y0+TH
-static_assert(kFastSH == 32 && kFastTW + 8 == kFastSP, "one warp per score row, 32 quads per row");
-
-#ifndef RPE_FAST_CPASYNC
-#define RPE_FAST_CPASYNC 1   // 1: 16-byte LDGSTS staging by all threads (2.23 -> 2.02 ms); 0: TMA bulk rows + mbarrier
-#endif
-
-struct FastTile {
-  const uint8_t* src;   // level base of this image
-  int level, x0, y0, astart, img;
-};
-
-__device__ __forceinline__ FastTile fast_tile(const OrbGeom& g, const uint8_t* pyr, const uint32_t* ftab, int tile, int img) {
-  FastTile T;
-  T.img = img;
-  const uint32_t e = __ldg(ftab + tile);                  // level<<24 | ty<<12 | tx
-  T.level = e >> 24;
-  T.x0 = kFastOrigin + (int)(e & 0xfff) * kFastTW;
-  T.y0 = kFastOrigin + (int)((e >> 12) & 0xfff) * kFastTH;
-  T.astart = (T.x0 - 8) & ~15;
-  T.src = pyr + (size_t)img * g.pyr_stride + g.lv[T.level].off;
-  return T;
-}
-
-// rows y0-4 .. y0+TH+3, columns astart .. astart+159, clipped to the level buffer.  Bytes
-// outside the level are never read for a pixel that can become a candidate.
-__device__ __forceinline__ void fast_issue(const OrbGeom& g, const FastTile& T, uint8_t* buf, uint64_t* bar, int tid) {
-  const LevelGeom& L = g.lv[T.level];
-  const int row_bytes = min(kFastIP, L.pitch - T.astart);
-  const int n_rows = min(kFastIH, L.h - (T.y0 - 4));
-#if RPE_FAST_CPASYNC
-  // 16-byte asynchronous copies (LDGSTS) by all threads, one commit group per tile.  Chunk q of this thread is
-  // (row, 16-byte column) = ((tid + 256 q) / 10, (tid + 256 q) % 10): tile-independent, the compiler hoists it
-  const uint8_t* base = T.src + (size_t)(T.y0 - 4) * L.pitch + T.astart;
-#pragma unroll
-  for (int q = 0; q < (kFastIH * (kFastIP / 16) + 255) / 256; ++q) {
-    const int idx = tid + 256 * q;
-    const int row = idx / (kFastIP / 16), col16 = (idx - row * (kFastIP / 16)) * 16;
-    if (row < n_rows && col16 < row_bytes)
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(buf) + row * kFastIP + col16),
-                   "l"(base + row * L.pitch + col16) : "memory");
-  }
-  asm volatile("cp.async.commit_group;" ::: "memory");
-#else
-  if (tid == 0) mbar_arrive_expect_tx(bar, (uint32_t)(row_bytes * n_rows));
-  if (tid < n_rows)
-    bulk_copy_g2s(buf + tid * kFastIP, T.src + (size_t)(T.y0 - 4 + tid) * L.pitch + T.astart, (uint32_t)row_bytes, bar);
-#endif
-}
-
-#ifndef RPE_FAST_TILES
-#define RPE_FAST_TILES 4
-#endif
-constexpr int kFastTilesPerCta = RPE_FAST_TILES;   // consecutive tiles of one image per CTA, TMA double-buffered
-
-#ifndef RPE_FAST_MINB
-#define RPE_FAST_MINB 6
-#endif
-__global__ void __launch_bounds__(256, RPE_FAST_MINB)
-k_fast_v1(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
-       int n_img, uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
-  __shared__ __align__(128) uint8_t simg2[2][kFastIH * kFastIP];
-  __shared__ __align__(16) uint8_t ssc[kFastSH * kFastSP];
-  __shared__ uint16_t s_cand[kFastSH * kFastSP];
-  __shared__ uint16_t s_corner[kFastSH * kFastSP];
-  __shared__ __align__(8) uint64_t s_bar[2];
-  __shared__ uint32_t s_ncand, s_ncorner;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int thr = g.fast_threshold;
-  const uint32_t t4 = (uint32_t)min(thr, 127) * 0x01010101u;
-  const int tile0 = blockIdx.x * kFastTilesPerCta;
-  const int ntile = min(kFastTilesPerCta, g.total_ftiles - tile0);
-  if (tid == 0) {
-    mbar_init(&s_bar[0], 1);
-    mbar_init(&s_bar[1], 1);
-  }
-  __syncthreads();
-  // the rows of tile j+1 are requested (TMA) before tile j is processed
-  fast_issue(g, fast_tile(g, pyr, ftab, tile0, blockIdx.y), simg2[0], &s_bar[0], tid);
-  for (int j = 0; j < ntile; ++j) {
-    const FastTile T = fast_tile(g, pyr, ftab, tile0 + j, blockIdx.y);
-    const uint8_t* simg = simg2[j & 1];
-    if (j + 1 < ntile)
-      fast_issue(g, fast_tile(g, pyr, ftab, tile0 + j + 1, blockIdx.y), simg2[(j + 1) & 1], &s_bar[(j + 1) & 1], tid);
-    if (tid == 0) {
-      s_ncand = 0;
-      s_ncorner = 0;
-    }
-    reinterpret_cast<uint4*>(ssc)[tid] = make_uint4(0, 0, 0, 0);
-#if RPE_FAST_CPASYNC
-    if (j + 1 < ntile) asm volatile("cp.async.wait_group 1;" ::: "memory");
-    else asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
-#else
-    __syncthreads();
-    mbar_wait(&s_bar[j & 1], (uint32_t)(j >> 1) & 1u);
-#endif
-    const LevelGeom& L = g.lv[T.level];
-    const int x0 = T.x0, y0 = T.y0;
-    // (2) packed pre-test.  Scores are only ever needed for x in [30, w-30), y in [30, h-30).
-    const int xlo = max(30, x0 - 1), xhi = min(L.w - 30, x0 + kFastTW + 1);
-    const int ylo = max(30, y0 - 1), yhi = min(L.h - 30, y0 + kFastTH + 1);
-    const int ib = x0 - 4 - T.astart;                      // smem byte column of score column 0
-    const int xq = x0 - 4 + 4 * lane;                      // first pixel of this lane's quad
-    const int lo = min(max(xlo - xq, 0), 4), hi = min(max(xhi - xq, 0), 4);
-    const uint32_t vmask = (uint32_t)(0x80808080ull << (8 * lo)) & (uint32_t)(0x80808080ull >> (8 * (4 - hi)));
-    const uint32_t* wimg = reinterpret_cast<const uint32_t*>(simg) + (ib >> 2) + lane;
-    // the four rows of the warp first, then ONE compaction: per-lane count -> warp scan -> one shared atomic per
-    // warp -> straight-line predicated stores (no per-lane loop over set bits: candidates cluster, so the loop ran
-    // to the worst lane's count)
-    uint32_t cw[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int sr = warp * 4 + k;
-      const int y = y0 - 1 + sr;
-      cw[k] = 0;
-      if (y >= ylo && y < yhi) {                           // warp-uniform
-        const uint32_t* row = wimg + (sr + 3) * (kFastIP / 4);
-        cw[k] = fast_compass4(row[-1], row[0], row[1], row[-3 * (kFastIP / 4)], row[3 * (kFastIP / 4)], t4) & vmask;
-      }
-    }
-    // bit 7 - k of byte j = row k, pixel j of this lane's quad
-    const uint32_t merged = cw[0] | (cw[1] >> 1) | (cw[2] >> 2) | (cw[3] >> 3);
-    if (__any_sync(0xffffffffu, merged != 0)) {
-      const uint32_t c = (uint32_t)__popc(merged);
-      uint32_t inc = c;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += v;
-      }
-      uint32_t base = 0;
-      if (lane == 31) base = atomicAdd(&s_ncand, inc);
-      base = __shfl_sync(0xffffffffu, base, 31);
-      uint16_t* out = s_cand + base + inc - c;
-      const uint32_t e00 = (uint32_t)((warp * 4) << 7) | (uint32_t)(4 * lane);
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-#pragma unroll
-        for (int jj = 0; jj < 4; ++jj)
-          if (merged & (0x80u >> k << (8 * jj))) *out++ = (uint16_t)(e00 + (k << 7) + jj);
-    }
-    __syncthreads();
-
-    // (3) corner test + score of the queued pixels in one pass (fast9_score: both polarities packed)
-    const int ncand = (int)s_ncand;
-    for (int i = tid; i < ncand; i += 256) {
-      const int e = s_cand[i];
-      const int sr = e >> 7, c = e & 127;
-      const int sc = fast9_score(&simg[(sr + 3) * kFastIP + ib + c], kFastIP, thr);
-      if (sc > 0) {
-        ssc[e] = (uint8_t)sc;
-        s_corner[atomicAdd(&s_ncorner, 1u)] = (uint16_t)e;
-      }
-    }
-    __syncthreads();
-    const int ncorner = (int)s_ncorner;
-
-    // (4) NMS + border filter + append
-    uint32_t* cnt = cand_cnt + T.img * g.nlevels + T.level;
-    uint32_t* hst = hist + (size_t)(T.img * g.nlevels + T.level) * 256;
-    uint32_t* out = cand_key + (size_t)T.img * g.cand_stride + L.cand_off;
-    for (int i = tid; i < ncorner; i += 256) {
-      const int e = s_corner[i];
-      const int sr = e >> 7, c = e & 127;
-      if (sr < 1 || sr > kFastTH || c < 4 || c >= 4 + kFastTW) continue;
-      const int x = x0 - 4 + c, y = y0 - 1 + sr;
-      if (x < 31 || x >= L.w - 31 || y < 31 || y >= L.h - 31) continue;
-      const uint8_t* p = &ssc[e];
-      const int s = p[0];
-      const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
-                        s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
-      if (!keep) continue;
-      const uint32_t pos = atomicAdd(cnt, 1u);
-      if (pos < (uint32_t)L.cand_cap) out[pos] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
-      atomicAdd(&hst[s], 1u);
-    }
-    __syncthreads();   // every reader of this tile's buffers is done before they are reused
-  }
-}
-
-static void launch_fast_v1(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
-  if (g.total_ftiles == 0) return;
-  dim3 grid((g.total_ftiles + kFastTilesPerCta - 1) / kFastTilesPerCta, n_img);
-  k_fast_v1<<<grid, 256, 0, s>>>(g, b.pyr, b.ftab, n_img, b.cand_key, b.cand_cnt, b.hist);
-  ++*launches;
-}
-
-}  // namespace fast_v1
-using fast_v1::launch_fast_v1;
-
-// ------------------------------------------------------------------ K2: FAST-9 + 3x3 NMS + border
-// One WARP = one 120x30 tile of one level of one image (flat tile table: ftab).  Warps are independent: own slice
-// of shared memory, own mbarrier, no CTA-wide barrier.  The scored region (tile + 1 px for the NMS neighbours) is
-// 32 rows x 32 aligned pixel quads: lane = quad column, the warp walks down the 32 rows.
+// One WARP = one 120x14 tile of one level of one image (flat tile table: ftab).  Warps are independent: own slice
+// of shared memory (6.3 KB: 32 warps per SM), own mbarrier, no CTA-wide barrier.  The scored region (tile + 1 px
+// for the NMS neighbours) is 16 rows x 32 aligned pixel quads: lane = quad column, the warp walks down the rows.
 //  (1) TMA: one bulk copy per image row of the tile (+halo) onto the warp's mbarrier (UBLKCP), issued by the lanes;
 //      the score tile is cleared while the rows are in flight;
-//  (2) packed pre-test, four pixels per lane and row (fast_compass4_unpacked): the unpacked column word of an image
-//      row is kept in a 7-row register window and serves as D, C and U of three score rows.  The pass bits of the
-//      lane's 32 x 4 pixels collect in four registers (one per band of 8 rows);
+//  (2) packed pre-test, four pixels per lane and row (fast_compass4_unpacked): the column word of an image row
+//      serves as D, C and U of three score rows (7-row register window).  The pass bits of the lane's 16 x 4 pixels
+//      collect in two registers (one per band of 8 rows);
 //  (3) compaction per CANDIDATE, not per pixel: one warp scan over the lanes' candidate counts, then every lane
-//      expands its own set bits into the warp's queue.  A lane owns 128 pixels (~4 candidates, worst lane ~10), so
-//      the lanes' loops are short and even - with 16 pixels per thread (one CTA per tile, four rows per warp) the
-//      same loop ran to a worst lane of ~6 against a mean of 0.5, and the per-pixel predicated stores that replaced
-//      it cost 133 instructions per thread and tile (9.5 per pixel; ncu, round 1);
+//      expands its own set bits into the warp's queue (round 1 spent 133 instructions per thread and tile on
+//      per-pixel predicated stores: 9.5 per pixel; ncu);
 //  (4) one lane per queued pixel: FAST-9 corner test + score in one packed min/max network (fast9_score) -> score
 //      tile; the corners are compacted in place at the head of the queue (ballot);
-//  (5) one lane per corner: strict 3x3 NMS on the score tile, 31-px border filter, append
-//      (score<<24 | y<<12 | x) to the level's candidate list + score histogram.
-// A tile with more candidates than the queue holds (dense noise) is processed band by band and its NMS scans the
-// score tile instead of a corner list.
-constexpr int kFastIP = 160;                 // staged bytes per image row (16-B aligned start)
+//  (5) one lane per corner: strict 3x3 NMS on the score tile, 31-px border filter; the survivors' keys
+//      (score<<24 | y<<12 | x) collect in shared memory (over the image rows, no longer needed) and go to the
+//      level's candidate list with ONE global atomicAdd per tile (a returning atomic per corner left the warp
+//      waiting on L2 round trips: 30 % of the stall samples of the first version of this kernel), + histogram.
+// A tile with more candidates than the queue holds (dense noise) is processed in half-bands of 4 rows and its NMS
+// scans the score tile instead of a corner list.
+// Measured on B200, 512 images 1280x720, 12 levels (profiles/): one CTA of 8 warps per 120x30 tile (round 1)
+// 3.78 ms at 44.6 thread-instructions per pixel; one warp per 120x30 tile 5.67 ms (33.7 instructions per pixel but 12
+// warps per SM); this form: see DESIGN.md.
+constexpr int kFastIP = 144;                 // staged bytes per image row (16-B aligned start; columns ib-3 .. ib+130 used)
 constexpr int kFastIH = kFastTH + 8;         // image rows y0-4 .. y0+TH+3
 constexpr int kFastSP = 128;                 // score tile pitch: x0-4 .. x0+123
 constexpr int kFastSH = kFastTH + 2;         // score rows y0-1 .. y0+TH
 constexpr int kFastIPW = kFastIP / 4;
-static_assert(kFastSH == 32 && kFastTW + 8 == kFastSP, "32 score rows in four bands of 8, 32 quads per row");
-// unpack a column word into its two u16x2 halves ONCE: volatile keeps ptxas from re-deriving them from the raw word
-// at each of the three rows that use them (it prefers the PRMTs to the registers: 7.7 instead of 6 per row)
+constexpr int kFastBands = kFastSH / 8;
+static_assert(kFastSH % 8 == 0 && kFastTW + 8 == kFastSP, "score rows in bands of 8, 32 quads per row");
+constexpr int kFastWarps = 4;                // independent warps (tiles) per CTA
+constexpr int kFastQueue = 512;              // queue entries per warp; a half-band of 4 rows x 128 px always fits
+
+// unpack a column word into its two u16x2 halves (volatile: keep the order of the window updates as written)
 __device__ __forceinline__ void fast_unpack_keep(uint32_t w, uint32_t& lo, uint32_t& hi) {
   asm volatile("prmt.b32 %0, %1, 0, 0x4140;" : "=r"(lo) : "r"(w));
   asm volatile("prmt.b32 %0, %1, 0, 0x4342;" : "=r"(hi) : "r"(w));
 }
-constexpr int kFastWarps = 4;                // independent warps (tiles) per CTA
-constexpr int kFastQueue = 1024;             // queue entries per warp; a band of 8 rows x 128 px always fits
 
 struct __align__(16) FastWarpSmem {
   uint8_t img[kFastIH * kFastIP];
   uint8_t score[kFastSH * kFastSP];
   uint16_t queue[kFastQueue];
   uint64_t bar;
-  uint64_t pad;
+  uint32_t n_keep, pad;
 };
 static_assert(sizeof(FastWarpSmem) % 16 == 0, "warp slices stay 16-byte aligned");
+static_assert(kFastIH * kFastIP >= 4 * ((kFastTH + 1) / 2) * ((kFastTW + 1) / 2), "kept keys (NMS maxima: at most one pixel in four) fit over the image rows");
 
-__global__ void __launch_bounds__(kFastWarps * 32, 4)
+__global__ void __launch_bounds__(kFastWarps * 32, 8)
 k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
        uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
   extern __shared__ __align__(128) uint8_t s_fast[];
@@ -505,16 +304,18 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
   const int pitch = L.pitch, lw = L.w, lh = L.h;
   const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off + (size_t)(y0 - 4) * pitch + astart;
 
-  // (1) rows y0-4 .. y0+TH+3, columns astart .. astart+159, clipped to the level buffer.  Bytes outside the level
+  // (1) rows y0-4 .. y0+TH+3, columns astart .. astart+143, clipped to the level buffer.  Bytes outside the level
   //     are never read for a pixel that can become a candidate
   const uint32_t row_bytes = (uint32_t)min(kFastIP, pitch - astart);
   const int n_rows = min(kFastIH, lh - (y0 - 4));
   if (lane == 0) {
+    S.n_keep = 0;
     mbar_init(&S.bar, 1);
     mbar_arrive_expect_tx(&S.bar, row_bytes * (uint32_t)n_rows);
   }
   __syncwarp();
-  for (int r = lane; r < n_rows; r += 32) bulk_copy_g2s(S.img + r * kFastIP, src + (size_t)r * pitch, row_bytes, &S.bar);
+  if (lane < n_rows) bulk_copy_g2s(S.img + lane * kFastIP, src + (size_t)lane * pitch, row_bytes, &S.bar);
+  static_assert(kFastIH <= 32, "one staged row per lane");
 #pragma unroll
   for (int i = 0; i < kFastSH * kFastSP / (16 * 32); ++i) reinterpret_cast<uint4*>(S.score)[i * 32 + lane] = make_uint4(0, 0, 0, 0);
   const int thr = g.fast_threshold;
@@ -536,7 +337,9 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
   for (int r = 0; r < 6; ++r) fast_unpack_keep(wimg[r * kFastIPW], wl[r], wh[r]);
   const uint32_t kt = fast_compass_kt(t4);
   const int sr_lo = ylo - (y0 - 1), sr_n = yhi - ylo;       // valid score rows: sr_lo <= sr < sr_lo + sr_n
-  uint32_t m[4] = {0u, 0u, 0u, 0u};                          // bit 7 - k of byte j of m[b] = score row 8 b + k, pixel j of the quad
+  uint32_t m[kFastBands];                                    // bit 7 - k of byte j of m[b] = score row 8 b + k, pixel j of the quad
+#pragma unroll
+  for (int b = 0; b < kFastBands; ++b) m[b] = 0u;
 #pragma unroll
   for (int sr = 0; sr < kFastSH; ++sr) {
     fast_unpack_keep(wimg[(sr + 6) * kFastIPW], wl[(sr + 6) % 7], wh[(sr + 6) % 7]);
@@ -548,9 +351,11 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
   }
 
   const uint32_t lt = (1u << lane) - 1u;
-  // queue the set bits of the bands in mm[] (all four, or one with the others zero); returns the warp's total
+  // queue the set bits of the bands in mm[]; returns the warp's total (<= kFastQueue by the caller's choice of mm)
   auto push = [&](const uint32_t* mm) -> int {
-    const int c = __popc(mm[0]) + __popc(mm[1]) + __popc(mm[2]) + __popc(mm[3]);
+    int c = 0;
+#pragma unroll
+    for (int b = 0; b < kFastBands; ++b) c += __popc(mm[b]);
     int inc = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -559,11 +364,11 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
     }
     uint16_t* out = S.queue + (inc - c);
 #pragma unroll
-    for (int b = 0; b < 4; ++b) {
+    for (int b = 0; b < kFastBands; ++b) {
       uint32_t bits = mm[b];
       while (bits) {
-        const int p = __ffs(bits) - 1;                       // bit p: pixel p >> 3 of the quad, row 8 b + 7 - (p & 7)
-        bits &= bits - 1u;
+        const int p = 31 - __clz(bits);                      // bit p: pixel p >> 3 of the quad, row 8 b + 7 - (p & 7)
+        bits ^= 1u << p;
         *out++ = (uint16_t)(((8 * b + 7 - (p & 7)) << 7) | (4 * lane + (p >> 3)));
       }
     }
@@ -591,11 +396,8 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
     __syncwarp();
     return n_corner;
   };
-  // (5) NMS + border filter + append, for the corner at score-tile offset e
-  uint32_t* cnt = cand_cnt + img * g.nlevels + level;
-  uint32_t* hst = hist + (size_t)(img * g.nlevels + level) * 256;
-  uint32_t* out_key = cand_key + (size_t)img * g.cand_stride + L.cand_off;
-  const uint32_t cap = (uint32_t)L.cand_cap;
+  // (5) NMS + border filter for the corner at score-tile offset e; survivors' keys -> shared memory
+  uint32_t* keep_keys = reinterpret_cast<uint32_t*>(S.img);  // (all scores are in the score tile by now)
   auto nms = [&](int e) {
     const int sr = e >> 7, c = e & 127;
     if (sr < 1 || sr > kFastTH || c < 4 || c >= 4 + kFastTW) return;
@@ -605,13 +407,12 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
     const int s = p[0];
     const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
                       s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
-    if (!keep) return;
-    const uint32_t pos = atomicAdd(cnt, 1u);
-    if (pos < cap) out_key[pos] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
-    atomicAdd(&hst[s], 1u);
+    if (keep) keep_keys[atomicAdd(&S.n_keep, 1u)] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
   };
 
-  int all = __popc(m[0]) + __popc(m[1]) + __popc(m[2]) + __popc(m[3]);
+  int all = 0;
+#pragma unroll
+  for (int b = 0; b < kFastBands; ++b) all += __popc(m[b]);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) all += __shfl_xor_sync(0xffffffffu, all, o);
   if (all == 0) return;
@@ -619,11 +420,12 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
     const int n_corner = score(push(m));
     for (int i = lane; i < n_corner; i += 32) nms(S.queue[i]);
   } else {
-    // dense tile: band by band (a band is at most 8 x 128 = kFastQueue pixels), then NMS over the score tile
+    // dense tile: half-bands of 4 rows (at most 4 x 128 = kFastQueue pixels), then NMS over the score tile
 #pragma unroll 1
-    for (int b = 0; b < 4; ++b) {
-      // (selects instead of a dynamic register index)
-      const uint32_t one[4] = {b == 0 ? m[0] : 0u, b == 1 ? m[1] : 0u, b == 2 ? m[2] : 0u, b == 3 ? m[3] : 0u};
+    for (int hb = 0; hb < 2 * kFastBands; ++hb) {
+      uint32_t one[kFastBands];
+#pragma unroll
+      for (int b = 0; b < kFastBands; ++b) one[b] = (hb >> 1) == b ? (m[b] & ((hb & 1) ? 0x0f0f0f0fu : 0xf0f0f0f0u)) : 0u;
       score(push(one));
     }
     for (int sr = 1; sr <= kFastTH; ++sr) {
@@ -633,12 +435,26 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
         if ((w >> (8 * j)) & 0xffu) nms(sr * kFastSP + 4 * lane + j);
     }
   }
+  __syncwarp();
+  // one slot reservation per tile, then coalesced key stores + the score histogram
+  const uint32_t n_keep = S.n_keep;
+  if (n_keep == 0) return;
+  uint32_t* cnt = cand_cnt + img * g.nlevels + level;
+  uint32_t* hst = hist + (size_t)(img * g.nlevels + level) * 256;
+  uint32_t* out_key = cand_key + (size_t)img * g.cand_stride + L.cand_off;
+  const uint32_t cap = (uint32_t)L.cand_cap;
+  uint32_t base = 0;
+  if (lane == 0) base = atomicAdd(cnt, n_keep);
+  base = __shfl_sync(0xffffffffu, base, 0);
+  for (uint32_t i = lane; i < n_keep; i += 32) {
+    const uint32_t key = keep_keys[i];
+    if (base + i < cap) out_key[base + i] = key;
+    atomicAdd(&hst[key >> 24], 1u);
+  }
 }
 
 void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   if (g.total_ftiles == 0) return;
-  static const bool v1 = getenv("RPE_FAST_V1") != nullptr;   // TEMPORARY A/B against the round-1 kernel
-  if (v1) { launch_fast_v1(g, b, n_img, s, launches); return; }
   dim3 grid((g.total_ftiles + kFastWarps - 1) / kFastWarps, n_img);
   k_fast<<<grid, kFastWarps * 32, kFastWarps * sizeof(FastWarpSmem), s>>>(g, b.pyr, b.ftab, b.cand_key, b.cand_cnt, b.hist);
   ++*launches;

@@ -30,7 +30,7 @@ struct LevelGeom {
   int kp_off, kp_cap;      // slice of the per-image per-level keypoint arrays
   int xtab, ytab;          // tap-table offsets for producing this level from the previous one
   int tile0, tiles_x, tiles_y;     // 64 x 32 tiles (blur)
-  int ftile0, ftiles_x, ftiles_y;  // 120 x 30 tiles restricted to the rows/cols FAST needs
+  int ftile0, ftiles_x, ftiles_y;  // kFastTW x kFastTH tiles restricted to the rows/cols FAST needs
 };
 
 struct OrbGeom {
@@ -51,7 +51,7 @@ struct OrbGeom {
 constexpr int kTileW = 64;
 constexpr int kTileH = 32;
 constexpr int kFastTW = 120;
-constexpr int kFastTH = 30;
+constexpr int kFastTH = 14;     // 16 score rows = two bands of 8 (k_fast: one warp per tile)
 constexpr int kBlurRows = 32;    // blur work item = 128 columns x two strips of kBlurRows rows (one warp)
 constexpr int kFastOrigin = 24;  // FAST tiles start at x = y = 24 (a multiple of 4): only scores in [30, size-30) can matter
 
@@ -83,6 +83,18 @@ struct MatchBuffers {
   int32_t* pstat;   // [NP] per pair: bit 0 = an image without descriptors, RPE_STATUS_FLAG_OVERFLOW = list overflow
 };
 
+// per-pair RANSAC state between the kernels of a super-round (kernels_geom.cu)
+struct RansacState {
+  unsigned long long rng;   // OpenCV's MWC generator, advanced exactly as cv2's loop advances it
+  int best, niters, it0, done, have_best, nh, solved, overflow;   // nh = hypotheses of the super-round in flight
+  double best_model[9];
+};
+// a model that can win OpenCV's sequential update: a prefix maximum of its chunk
+struct RansacCand {
+  int h, r, count, pad;     // hypothesis index inside the super-round, model index, inlier count
+  double E[9];
+};
+
 struct GeomBuffers {
   double* npts;     // [NP][mcap][4] normalised (x1, y1, x2, y2)
   double* E;        // [NP][9]
@@ -92,6 +104,10 @@ struct GeomBuffers {
   int32_t* pose_cnt;
   uint8_t* pmask;
   int32_t* status;
+  RansacState* rstate;      // [NP]
+  int32_t* rsubsets;        // [NP][kMaxChunks * kChunk][5]
+  RansacCand* rcands;       // [NP][kMaxChunks][kCandCap]
+  int32_t* rncand;          // [NP][kMaxChunks]
   // optional per-hypothesis trace of pair 0 (stage entry point only)
   int32_t* tr_subset; int32_t* tr_nmodels; int32_t* tr_counts; double* tr_models; int32_t tr_cap;
 };
@@ -134,5 +150,7 @@ void launch_eval_summary(int n, const double* errors, double* summary, cudaStrea
 int setup_orb_attributes(int sort_cap);
 int setup_match_attributes(int sort_cap);
 int setup_geom_attributes();
+constexpr int kRansacSuperRoundCap = 8 * 64;   // kMaxChunks * kChunk (kernels_geom.cu)
+constexpr int kRansacCandPerPair = 8 * 32;     // kMaxChunks * kCandCap
 
 }  // namespace rpe
