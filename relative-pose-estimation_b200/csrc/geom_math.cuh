@@ -62,6 +62,39 @@ RPE_HD float sampson_err_f32(const double* E, double x1, double y1, double x2, d
   return (float)(f64_mul(x2tEx1, x2tEx1) / den);
 }
 
+// The inlier decision `(float)(num2 / den) <= t2` of the RANSAC loop WITHOUT the FP64 division (a third of the
+// scoring instructions; ncu).  (float)q <= t2 holds iff q lies below the midpoint `mid` between t2 and the next
+// float (or on it when the tie rounds down to t2), and q = fl(num2 / den) lies on the same side of mid as the exact
+// quotient whenever that is further than a few ulps from mid: then sign(num2 - mid * den) decides.  The rare pair
+// within 1e-13 of the boundary (and den == 0) takes the division, so the decision is the reference's in every case.
+struct SampsonGate {
+  float t2;
+  double mid;
+};
+RPE_HD SampsonGate sampson_gate(float t2) {
+  SampsonGate g;
+  g.t2 = t2;
+  union { float f; uint32_t u; } a, b;
+  a.f = t2;
+  b.u = a.u + 1u;                                   // next float above t2 (t2 > 0, finite)
+  g.mid = ((double)a.f + (double)b.f) * 0.5;        // exact in double
+  return g;
+}
+RPE_HD bool sampson_is_inlier(const double* E, double x1, double y1, double x2, double y2, const SampsonGate& g) {
+  const double Ex0 = f64_add(f64_add(f64_mul(E[0], x1), f64_mul(E[1], y1)), E[2]);
+  const double Ex1 = f64_add(f64_add(f64_mul(E[3], x1), f64_mul(E[4], y1)), E[5]);
+  const double Ex2 = f64_add(f64_add(f64_mul(E[6], x1), f64_mul(E[7], y1)), E[8]);
+  const double Et0 = f64_add(f64_add(f64_mul(E[0], x2), f64_mul(E[3], y2)), E[6]);
+  const double Et1 = f64_add(f64_add(f64_mul(E[1], x2), f64_mul(E[4], y2)), E[7]);
+  const double x2tEx1 = f64_add(f64_add(f64_mul(x2, Ex0), f64_mul(y2, Ex1)), Ex2);
+  const double den = f64_add(f64_add(f64_add(f64_mul(Ex0, Ex0), f64_mul(Ex1, Ex1)), f64_mul(Et0, Et0)), f64_mul(Et1, Et1));
+  const double num2 = f64_mul(x2tEx1, x2tEx1);
+  const double md = g.mid * den;
+  const double r = num2 - md;
+  if (fabs(r) > 1e-13 * md) return r < 0.0;         // (false for NaN / inf operands as well: they take the division)
+  return (float)(num2 / den) <= g.t2;
+}
+
 // ------------------------------------------------------------------ five-point solver
 // monomial bookkeeping: linear {x,y,z,1}; quadratic (10); cubic (20) in the column order
 // [x3 y3 x2y xy2 x2z x2 y2z y2 xyz xy | xz2 xz x yz2 yz y z3 z2 z 1]
@@ -100,10 +133,17 @@ RPE_HD Cplx cdiv(Cplx a, Cplx b) {
 #if !defined(__CUDA_ARCH__)
 static int g_dk_iters_last = 0;   // TEST-ONLY instrumentation of the host instantiation
 #endif
-RPE_HDN void solve_poly10(const double* c, Cplx* roots, int max_iters) {
-  const int n = 10;
+RPE_HDN void solve_poly10(const double* c_in, Cplx* roots_out, int max_iters) {
+  // coefficients and roots live in registers: every loop over them is fully unrolled (with the roots behind the
+  // caller's pointer the inner loop was 20 local-memory loads per root and iteration; ncu, round 2)
+  constexpr int n = 10;
+  double c[n + 1];
+#pragma unroll
+  for (int i = 0; i <= n; ++i) c[i] = c_in[i];
+  Cplx roots[n];
   Cplx p{1.0, 0.0};
   const Cplx r{1.0, 1.0};
+#pragma unroll
   for (int i = 0; i < n; ++i) {
     roots[i] = p;
     p = cmul(p, r);
@@ -111,9 +151,11 @@ RPE_HDN void solve_poly10(const double* c, Cplx* roots, int max_iters) {
   int iter = 0;
   for (; iter < max_iters; ++iter) {
     bool settled = true;
+#pragma unroll
     for (int i = 0; i < n; ++i) {
       p = roots[i];
       Cplx num{c[n], 0.0}, den{c[n], 0.0};
+#pragma unroll
       for (int j = 0; j < n; ++j) {
         num = cmul(num, p);
         num.re += c[n - j - 1];
@@ -135,10 +177,12 @@ RPE_HDN void solve_poly10(const double* c, Cplx* roots, int max_iters) {
   g_dk_iters_last = iter;
 #endif
   // Newton polish: z <- z - f(z) / f'(z), both by Horner
+#pragma unroll
   for (int i = 0; i < n; ++i) {
     Cplx z = roots[i];
     for (int k = 0; k < 8; ++k) {
       Cplx f{c[n], 0.0}, df{0.0, 0.0};
+#pragma unroll
       for (int j = n - 1; j >= 0; --j) {
         df = cmul(df, z);
         df.re += f.re; df.im += f.im;
@@ -152,7 +196,7 @@ RPE_HDN void solve_poly10(const double* c, Cplx* roots, int max_iters) {
       z.re -= dz.re; z.im -= dz.im;
       if (upd <= 4e-16 * mag) break;
     }
-    roots[i] = z;
+    roots_out[i] = z;
   }
 }
 

@@ -107,7 +107,7 @@ k_ransac_solve(const int32_t* __restrict__ m_n, int mcap, const double* __restri
   const int M = m_n[pair];
   const double4* P = reinterpret_cast<const double4*>(npts) + (size_t)pair * mcap;
   const double thr = rp.threshold / ((K[0] + K[4]) * 0.5);
-  const float t2 = (float)(thr * thr);
+  const SampsonGate gate = sampson_gate((float)(thr * thr));
   const int32_t* sub = subsets + ((size_t)pair * sr_cap + h0) * 5;
   for (int i = tid; i < nh * 5; i += kRansacThreads) S.subset[i / 5][i % 5] = sub[i];
   __syncthreads();
@@ -129,7 +129,7 @@ k_ransac_solve(const int32_t* __restrict__ m_n, int mcap, const double* __restri
     int cnt = 0;
     for (int i = lane; i < M; i += 32) {
       const double4 p = P[i];
-      cnt += (sampson_err_f32(E, p.x, p.y, p.z, p.w) <= t2) ? 1 : 0;
+      cnt += sampson_is_inlier(E, p.x, p.y, p.z, p.w, gate) ? 1 : 0;
     }
     for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     if (lane == 0) S.counts[h][r] = cnt;
@@ -233,12 +233,12 @@ k_ransac_finish(const int32_t* __restrict__ m_n, int mcap, const double* __restr
   __syncthreads();
   const double4* P = reinterpret_cast<const double4*>(npts) + (size_t)pair * mcap;
   const double thr = rp.threshold / ((K[0] + K[4]) * 0.5);
-  const float t2 = (float)(thr * thr);
+  const SampsonGate gate = sampson_gate((float)(thr * thr));
   for (int i = tid; i < M; i += kRansacThreads) {
     uint8_t v = 0;
     if (st.have_best) {
       const double4 p = P[i];
-      v = sampson_err_f32(sE, p.x, p.y, p.z, p.w) <= t2;
+      v = sampson_is_inlier(sE, p.x, p.y, p.z, p.w, gate);
     }
     rmask[(size_t)pair * mcap + i] = v;
   }

@@ -137,6 +137,14 @@ def sampson(E, x1, x2):
     return out
 
 
+def sampson_inlier(E, x1, x2, t2):
+    E = np.ascontiguousarray(E, np.float64); x1 = np.ascontiguousarray(x1, np.float64)
+    x2 = np.ascontiguousarray(x2, np.float64)
+    out = np.zeros(x1.shape[0], np.uint8)
+    lib().hc_sampson_inlier(_p(E), _p(x1), _p(x2), x1.shape[0], C.c_float(float(t2)), _p(out))
+    return out.astype(bool)
+
+
 def decompose(E):
     E = np.ascontiguousarray(E, np.float64)
     R1 = np.zeros((3, 3)); R2 = np.zeros((3, 3)); t = np.zeros(3)

@@ -106,6 +106,10 @@ int hc_five_point(const double* x1, const double* x2, double* E) { return five_p
 void hc_sampson(const double* E, const double* x1, const double* x2, int n, float* err) {
   for (int i = 0; i < n; ++i) err[i] = sampson_err_f32(E, x1[2 * i], x1[2 * i + 1], x2[2 * i], x2[2 * i + 1]);
 }
+void hc_sampson_inlier(const double* E, const double* x1, const double* x2, int n, float t2, uint8_t* ok) {
+  const SampsonGate g = sampson_gate(t2);
+  for (int i = 0; i < n; ++i) ok[i] = sampson_is_inlier(E, x1[2 * i], x1[2 * i + 1], x2[2 * i], x2[2 * i + 1], g);
+}
 void hc_decompose(const double* E, double* R1, double* R2, double* t) { decompose_essential(E, R1, R2, t); }
 void hc_cheirality(const double* R, const double* t, const double* x1, const double* x2, int n, double dist,
                    uint8_t* ok) {

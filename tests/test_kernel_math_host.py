@@ -121,6 +121,27 @@ def test_five_point_and_sampson():
     assert np.array_equal(hc.sampson(E, x1, x2), og.sampson_error_f32(E, x1, x2))
 
 
+def test_division_free_inlier_gate_is_the_reference_decision():
+    """sampson_is_inlier (no FP64 division) == `(float)(num2 / den) <= t2` for every point, including thresholds placed
+    exactly ON a point's error, one float above / below it, and the degenerate den == 0."""
+    p1, p2 = _points()
+    K = default_K()
+    x1, x2 = og.normalize_points(p1, K), og.normalize_points(p2, K)
+    E, _ = cv2.findEssentialMat(p1, p2, K, method=cv2.RANSAC, prob=0.999, threshold=1.0)
+    rng = np.random.default_rng(9)
+    for Em in (E, rng.standard_normal((3, 3)), np.zeros((3, 3))):
+        err = hc.sampson(Em, x1, x2)
+        finite = err[np.isfinite(err)]
+        thrs = [np.float32((1.0 / ((K[0, 0] + K[1, 1]) / 2)) ** 2)]
+        for e in (finite[:40] if len(finite) else []):
+            if e > 0:
+                thrs += [np.float32(e), np.nextafter(np.float32(e), np.float32(np.inf)), np.nextafter(np.float32(e), np.float32(0))]
+        for t2 in thrs:
+            with np.errstate(invalid="ignore"):
+                want = err <= t2
+            assert np.array_equal(hc.sampson_inlier(Em, x1, x2, t2), want), t2
+
+
 def test_decompose_cheirality_euler():
     p1, p2 = _points()
     K = default_K()
