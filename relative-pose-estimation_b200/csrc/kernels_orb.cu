@@ -975,18 +975,43 @@ k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, c
   // a warp only ever touches its own keypoints (k = warp, warp + 4, ...): warp-level synchronisation is enough, and
   // the four warps of the CTA drift through the phases independently
   __syncwarp();
-  // (3) descriptor
-#ifdef RPE_DESC_UNROLL
-#pragma unroll RPE_DESC_UNROLL
-#endif
-  for (int k = warp; k < nk; k += 4) {
+  // (3) descriptor.  The 256 steered tests of a keypoint gather 512 bytes from a 37 x 37 window of the blurred level
+  //     (pattern radius sqrt(13^2 + 13^2) = 18.4).  The warp first stages that window in shared memory with row-
+  //     contiguous word loads (37 rows x 11 aligned words), then gathers from there: straight from global memory a
+  //     gather instruction touched ~25 sectors and the kernel waited on them (ncu round 2: 41 % of the stall samples
+  //     on the compare that consumes the two bytes, l1tex at 68 %).  The next keypoint's window is in flight (in
+  //     registers) while the tests of the current one run.
+  constexpr int kWinR = 18, kWinRows = 2 * kWinR + 1, kWinWords = 11, kWinPitch = 4 * kWinWords;
+  constexpr int kWinLoads = (kWinRows * kWinWords + 31) / 32;
+  __shared__ __align__(16) uint8_t s_win[4][kWinRows * kWinPitch];
+  uint8_t* win = s_win[warp];
+  uint32_t wreg[kWinLoads];
+  auto fetch = [&](int k) {
     const LevelGeom& L = g.lv[s_level[k]];
-    const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];
+    const uint8_t* base = blur + (size_t)img * g.pyr_stride + L.off + (size_t)(s_cy[k] - kWinR) * L.pitch +
+                          ((s_cx[k] - kWinR) & ~3);
+#pragma unroll
+    for (int i = 0; i < kWinLoads; ++i) {
+      const int idx = lane + 32 * i, r = idx / kWinWords, w = idx - r * kWinWords;
+      wreg[i] = idx < kWinRows * kWinWords ? __ldg(reinterpret_cast<const uint32_t*>(base + (size_t)r * L.pitch) + w) : 0u;
+    }
+  };
+  if (warp < nk) fetch(warp);
+  for (int k = warp; k < nk; k += 4) {
+#pragma unroll
+    for (int i = 0; i < kWinLoads; ++i) {
+      const int idx = lane + 32 * i;
+      if (idx < kWinRows * kWinWords) reinterpret_cast<uint32_t*>(win)[idx] = wreg[i];   // (row r, word w) sits at word r * 11 + w
+    }
+    __syncwarp();
+    const uint8_t* c = win + kWinR * kWinPitch + kWinR + ((s_cx[k] - kWinR) & 3);          // the keypoint centre in the window
     const float a = s_a[k], b = s_b[k];
+    if (k + 4 < nk) fetch(k + 4);
     uint32_t byte = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) byte |= brief_test(c, L.pitch, a, b, pat[j]) << j;
+    for (int j = 0; j < 8; ++j) byte |= brief_test(c, kWinPitch, a, b, pat[j]) << j;
     desc[((size_t)img * g.kp_stride + i0 + k) * 32 + lane] = (uint8_t)byte;
+    __syncwarp();
   }
 }
 

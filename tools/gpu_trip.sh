@@ -24,7 +24,7 @@ for what in "$@"; do
       timeout 1500 compute-sanitizer --tool racecheck --error-exitcode 9 python tools/sanitize_target.py > gpurun_out/sanitizer_racecheck.log 2>&1; echo "racecheck rc=$?"; tail -4 gpurun_out/sanitizer_racecheck.log ;;
     ncu)
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --lean --inflight 1 > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-      timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'k_fast|k_blur|k_hamming|k_resize|k_ransac|k_describe|k_pose|k_select|k_build' --launch-skip 20 -c 20 -o gpurun_out/full -f python bench.py --steps 2 --warmup 1 --no-cpu-baseline --lean --batch 32 --inflight 1 > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?" ;;
+      timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'k_fast|k_blur|k_hamming|k_resize|k_ransac_solve|k_describe|k_pose|k_select|k_build' --launch-skip 20 -c 24 -o gpurun_out/full -f python bench.py --steps 2 --warmup 1 --no-cpu-baseline --lean --batch 32 --inflight 1 > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?" ;;
     cfg2)
       timeout 300 python tools/gpu_cfg2_time.py > gpurun_out/cfg2_time.log 2>&1; echo "cfg2 rc=$?"; tail -5 gpurun_out/cfg2_time.log
       timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_ransac|k_hamming|k_pose' -c 3 -o gpurun_out/cfg2 -f python tools/gpu_cfg2_time.py > gpurun_out/ncu_cfg2.log 2>&1; echo "ncu cfg2 rc=$?" ;;
