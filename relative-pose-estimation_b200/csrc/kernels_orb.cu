@@ -38,7 +38,7 @@ void launch_bgr2gray(const uint8_t* bgr, size_t src_stride, int src_pitch, uint8
 
 // ------------------------------------------------------------------ K1: pyramid level l from l-1
 __global__ void __launch_bounds__(256)
-k_resize(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,
+k_resize(const __grid_constant__ OrbGeom g, const PyrView pv, const int2* __restrict__ taps,
          int level) {
   const LevelGeom& d = g.lv[level];
   const LevelGeom& s = g.lv[level - 1];
@@ -46,8 +46,8 @@ k_resize(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int
   const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int y = blockIdx.y * 8 + threadIdx.y;
   if (y >= d.h || x4 >= d.pitch) return;
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + s.off;
-  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
+  const uint8_t* src = pv.level(g, img, level - 1);
+  uint8_t* dst = pv.pyr + (size_t)img * g.pyr_stride + d.off;
   const int2 ty = taps[d.ytab + y];
   uint32_t out = 0;
 #pragma unroll
@@ -69,7 +69,7 @@ k_resize(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int
 constexpr int kResizeRows = 8;
 
 __global__ void __launch_bounds__(256)
-k_resize_strip(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,
+k_resize_strip(const __grid_constant__ OrbGeom g, const PyrView pv, const int2* __restrict__ taps,
                int level) {
   const LevelGeom& d = g.lv[level];
   const LevelGeom& s = g.lv[level - 1];
@@ -77,8 +77,8 @@ k_resize_strip(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, con
   const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int y_first = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
   if (y_first >= d.h || x4 >= d.pitch) return;
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + s.off;
-  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
+  const uint8_t* src = pv.level(g, img, level - 1);
+  uint8_t* dst = pv.pyr + (size_t)img * g.pyr_stride + d.off;
   // horizontal taps of the four columns
   uint32_t sel[4], wgt[4];
   int xbase;
@@ -150,7 +150,7 @@ constexpr int kResizeSrcRows = 11;
 constexpr int kResizeStageBytes = kResizeSrcRows * 3 * 256 * 4;
 
 __global__ void __launch_bounds__(256)
-k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, const int2* __restrict__ taps,
+k_resize_staged(const __grid_constant__ OrbGeom g, const PyrView pv, const int2* __restrict__ taps,
                 int level) {
   extern __shared__ uint32_t s_rows[];   // [kResizeSrcRows][3][256 threads]
   const LevelGeom& d = g.lv[level];
@@ -160,8 +160,8 @@ k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, co
   const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int y_first = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
   if (y_first >= d.h || x4 >= d.pitch) return;
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + s.off;
-  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
+  const uint8_t* src = pv.level(g, img, level - 1);
+  uint8_t* dst = pv.pyr + (size_t)img * g.pyr_stride + d.off;
   const int y_end = min(y_first + kResizeRows, d.h);
   int2 ty = __ldg(&taps[d.ytab + y_first]);
   const int ra0 = ty.x;
@@ -221,19 +221,22 @@ k_resize_staged(const __grid_constant__ OrbGeom g, uint8_t* __restrict__ pyr, co
   }
 }
 
+static PyrView pyr_view(const OrbBuffers& b) { return PyrView{b.pyr, b.lvl0, b.lvl0_stride}; }
+
 void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
+  const PyrView pv = pyr_view(b);
   for (int l = 1; l < g.nlevels; ++l) {
     const LevelGeom& d = g.lv[l];
     // B200, 256 pairs: k_resize_strip on every level 2.20 ms; k_resize_staged on every level 1.81 ms
     if (g.resize_strip_ok && g.resize_span <= kResizeSrcRows) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
-      k_resize_staged<<<grid, block, kResizeStageBytes, s>>>(g, b.pyr, b.taps, l);
+      k_resize_staged<<<grid, block, kResizeStageBytes, s>>>(g, pv, b.taps, l);
     } else if (g.resize_strip_ok) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
-      k_resize_strip<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
+      k_resize_strip<<<grid, block, 0, s>>>(g, pv, b.taps, l);
     } else {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 7) / 8, n_img), block(32, 8);
-      k_resize<<<grid, block, 0, s>>>(g, b.pyr, b.taps, l);
+      k_resize<<<grid, block, 0, s>>>(g, pv, b.taps, l);
     }
     ++*launches;
   }
@@ -289,7 +292,7 @@ static_assert(sizeof(FastWarpSmem) % 16 == 0, "warp slices stay 16-byte aligned"
 static_assert(kFastIH * kFastIP >= 4 * ((kFastTH + 1) / 2) * ((kFastTW + 1) / 2), "kept keys (NMS maxima: at most one pixel in four) fit over the image rows");
 
 __global__ void __launch_bounds__(kFastWarps * 32, 8)
-k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ ftab,
+k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __restrict__ ftab,
        uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
   extern __shared__ __align__(128) uint8_t s_fast[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -302,7 +305,7 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
   const int x0 = kFastOrigin + (int)(te & 0xfff) * kFastTW, y0 = kFastOrigin + (int)((te >> 12) & 0xfff) * kFastTH;
   const int astart = (x0 - 8) & ~15;
   const int pitch = L.pitch, lw = L.w, lh = L.h;
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off + (size_t)(y0 - 4) * pitch + astart;
+  const uint8_t* src = pv.level(g, img, level) + (size_t)(y0 - 4) * pitch + astart;
 
   // (1) rows y0-4 .. y0+TH+3, columns astart .. astart+143, clipped to the level buffer.  Bytes outside the level
   //     are never read for a pixel that can become a candidate
@@ -456,7 +459,7 @@ k_fast(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const
 void launch_fast(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   if (g.total_ftiles == 0) return;
   dim3 grid((g.total_ftiles + kFastWarps - 1) / kFastWarps, n_img);
-  k_fast<<<grid, kFastWarps * 32, kFastWarps * sizeof(FastWarpSmem), s>>>(g, b.pyr, b.ftab, b.cand_key, b.cand_cnt, b.hist);
+  k_fast<<<grid, kFastWarps * 32, kFastWarps * sizeof(FastWarpSmem), s>>>(g, pyr_view(b), b.ftab, b.cand_key, b.cand_cnt, b.hist);
   ++*launches;
 }
 
@@ -545,7 +548,7 @@ __device__ __forceinline__ void warp_select_bin(const uint32_t* hist, uint32_t k
 #define RPE_SEL_MINB 2
 #endif
 __global__ void __launch_bounds__(kSelThreads, RPE_SEL_MINB)
-k_select(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr,
+k_select(const __grid_constant__ OrbGeom g, const PyrView pv,
          const uint32_t* __restrict__ cand_key, const uint32_t* __restrict__ cand_cnt,
          const uint32_t* __restrict__ hist, uint32_t* __restrict__ sel_key, float* __restrict__ sel_resp,
          uint32_t* __restrict__ lvl_key, float* __restrict__ lvl_resp, uint32_t* __restrict__ lvl_cnt,
@@ -560,7 +563,7 @@ k_select(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr,
   const uint32_t n = min(raw, (uint32_t)L.cand_cap);
   if (raw > (uint32_t)L.cand_cap && tid == 0) atomicOr(&img_flags[img], 1u);
   const uint32_t quota = (uint32_t)L.quota;
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
+  const uint8_t* src = pv.level(g, img, level);
   const uint32_t* ck = cand_key + (size_t)img * g.cand_stride + L.cand_off;
   uint32_t* sk = sel_key + (size_t)img * g.cand_stride + L.cand_off;
   float* sr = sel_resp + (size_t)img * g.cand_stride + L.cand_off;
@@ -662,7 +665,7 @@ k_select(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr,
 
 void launch_select(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   dim3 grid(g.nlevels, n_img);
-  k_select<<<grid, kSelThreads, (size_t)g.sort_cap * 8, s>>>(g, b.pyr, b.cand_key, b.cand_cnt, b.hist, b.sel_key,
+  k_select<<<grid, kSelThreads, (size_t)g.sort_cap * 8, s>>>(g, pyr_view(b), b.cand_key, b.cand_cnt, b.hist, b.sel_key,
                                                              b.sel_resp, b.lvl_key, b.lvl_resp, b.lvl_cnt,
                                                              b.img_flags);
   ++*launches;
@@ -728,7 +731,7 @@ __device__ __forceinline__ void blur_rows_x2(const uint8_t* rowA, const uint8_t*
 }
 
 __global__ void __launch_bounds__(128, 4)
-k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
+k_blur(const __grid_constant__ OrbGeom g, const PyrView pv, uint8_t* __restrict__ blur,
        const uint32_t* __restrict__ btab) {
   extern __shared__ __align__(128) uint8_t s_blur[];
   __shared__ __align__(8) uint64_t s_bar[4];
@@ -741,7 +744,7 @@ k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8
   const int x0 = (int)(e & 0xfff) * 128;
   const int yA = (int)((e >> 12) & 0xfff) * (2 * kBlurRows), yB = yA + kBlurRows;
   const int nA = min(kBlurRows, h - yA), nB = min(kBlurRows, h - yB);   // nB may be <= 0: strip B idle
-  const uint8_t* src = pyr + (size_t)img * g.pyr_stride + L.off;
+  const uint8_t* src = pv.level(g, img, (int)(e >> 24));
   uint8_t* sA = s_blur + warp * kBlurWarpBytes;
   uint8_t* sB = sA + kBlurSR * kBlurSP;
   uint64_t* bar = &s_bar[warp];
@@ -816,7 +819,7 @@ k_blur(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, uint8
 void launch_blur(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   if (g.total_bitems == 0) return;
   dim3 grid((g.total_bitems + 3) / 4, n_img);
-  k_blur<<<grid, 128, 4 * kBlurWarpBytes, s>>>(g, b.pyr, b.blur, b.btab);
+  k_blur<<<grid, 128, 4 * kBlurWarpBytes, s>>>(g, pyr_view(b), b.blur, b.btab);
   ++*launches;
 }
 
@@ -859,7 +862,7 @@ static void build_ori_table(uint2* tab) {
 }
 
 __global__ void __launch_bounds__(128)
-k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
+k_describe(const __grid_constant__ OrbGeom g, const PyrView pv, const uint8_t* __restrict__ blur,
            const uint32_t* __restrict__ lvl_key, const float* __restrict__ lvl_resp,
            const uint32_t* __restrict__ lvl_cnt, float* __restrict__ kp_x, float* __restrict__ kp_y,
            float* __restrict__ kp_size, float* __restrict__ kp_angle, float* __restrict__ kp_resp,
@@ -927,8 +930,8 @@ k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, c
       const LevelGeom& La = g.lv[s_level[k]];
       const LevelGeom& Lb = g.lv[s_level[kb]];
       const int xA = s_x[k], xB = s_x[kb];
-      const uint8_t* ca = pyr + (size_t)img * g.pyr_stride + La.off + (size_t)(s_y[k] - 15 + rsub) * La.pitch + ((xA - 15) & ~3) + 4 * w;
-      const uint8_t* cb = pyr + (size_t)img * g.pyr_stride + Lb.off + (size_t)(s_y[kb] - 15 + rsub) * Lb.pitch + ((xB - 15) & ~3) + 4 * w;
+      const uint8_t* ca = pv.level(g, img, s_level[k]) + (size_t)(s_y[k] - 15 + rsub) * La.pitch + ((xA - 15) & ~3) + 4 * w;
+      const uint8_t* cb = pv.level(g, img, s_level[kb]) + (size_t)(s_y[kb] - 15 + rsub) * Lb.pitch + ((xB - 15) & ~3) + 4 * w;
       const uint2* ta = kOriTab_dev + (((xA - 15) & 3) * 31 + rsub) * 10 + w;
       const uint2* tb = kOriTab_dev + (((xB - 15) & 3) * 31 + rsub) * 10 + w;
       int a10 = 0, a01 = 0, b10 = 0, b01 = 0;
@@ -975,49 +978,24 @@ k_describe(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ pyr, c
   // a warp only ever touches its own keypoints (k = warp, warp + 4, ...): warp-level synchronisation is enough, and
   // the four warps of the CTA drift through the phases independently
   __syncwarp();
-  // (3) descriptor.  The 256 steered tests of a keypoint gather 512 bytes from a 37 x 37 window of the blurred level
-  //     (pattern radius sqrt(13^2 + 13^2) = 18.4).  The warp first stages that window in shared memory with row-
-  //     contiguous word loads (37 rows x 11 aligned words), then gathers from there: straight from global memory a
-  //     gather instruction touched ~25 sectors and the kernel waited on them (ncu round 2: 41 % of the stall samples
-  //     on the compare that consumes the two bytes, l1tex at 68 %).  The next keypoint's window is in flight (in
-  //     registers) while the tests of the current one run.
-  constexpr int kWinR = 18, kWinRows = 2 * kWinR + 1, kWinWords = 11, kWinPitch = 4 * kWinWords;
-  constexpr int kWinLoads = (kWinRows * kWinWords + 31) / 32;
-  __shared__ __align__(16) uint8_t s_win[4][kWinRows * kWinPitch];
-  uint8_t* win = s_win[warp];
-  uint32_t wreg[kWinLoads];
-  auto fetch = [&](int k) {
-    const LevelGeom& L = g.lv[s_level[k]];
-    const uint8_t* base = blur + (size_t)img * g.pyr_stride + L.off + (size_t)(s_cy[k] - kWinR) * L.pitch +
-                          ((s_cx[k] - kWinR) & ~3);
-#pragma unroll
-    for (int i = 0; i < kWinLoads; ++i) {
-      const int idx = lane + 32 * i, r = idx / kWinWords, w = idx - r * kWinWords;
-      wreg[i] = idx < kWinRows * kWinWords ? __ldg(reinterpret_cast<const uint32_t*>(base + (size_t)r * L.pitch) + w) : 0u;
-    }
-  };
-  if (warp < nk) fetch(warp);
+  // (3) descriptor: lanes = descriptor bytes, 8 steered tests each, gathered straight from the blurred level.
+  //     (Staging the keypoint's 37 x 37 window in shared memory first - 13 row-contiguous word loads per lane, then
+  //     LDS gathers - was measured and lost: 2.02 ms against 1.87 ms for 512 images x 5000 keypoints; the extra
+  //     staging instructions and the lower occupancy, 80 registers, cost more than the scattered sectors.)
   for (int k = warp; k < nk; k += 4) {
-#pragma unroll
-    for (int i = 0; i < kWinLoads; ++i) {
-      const int idx = lane + 32 * i;
-      if (idx < kWinRows * kWinWords) reinterpret_cast<uint32_t*>(win)[idx] = wreg[i];   // (row r, word w) sits at word r * 11 + w
-    }
-    __syncwarp();
-    const uint8_t* c = win + kWinR * kWinPitch + kWinR + ((s_cx[k] - kWinR) & 3);          // the keypoint centre in the window
+    const LevelGeom& L = g.lv[s_level[k]];
+    const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];
     const float a = s_a[k], b = s_b[k];
-    if (k + 4 < nk) fetch(k + 4);
     uint32_t byte = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) byte |= brief_test(c, kWinPitch, a, b, pat[j]) << j;
+    for (int j = 0; j < 8; ++j) byte |= brief_test(c, L.pitch, a, b, pat[j]) << j;
     desc[((size_t)img * g.kp_stride + i0 + k) * 32 + lane] = (uint8_t)byte;
-    __syncwarp();
   }
 }
 
 void launch_describe(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
   dim3 grid((g.kp_stride + kDescKp - 1) / kDescKp, n_img);
-  k_describe<<<grid, 128, 0, s>>>(g, b.pyr, b.blur, b.lvl_key, b.lvl_resp, b.lvl_cnt, b.kp_x, b.kp_y, b.kp_size,
+  k_describe<<<grid, 128, 0, s>>>(g, pyr_view(b), b.blur, b.lvl_key, b.lvl_resp, b.lvl_cnt, b.kp_x, b.kp_y, b.kp_size,
                                   b.kp_angle, b.kp_resp, b.kp_oct, b.desc, b.kp_n);
   ++*launches;
 }

@@ -55,8 +55,24 @@ constexpr int kFastTH = 14;     // 16 score rows = two bands of 8 (k_fast: one w
 constexpr int kBlurRows = 32;    // blur work item = 128 columns x two strips of kBlurRows rows (one warp)
 constexpr int kFastOrigin = 24;  // FAST tiles start at x = y = 24 (a multiple of 4): only scores in [30, size-30) can matter
 
+// Where the pyramid levels of image slot `img` live: level l >= 1 inside the handle's pyramid slab; level 0 there too
+// (copied in by the upload), or - when the caller's device buffer already has the pyramid's row pitch and 16-byte
+// alignment - in the caller's buffer itself (lvl0 != nullptr: no copy at all).
+struct PyrView {
+  uint8_t* pyr;
+  const uint8_t* lvl0;
+  size_t lvl0_stride;
+#if defined(__CUDACC__)
+  __device__ __forceinline__ const uint8_t* level(const OrbGeom& g, int img, int l) const {
+    return (l == 0 && lvl0 != nullptr) ? lvl0 + (size_t)img * lvl0_stride : pyr + (size_t)img * g.pyr_stride + g.lv[l].off;
+  }
+#endif
+};
+
 struct OrbBuffers {
   uint8_t* pyr;
+  const uint8_t* lvl0;     // see PyrView
+  size_t lvl0_stride;
   uint8_t* blur;
   uint32_t* cand_key;
   uint32_t* cand_cnt;

@@ -238,3 +238,49 @@ def test_estimate_from_matches_batch_and_hard_ransac():
             assert abs(int(out["info"][i, 1]) - n_cv) <= 2
     finally:
         eng.close()
+
+
+def test_device_resident_frames_are_used_in_place_or_copied_with_identical_results():
+    """rpe_estimate_batch_device / rpe_estimate_sequence_device: frames whose device layout already is the pyramid's
+    (pitch = align16(W), 16-byte aligned) serve as level 0 in place (no copy); any other pitch / alignment is copied.
+    Same bits either way, and the same as the host-buffer call; the caller's buffer is not modified."""
+    import torch
+    import rpe_b200
+    from rpe_b200 import _lib as L
+    a, b, c = load_gray("sim_000000.png"), load_gray("sim_000015.png"), load_gray("sim_000030.png")
+    K = default_K()
+    H, W = a.shape
+    frames = np.ascontiguousarray(np.stack([a, b, b, c]))
+    eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=W, max_height=H, max_pairs=3))
+    try:
+        want = eng.estimate_batch_interleaved(frames, K)
+        assert (want["status"] == 0).all()
+        want_seq = eng.estimate_sequence(np.ascontiguousarray(np.stack([a, b, c])), K)
+        dev = torch.from_numpy(frames).cuda()
+        keep = dev.clone()
+        got = eng.estimate_batch_device(dev.data_ptr(), H * W, 2, H, W, W, K)                   # in place
+        lvl0 = eng.get_stage(1, 1, L.STAGE_PYRAMID_LEVEL, 0, np.uint8, nbytes=H * W).reshape(H, W)
+        assert np.array_equal(lvl0, c)
+        lvl1 = eng.get_stage(0, 0, L.STAGE_PYRAMID_LEVEL, 1, np.uint8, nbytes=H * W)
+        host1 = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=W, max_height=H, max_pairs=1))
+        try:
+            host1.estimate_batch([a], [b], K)
+            assert np.array_equal(lvl1, host1.get_stage(0, 0, L.STAGE_PYRAMID_LEVEL, 1, np.uint8, nbytes=H * W))
+        finally:
+            host1.close()
+        wide = torch.zeros((4, H, W + 16), dtype=torch.uint8, device="cuda")                     # other pitch: copied
+        wide[:, :, :W] = dev
+        got_wide = eng.estimate_batch_device(wide.data_ptr(), H * (W + 16), 2, H, W, W + 16, K)
+        raw = torch.zeros(4 * H * W + 64, dtype=torch.uint8, device="cuda")                       # unaligned base: copied
+        raw[4:4 + 4 * H * W] = dev.reshape(-1)
+        got_off = eng.estimate_batch_device(raw.data_ptr() + 4, H * W, 2, H, W, W, K)
+        for g in (got, got_wide, got_off):
+            for k in ("R", "t", "euler", "status", "info"):
+                assert np.array_equal(g[k], want[k]), k
+        seq = torch.from_numpy(np.ascontiguousarray(np.stack([a, b, c]))).cuda()
+        got_seq = eng.estimate_sequence_device(seq.data_ptr(), H * W, 3, H, W, W, K)
+        for k in ("R", "t", "euler", "status", "info"):
+            assert np.array_equal(got_seq[k], want_seq[k]), k
+        assert torch.equal(dev, keep)
+    finally:
+        eng.close()
