@@ -112,13 +112,16 @@ k_ransac_solve(const int32_t* __restrict__ m_n, int mcap, const double* __restri
   for (int i = tid; i < nh * 5; i += kRansacThreads) S.subset[i / 5][i % 5] = sub[i];
   __syncthreads();
   // (b) minimal solver, one hypothesis per thread
+  RPE_ASSERT(chunk < kMaxChunks && st.nh <= sr_cap && M >= 5 && M <= mcap);
   if (tid < nh) {
     double x1[10], x2[10];
     for (int k = 0; k < 5; ++k) {
+      RPE_ASSERT(S.subset[tid][k] >= 0 && S.subset[tid][k] < M);
       const double4 p = P[S.subset[tid][k]];
       x1[2 * k] = p.x; x1[2 * k + 1] = p.y; x2[2 * k] = p.z; x2[2 * k + 1] = p.w;
     }
     S.nmodels[tid] = five_point_solve(x1, x2, &S.models[tid][0][0]);
+    RPE_ASSERT(S.nmodels[tid] >= 0 && S.nmodels[tid] <= 10);
   }
   __syncthreads();
   // (c) Sampson scoring, one model per warp
@@ -189,6 +192,7 @@ k_ransac_replay(const int32_t* __restrict__ m_n, int n_pairs, RansacParams rp, R
     if (n > kCandCap) st.overflow = 1;
     for (int i = 0; i < min(n, kCandCap); ++i) {
       const int h = in[i].h;
+      RPE_ASSERT(h >= c * kChunk && h < min((c + 1) * kChunk, st.nh) && in[i].count <= M && h >= last_h);
       if (h != last_h && st.it0 + h >= st.niters) { stop = true; break; }   // (models of one hypothesis are all visited)
       last_h = h;
       const int cnt = in[i].count;

@@ -77,6 +77,7 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
     __syncthreads();
     if (!kTop2 && t0 > tbeg && tid < kTrainTile) {           // flush the previous tile's column minima
       const uint32_t v = s_col[tid];
+      RPE_ASSERT(t0 - kTrainTile + tid >= 0 && t0 - kTrainTile + tid < nt_all && (v == 0xffffffffu || (int)(v & 0xfffffu) < nq));
       if (v != 0xffffffffu) atomicMin(&bwd1[(size_t)pair * kp_stride + t0 - kTrainTile + tid], v);
     }
     if (!kTop2) s_col[tid] = 0xffffffffu;
@@ -143,6 +144,7 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
           const uint32_t c = __reduce_min_sync(0xffffffffu, min(r0 + (uint32_t)(dq0 - j), r1 + (uint32_t)(dq1 - j)));
           if (lane == ((j - jb) & 31)) mine = c;
         }
+        RPE_ASSERT(jb + 31 < kTrainTile || jb + lane >= tn || jb + lane < kTrainTile);
         if (jb + lane < tn) atomicMin(&s_col[jb + lane], mine);
       }
     }
@@ -157,6 +159,7 @@ k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, in
 #pragma unroll
   for (int k = 0; k < kQPT; ++k) {
     const int qq = q0 + tid + k * kMatchThreads;
+    RPE_ASSERT(nq <= kp_stride && nt_all <= kp_stride && (best1[k] == 0xffffffffu || (int)(best1[k] & 0xfffffu) < nt_all));
     if (qq < nq) {
       if (nsplit > 1) {
         // outputs preset to 0xffffffff.  Every key except the overall minimum loses one atomicMin on o1 (as
@@ -275,6 +278,7 @@ k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, 
     const bool keep = valid && (d < cut || (at_cut && rank < take));
     if (keep) {
       const uint32_t j = atomicAdd(&s_n, 1u);
+      RPE_ASSERT(j < (uint32_t)sort_cap);      // limit <= mcap <= sort_cap, and at most `limit` keys are kept
       if (j < (uint32_t)sort_cap) s_keys[j] = k;
     }
     __syncthreads();
@@ -309,6 +313,7 @@ k_build_matches(const float* __restrict__ kp_x, const float* __restrict__ kp_y, 
     const uint32_t k = s_keys[i];
     const int q = k & 0xfffffu, d = k >> 20;
     const int t = f1[q] & 0xfffffu;
+    RPE_ASSERT(q < n1 && t < n2 && i < (uint32_t)mcap);
     const size_t o = (size_t)pair * mcap + i;
     m_q[o] = q; m_t[o] = t; m_d[o] = d;
     pts1[2 * o] = x1[q]; pts1[2 * o + 1] = y1[q];

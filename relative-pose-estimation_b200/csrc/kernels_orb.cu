@@ -209,6 +209,7 @@ k_resize_staged(const __grid_constant__ OrbGeom g, const PyrView pv, const int2*
     if (y_first + j < y_end) {
       uint32_t hA[4], hB[4];
       const int rel = tys[j].x - ra0;
+      RPE_ASSERT(rel >= 0 && rel + 1 < kResizeSrcRows && n_src <= kResizeSrcRows);
       hpass(rel, hA);
       hpass(rel + 1, hB);
       const uint32_t cy1 = (uint32_t)tys[j].y, cy0 = 256u - cy1;
@@ -317,6 +318,8 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
     mbar_arrive_expect_tx(&S.bar, row_bytes * (uint32_t)n_rows);
   }
   __syncwarp();
+  RPE_ASSERT(level < g.nlevels && n_rows > 0 && row_bytes > 0 && row_bytes % 16 == 0 && y0 - 4 >= 0 && astart >= 0 &&
+             astart + (int)row_bytes <= pitch && (x0 - 4 - astart == 4 || x0 - 4 - astart == 12));
   if (lane < n_rows) bulk_copy_g2s(S.img + lane * kFastIP, src + (size_t)lane * pitch, row_bytes, &S.bar);
   static_assert(kFastIH <= 32, "one staged row per lane");
 #pragma unroll
@@ -372,6 +375,7 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
       while (bits) {
         const int p = 31 - __clz(bits);                      // bit p: pixel p >> 3 of the quad, row 8 b + 7 - (p & 7)
         bits ^= 1u << p;
+        RPE_ASSERT(out >= S.queue && out < S.queue + kFastQueue);
         *out++ = (uint16_t)(((8 * b + 7 - (p & 7)) << 7) | (4 * lane + (p >> 3)));
       }
     }
@@ -387,6 +391,8 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
       int e = 0, sc = 0;
       if (i < total) {
         e = S.queue[i];
+        RPE_ASSERT(e < kFastSH * kFastSP && ((e >> 7) + 6) * kFastIP + ib + (e & 127) + 3 < kFastIH * kFastIP &&
+                   (e >> 7) + 6 < n_rows);
         sc = fast9_score(&S.img[((e >> 7) + 3) * kFastIP + ib + (e & 127)], kFastIP, thr);
       }
       const uint32_t bal = __ballot_sync(0xffffffffu, sc > 0);
@@ -410,7 +416,11 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
     const int s = p[0];
     const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
                       s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
-    if (keep) keep_keys[atomicAdd(&S.n_keep, 1u)] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+    if (keep) {
+      const uint32_t slot = atomicAdd(&S.n_keep, 1u);
+      RPE_ASSERT(4 * (slot + 1) <= (uint32_t)(kFastIH * kFastIP) && e - kFastSP - 1 >= 0 && e + kFastSP + 1 < kFastSH * kFastSP);
+      keep_keys[slot] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+    }
   };
 
   int all = 0;
@@ -451,6 +461,7 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
   base = __shfl_sync(0xffffffffu, base, 0);
   for (uint32_t i = lane; i < n_keep; i += 32) {
     const uint32_t key = keep_keys[i];
+    RPE_ASSERT((key & 0xfff) < (uint32_t)lw && ((key >> 12) & 0xfff) < (uint32_t)lh && (key >> 24) > 0);
     if (base + i < cap) out_key[base + i] = key;
     atomicAdd(&hst[key >> 24], 1u);
   }
@@ -762,6 +773,7 @@ k_blur(const __grid_constant__ OrbGeom g, const PyrView pv, uint8_t* __restrict_
     const bool isB = r >= rowsA;
     const int rr = isB ? r - rowsA : r;
     const int sy = min(max(reflect101((isB ? yB : yA) - 3 + rr, h), 0), h - 1);
+    RPE_ASSERT(rr < kBlurSR && gx0 - (x0 - 16) >= 0 && gx0 - (x0 - 16) + (int)rb <= kBlurSP && rb % 16 == 0 && gx1 <= pitch);
     bulk_copy_g2s((isB ? sB : sA) + rr * kBlurSP + (gx0 - (x0 - 16)), src + (size_t)sy * pitch + gx0, rb, bar);
   }
   mbar_wait(bar, 0);
@@ -985,6 +997,7 @@ k_describe(const __grid_constant__ OrbGeom g, const PyrView pv, const uint8_t* _
   for (int k = warp; k < nk; k += 4) {
     const LevelGeom& L = g.lv[s_level[k]];
     const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];
+    RPE_ASSERT(s_cx[k] >= 19 && s_cx[k] < L.w - 19 && s_cy[k] >= 19 && s_cy[k] < L.h - 19);   // pattern radius 18.4
     const float a = s_a[k], b = s_b[k];
     uint32_t byte = 0;
 #pragma unroll

@@ -19,6 +19,17 @@
 #include <stdint.h>
 #include "../../include/rpe.h"
 
+// Checked build (-DRPE_CHECKED=1; python relative-pose-estimation_b200/build.py with RPE_LIB_VARIANT=checked
+// RPE_EXTRA_DEFS=-DRPE_CHECKED=1): device-side assertions on every hand-computed shared-memory / global index of the
+// kernels.  compute-sanitizer is closed on the GPU pool (profiles/r02_compute_sanitizer_closed.txt), so the GPU test
+// suite is run once against this variant instead; a violated assertion traps the kernel and fails the test.
+#if defined(RPE_CHECKED) && defined(__CUDACC__)
+#include <cassert>
+#define RPE_ASSERT(c) assert(c)
+#else
+#define RPE_ASSERT(c) ((void)0)
+#endif
+
 namespace rpe {
 
 struct LevelGeom {

@@ -1,6 +1,6 @@
 #!/bin/bash
 # One GPU-box visit: parity tests, smoke, bench (+ A/B legs), pipe rates, optional sanitizer / ncu captures.
-# usage: bash tools/gpu_trip.sh [tests] [bench] [ab] [rates] [sanitize] [ncu] [cfg2]
+# usage: bash tools/gpu_trip.sh [tests|tests_all] [checked] [smoke] [bench] [rates] [sanitize] [ncu] [cfg2]
 mkdir -p gpurun_out
 for what in "$@"; do
   case "$what" in
@@ -8,15 +8,16 @@ for what in "$@"; do
       timeout 1500 python -m pytest tests -m gpu -q -x --durations=8 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -25 gpurun_out/pytest_gpu.log ;;
     tests_all)
       timeout 1800 python -m pytest tests -m gpu -q --durations=8 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -40 gpurun_out/pytest_gpu.log ;;
+    checked)
+      # the GPU suite against the checked build (device-side assertions on every hand-computed index; stands in for
+      # compute-sanitizer, which is closed on this pool)
+      RPE_LIB_VARIANT=checked RPE_EXTRA_DEFS=-DRPE_CHECKED=1 timeout 1800 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu_checked.log 2>&1; echo "checked pytest rc=$?"; tail -6 gpurun_out/pytest_gpu_checked.log
+      RPE_LIB_VARIANT=checked RPE_EXTRA_DEFS=-DRPE_CHECKED=1 timeout 600 python tools/sanitize_target.py > gpurun_out/checked_target.log 2>&1; echo "checked target rc=$?"; tail -2 gpurun_out/checked_target.log ;;
     smoke)
       timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log ;;
     bench)
       timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -3 gpurun_out/bench.err
       python tools/show_bench.py gpurun_out/bench.json ;;
-    ab)
-      for v in "" "RPE_FAST_V1=1"; do
-        env $v timeout 300 python bench.py --no-cpu-baseline --lean > gpurun_out/bench_ab_${v:-new}.json 2> gpurun_out/bench_ab.err || tail -3 gpurun_out/bench_ab.err
-        echo "A/B ${v:-new}"; python tools/show_bench.py gpurun_out/bench_ab_${v:-new}.json; done ;;
     rates)
       timeout 120 tools/build/pipe_rates > gpurun_out/pipe_rates.json; cat gpurun_out/pipe_rates.json ;;
     sanitize)
