@@ -327,6 +327,7 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out) {
     A(dalloc(h, &gb.rinfo, NP * 4));
     A(dalloc(h, &gb.rstate, NP)); A(dalloc(h, &gb.rsubsets, NP * kRansacSuperRoundCap * 5));
     A(dalloc(h, &gb.rcands, NP * kRansacCandPerPair)); A(dalloc(h, &gb.rncand, NP * 8));
+    A(dalloc(h, &gb.rmodels, NP * kRansacSuperRoundCap * 90)); A(dalloc(h, &gb.rnm, NP * kRansacSuperRoundCap));
     A(dalloc(h, &gb.R, NP * 9)); A(dalloc(h, &gb.t, NP * 3)); A(dalloc(h, &gb.euler, NP * 3));
     A(dalloc(h, &gb.pose_cnt, NP)); A(dalloc(h, &gb.status, NP));
     A(dalloc(h, &h->dK[k], 9));
@@ -468,6 +469,7 @@ static GeomBuffers geom_view(const rpe_handle* h, int set, int pair0) {
   const size_t p = (size_t)pair0, MC = h->mcap;
   g.npts += p * MC * 4; g.E += p * 9; g.rmask += p * MC; g.pmask += p * MC; g.rinfo += p * 4;
   g.rstate += p; g.rsubsets += p * kRansacSuperRoundCap * 5; g.rcands += p * kRansacCandPerPair; g.rncand += p * 8;
+  g.rmodels += p * kRansacSuperRoundCap * 90; g.rnm += p * kRansacSuperRoundCap;
   g.R += p * 9; g.t += p * 3; g.euler += p * 3; g.pose_cnt += p; g.status += p;
   g.tr_subset = nullptr;
   return g;

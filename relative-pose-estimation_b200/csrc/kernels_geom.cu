@@ -38,15 +38,16 @@ void launch_normalize(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, i
 // RANSAC over a batch, hypotheses in parallel ACROSS CTAs.  OpenCV's loop is sequential (strict ">" best update,
 // adaptive iteration count); here it advances in super-rounds:
 //   k_ransac_begin   thread per pair: state (cv2's RNG seed, niters = maxIters), subsets of the first, small round
-//   k_ransac_solve   CTA per (chunk of kChunk hypotheses, pair): minimal solver one hypothesis per thread, Sampson
-//                    scoring one model per warp, then the chunk's PREFIX MAXIMA (the models whose inlier count beats
-//                    everything before them in the chunk and the best held at the start of the super-round): only
-//                    those can ever win the sequential update, so only they (<= kCandCap, with their E) go to HBM
+//   k_ransac_solve   CTA per (chunk of kChunk hypotheses, pair): minimal solver, one hypothesis per thread -> models
+//   k_ransac_score   CTA per (chunk, pair): Sampson scoring one model per warp, then the chunk's PREFIX MAXIMA (the
+//                    models whose inlier count beats everything before them in the chunk and the best held at the
+//                    start of the super-round): only those can ever win the sequential update, so only they
+//                    (<= kCandCap, with their E) are handed to the replay
 //   k_ransac_replay  thread per pair: cv2's sequential rule replayed over the chunks' prefix maxima in hypothesis
 //                    order (stop where cv2 stops: it0 + h >= niters), then the next super-round's subsets from the
 //                    pair's RNG stream
 //   k_ransac_finish  CTA per pair: inlier mask of the held model, E, rinfo
-// [solve, replay] is enqueued a fixed number of times (enough for maxIters); CTAs of finished pairs, and chunks past
+// [solve, score, replay] is enqueued a fixed number of times (enough for maxIters); CTAs of finished pairs, and chunks past
 // the iterations still needed, return at once.  Same RNG stream, exactly the drawn subsets consumed in order, same
 // update rule => the same stop iteration and the same held model as the one-CTA-per-pair loop of round 1, whatever
 // the chunking.  What changes is latency: a pair that needs 1000 iterations (the reference's simulator frames) takes
@@ -57,15 +58,8 @@ constexpr int kChunk = 64;                      // hypotheses per solve CTA
 constexpr int kFirstRound = 16;                 // the first round is small: it brings niters down for an easy pair
 constexpr int kMaxChunks = 8;                   // chunks per pair and super-round
 constexpr int kCandCap = 32;                    // prefix maxima kept per chunk
-constexpr int kRansacThreads = 128;
-static_assert(kRansacThreads >= kChunk && kRansacThreads % 32 == 0, "one solver thread per hypothesis of a chunk");
-
-struct RansacShared {
-  double models[kChunk][10][9];
-  int nmodels[kChunk];
-  int counts[kChunk][10];
-  int subset[kChunk][5];
-};
+constexpr int kScoreThreads = 256;              // k_ransac_score / k_ransac_finish
+constexpr int kRansacThreads = kScoreThreads;
 
 __global__ void __launch_bounds__(128)
 k_ransac_begin(const int32_t* __restrict__ m_n, int n_pairs, RansacParams rp, RansacState* __restrict__ state,
@@ -89,13 +83,45 @@ k_ransac_begin(const int32_t* __restrict__ m_n, int n_pairs, RansacParams rp, Ra
   state[pair] = st;
 }
 
-__global__ void __launch_bounds__(kRansacThreads)
-k_ransac_solve(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npts, const double* __restrict__ K,
+// One thread = one hypothesis; 64 threads per CTA and nothing in shared memory, so that four CTAs (eight solver
+// warps) share an SM: the solver is a long dependent FP64 chain (Durand-Kerner), bound by latency, not by the pipe.
+// Models go to HBM (<= 10 x 9 doubles per hypothesis) for k_ransac_score.
+__global__ void __launch_bounds__(kChunk)
+k_ransac_solve(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npts,
+               const RansacState* __restrict__ state, const int32_t* __restrict__ subsets, int sr_cap,
+               double* __restrict__ gmodels, int32_t* __restrict__ gnm) {
+  const int pair = blockIdx.y, chunk = blockIdx.x, tid = threadIdx.x;
+  const RansacState& st = state[pair];
+  if (st.done) return;
+  const int h0 = chunk * kChunk;
+  if (h0 + tid >= st.nh) return;
+  const int M = m_n[pair];
+  RPE_ASSERT(chunk < kMaxChunks && st.nh <= sr_cap && M >= 5 && M <= mcap);
+  const double4* P = reinterpret_cast<const double4*>(npts) + (size_t)pair * mcap;
+  const int32_t* sub = subsets + ((size_t)pair * sr_cap + h0 + tid) * 5;
+  double x1[10], x2[10];
+  for (int k = 0; k < 5; ++k) {
+    const int idx = sub[k];
+    RPE_ASSERT(idx >= 0 && idx < M);
+    const double4 p = P[idx];
+    x1[2 * k] = p.x; x1[2 * k + 1] = p.y; x2[2 * k] = p.z; x2[2 * k + 1] = p.w;
+  }
+  const size_t slot = ((size_t)pair * kMaxChunks + chunk) * kChunk + tid;
+  const int nm = five_point_solve(x1, x2, gmodels + slot * 90);
+  RPE_ASSERT(nm >= 0 && nm <= 10);
+  gnm[slot] = nm;
+}
+
+// Sampson scoring of a chunk's models, one model per warp (eight warps, few registers: the FP64 pipe is the bound
+// here and many warps keep it busy), then the chunk's prefix maxima.
+__global__ void __launch_bounds__(kScoreThreads)
+k_ransac_score(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npts, const double* __restrict__ K,
                RansacParams rp, const RansacState* __restrict__ state, const int32_t* __restrict__ subsets, int sr_cap,
-               RansacCand* __restrict__ cands, int32_t* __restrict__ n_cand, int32_t* tr_subset, int32_t* tr_nmodels,
-               int32_t* tr_counts, double* tr_models, int tr_cap) {
-  extern __shared__ __align__(16) unsigned char s_raw[];
-  RansacShared& S = *reinterpret_cast<RansacShared*>(s_raw);
+               const double* __restrict__ gmodels, const int32_t* __restrict__ gnm, RansacCand* __restrict__ cands,
+               int32_t* __restrict__ n_cand, int32_t* tr_subset, int32_t* tr_nmodels, int32_t* tr_counts,
+               double* tr_models, int tr_cap) {
+  __shared__ int s_nm[kChunk];
+  __shared__ int s_counts[kChunk][10];
   const int pair = blockIdx.y, chunk = blockIdx.x, tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   const RansacState& st = state[pair];
@@ -108,48 +134,36 @@ k_ransac_solve(const int32_t* __restrict__ m_n, int mcap, const double* __restri
   const double4* P = reinterpret_cast<const double4*>(npts) + (size_t)pair * mcap;
   const double thr = rp.threshold / ((K[0] + K[4]) * 0.5);
   const SampsonGate gate = sampson_gate((float)(thr * thr));
-  const int32_t* sub = subsets + ((size_t)pair * sr_cap + h0) * 5;
-  for (int i = tid; i < nh * 5; i += kRansacThreads) S.subset[i / 5][i % 5] = sub[i];
+  const size_t slot0 = ((size_t)pair * kMaxChunks + chunk) * kChunk;
+  if (tid < nh) s_nm[tid] = gnm[slot0 + tid];
   __syncthreads();
-  // (b) minimal solver, one hypothesis per thread
-  RPE_ASSERT(chunk < kMaxChunks && st.nh <= sr_cap && M >= 5 && M <= mcap);
-  if (tid < nh) {
-    double x1[10], x2[10];
-    for (int k = 0; k < 5; ++k) {
-      RPE_ASSERT(S.subset[tid][k] >= 0 && S.subset[tid][k] < M);
-      const double4 p = P[S.subset[tid][k]];
-      x1[2 * k] = p.x; x1[2 * k + 1] = p.y; x2[2 * k] = p.z; x2[2 * k + 1] = p.w;
-    }
-    S.nmodels[tid] = five_point_solve(x1, x2, &S.models[tid][0][0]);
-    RPE_ASSERT(S.nmodels[tid] >= 0 && S.nmodels[tid] <= 10);
-  }
-  __syncthreads();
-  // (c) Sampson scoring, one model per warp
-  for (int mi = warp; mi < nh * 10; mi += kRansacThreads / 32) {
+  for (int mi = warp; mi < nh * 10; mi += kScoreThreads / 32) {
     const int h = mi / 10, r = mi % 10;
-    if (r >= S.nmodels[h]) continue;
-    const double* E = S.models[h][r];
+    if (r >= s_nm[h]) continue;
+    double E[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) E[k] = gmodels[(slot0 + h) * 90 + r * 9 + k];
     int cnt = 0;
     for (int i = lane; i < M; i += 32) {
       const double4 p = P[i];
       cnt += sampson_is_inlier(E, p.x, p.y, p.z, p.w, gate) ? 1 : 0;
     }
     for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    if (lane == 0) S.counts[h][r] = cnt;
+    if (lane == 0) s_counts[h][r] = cnt;
   }
   __syncthreads();
-  // (d) prefix maxima of the chunk, in (hypothesis, model) order, above what the pair held when the super-round began
+  // prefix maxima of the chunk, in (hypothesis, model) order, above what the pair held when the super-round began
   if (tid == 0) {
     RansacCand* out = cands + ((size_t)pair * kMaxChunks + chunk) * kCandCap;
     int run = max(best0, 4), n = 0;
     for (int h = 0; h < nh; ++h)
-      for (int r = 0; r < S.nmodels[h]; ++r) {
-        const int c = S.counts[h][r];
+      for (int r = 0; r < s_nm[h]; ++r) {
+        const int c = s_counts[h][r];
         if (c > run) {
           run = c;
           if (n < kCandCap) {
             out[n].h = h0 + h; out[n].r = r; out[n].count = c; out[n].pad = 0;
-            for (int k = 0; k < 9; ++k) out[n].E[k] = S.models[h][r][k];
+            for (int k = 0; k < 9; ++k) out[n].E[k] = gmodels[(slot0 + h) * 90 + r * 9 + k];
           }
           ++n;
         }
@@ -157,14 +171,15 @@ k_ransac_solve(const int32_t* __restrict__ m_n, int mcap, const double* __restri
     n_cand[pair * kMaxChunks + chunk] = n;
   }
   if (tr_subset != nullptr && pair == 0) {
-    for (int i = tid; i < nh; i += kRansacThreads) {
+    const int32_t* sub = subsets + ((size_t)pair * sr_cap + h0) * 5;
+    for (int i = tid; i < nh; i += kScoreThreads) {
       const int g = it0 + h0 + i;
       if (g < tr_cap) {
-        tr_nmodels[g] = S.nmodels[i];
-        for (int k = 0; k < 5; ++k) tr_subset[g * 5 + k] = S.subset[i][k];
+        tr_nmodels[g] = s_nm[i];
+        for (int k = 0; k < 5; ++k) tr_subset[g * 5 + k] = sub[i * 5 + k];
         for (int r = 0; r < 10; ++r) {
-          tr_counts[g * 10 + r] = r < S.nmodels[i] ? S.counts[i][r] : -1;
-          for (int k = 0; k < 9; ++k) tr_models[(size_t)g * 90 + r * 9 + k] = r < S.nmodels[i] ? S.models[i][r][k] : 0.0;
+          tr_counts[g * 10 + r] = r < s_nm[i] ? s_counts[i][r] : -1;
+          for (int k = 0; k < 9; ++k) tr_models[(size_t)g * 90 + r * 9 + k] = r < s_nm[i] ? gmodels[(slot0 + i) * 90 + r * 9 + k] : 0.0;
         }
       }
     }
@@ -273,11 +288,12 @@ void launch_ransac(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int 
   const int rounds = 1 + (max(rp.max_iters - kFirstRound, 0) + chunks * kChunk - 1) / (chunks * kChunk);
   for (int r = 0; r < rounds; ++r) {
     dim3 grid(r == 0 ? 1 : chunks, n_pairs);
-    k_ransac_solve<<<grid, kRansacThreads, sizeof(RansacShared), s>>>(mb.m_n, mcap, gb.npts, dK, rp, gb.rstate, gb.rsubsets,
-                                                                      sr_cap, gb.rcands, gb.rncand, gb.tr_subset,
-                                                                      gb.tr_nmodels, gb.tr_counts, gb.tr_models, gb.tr_cap);
+    k_ransac_solve<<<grid, kChunk, 0, s>>>(mb.m_n, mcap, gb.npts, gb.rstate, gb.rsubsets, sr_cap, gb.rmodels, gb.rnm);
+    k_ransac_score<<<grid, kScoreThreads, 0, s>>>(mb.m_n, mcap, gb.npts, dK, rp, gb.rstate, gb.rsubsets, sr_cap, gb.rmodels,
+                                                  gb.rnm, gb.rcands, gb.rncand, gb.tr_subset, gb.tr_nmodels, gb.tr_counts,
+                                                  gb.tr_models, gb.tr_cap);
     k_ransac_replay<<<tb, 128, 0, s>>>(mb.m_n, n_pairs, rp, gb.rstate, gb.rsubsets, sr_cap, chunks, gb.rcands, gb.rncand);
-    *launches += 2;
+    *launches += 3;
   }
   k_ransac_finish<<<n_pairs, kRansacThreads, 0, s>>>(mb.m_n, mcap, gb.npts, dK, rp, gb.rstate, gb.E, gb.rmask, gb.rinfo);
   ++*launches;
@@ -366,9 +382,6 @@ void launch_pose(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_
   ++*launches;
 }
 
-int setup_geom_attributes() {
-  return (int)cudaFuncSetAttribute(k_ransac_solve, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)sizeof(RansacShared));
-}
+int setup_geom_attributes() { return 0; }
 
 }  // namespace rpe

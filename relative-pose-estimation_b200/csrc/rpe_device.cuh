@@ -135,6 +135,8 @@ struct GeomBuffers {
   int32_t* rsubsets;        // [NP][kMaxChunks * kChunk][5]
   RansacCand* rcands;       // [NP][kMaxChunks][kCandCap]
   int32_t* rncand;          // [NP][kMaxChunks]
+  double* rmodels;          // [NP][kMaxChunks * kChunk][10][9]  models of the super-round in flight
+  int32_t* rnm;             // [NP][kMaxChunks * kChunk]          models per hypothesis
   // optional per-hypothesis trace of pair 0 (stage entry point only)
   int32_t* tr_subset; int32_t* tr_nmodels; int32_t* tr_counts; double* tr_models; int32_t tr_cap;
 };
