@@ -158,6 +158,39 @@ def solve_poly_dk(coeffs: np.ndarray, max_iters: int = 300) -> np.ndarray:
     return roots
 
 
+def _cv_svd_fill_signs() -> np.ndarray:
+    """The 36 draws of cv::RNG(0x12345678) that OpenCV's JacobiSVDImpl_ turns into +-1 (bit 8 of each draw)."""
+    state, out = 0x12345678, []
+    for _ in range(36):
+        state = ((state & 0xFFFFFFFF) * 4164903690 + (state >> 32)) & 0xFFFFFFFFFFFFFFFF
+        out.append(1.0 if (state & 0xFFFFFFFF) & 256 else -1.0)
+    return np.array(out).reshape(4, 9)
+
+
+_SVD_FILL = _cv_svd_fill_signs()
+
+
+def cv2_null_space(Q: np.ndarray) -> np.ndarray:
+    """Rows 5..8 of Vt as cv2's five-point solver gets them from SVD::compute(Q, FULL_UV) on its 5 x 9 system.
+    OpenCV's HAL hands matrices this small to its own one-sided Jacobi SVD even in LAPACK builds, and that routine
+    FILLS the rows beyond the rank by Gram-Schmidt: row i = a fixed pseudo-random +-1/9 vector (RNG re-seeded with
+    0x12345678 on every call), orthogonalised twice against all previous rows with an L1 rescale after every
+    projection, then normalised.  Only the row space of Q enters.  Verified against cv2.SVDecomp to 1e-15
+    (tests/test_oracle_geometry.py); this basis fixes the parametrisation E = x E1 + y E2 + z E3 + E4, hence the
+    order in which cv2.solvePoly returns the roots in z, hence the ORDER of the models of a hypothesis."""
+    eps = np.finfo(np.float64).eps * 10
+    rows = list(np.linalg.qr(Q.T, mode="complete")[0][:, :5].T)
+    for i in range(4):
+        v = _SVD_FILL[i] / 9.0
+        for _ in range(2):
+            for r in rows:
+                v = v - float(v @ r) * r
+                asum = np.abs(v).sum()
+                v = v * (1.0 / asum if asum > eps * 100 else 0.0)
+        rows.append(v / np.sqrt((v * v).sum()))
+    return np.array(rows[5:])
+
+
 def five_point_models(x1: np.ndarray, x2: np.ndarray, roots_fn=None) -> list[np.ndarray]:
     """All real essential matrices through 5 normalised correspondences (x2' E x1 = 0),
     each with ||E||_F = 1.  x1, x2: (5, 2) float64."""
@@ -171,8 +204,7 @@ def five_point_models(x1: np.ndarray, x2: np.ndarray, roots_fn=None) -> list[np.
     Q = np.stack([x2[:, 0] * x1[:, 0], x2[:, 0] * x1[:, 1], x2[:, 0],
                   x2[:, 1] * x1[:, 0], x2[:, 1] * x1[:, 1], x2[:, 1],
                   x1[:, 0], x1[:, 1], np.ones(5)], axis=1)
-    _, _, Vt = np.linalg.svd(Q, full_matrices=True)
-    basis = Vt[5:9]                                   # 4 x 9, rows = E1..E4 (row-major 3x3)
+    basis = cv2_null_space(Q)                         # 4 x 9, rows = E1..E4 (row-major 3x3)
     A = _constraint_matrix(basis)
     try:
         G = np.linalg.solve(A[:, :10], A[:, 10:])     # Gauss-Jordan of the first ten monomials
@@ -218,14 +250,18 @@ def five_point_models(x1: np.ndarray, x2: np.ndarray, roots_fn=None) -> list[np.
 
 
 def sampson_error_f32(E: np.ndarray, x1: np.ndarray, x2: np.ndarray) -> np.ndarray:
-    """EMEstimatorCallback::computeError: f64 Sampson distance stored as float32."""
-    n = x1.shape[0]
-    X1 = np.concatenate([x1, np.ones((n, 1))], axis=1)
-    X2 = np.concatenate([x2, np.ones((n, 1))], axis=1)
-    Ex1 = X1 @ E.T
-    Etx2 = X2 @ E
-    x2tEx1 = (X2 * Ex1).sum(axis=1)
-    den = Ex1[:, 0] ** 2 + Ex1[:, 1] ** 2 + Etx2[:, 0] ** 2 + Etx2[:, 1] ** 2
+    """EMEstimatorCallback::computeError: f64 Sampson distance stored as float32.  Every product and sum is rounded
+    on its own, in cv2's order (Matx row times vector left to right, the dot product, a + b + c + d): cv2 is built
+    without FMA contraction, and numpy's elementwise operations round the same way."""
+    E = np.asarray(E, dtype=np.float64).reshape(3, 3)
+    xa, ya, xb, yb = x1[:, 0], x1[:, 1], x2[:, 0], x2[:, 1]
+    Ex0 = (E[0, 0] * xa + E[0, 1] * ya) + E[0, 2]
+    Ex1 = (E[1, 0] * xa + E[1, 1] * ya) + E[1, 2]
+    Ex2 = (E[2, 0] * xa + E[2, 1] * ya) + E[2, 2]
+    Et0 = (E[0, 0] * xb + E[1, 0] * yb) + E[2, 0]
+    Et1 = (E[0, 1] * xb + E[1, 1] * yb) + E[2, 1]
+    x2tEx1 = (xb * Ex0 + yb * Ex1) + Ex2
+    den = ((Ex0 * Ex0 + Ex1 * Ex1) + Et0 * Et0) + Et1 * Et1
     with np.errstate(divide="ignore", invalid="ignore"):
         return (x2tEx1 * x2tEx1 / den).astype(np.float32)
 

@@ -219,13 +219,17 @@ RPE_HDN int five_point_solve(const double* x1, const double* x2, double* Eout) {
       return 1;
     }
   }
-  // --- 1. null space of the 5x9 epipolar system, in the SAME basis OpenCV gets from LAPACK.
-  // cv2 (built with LAPACK) calls dgesdd(FULL_UV) on the 5x9 matrix; for that shape dgesdd takes
-  // the "LQ first" path, so rows 5..8 of Vt are rows 5..8 of the full Householder Q of A = L Q.
-  // The essential-matrix parametrisation E = x N0 + y N1 + z N2 + N3 depends on this basis, and
-  // for near-degenerate samples (planar scenes) its conditioning does too: an arbitrary
-  // orthonormal basis moves the models by up to 1e-2, this one reproduces cv2's to ~1e-8
-  // (tests/test_kernel_math_host.py).  Householder reflectors exactly as dgelq2 / dlarfg.
+  // --- 1. null space of the 5x9 epipolar system, in the SAME basis cv2 uses.  The essential-matrix parametrisation
+  // E = x N0 + y N1 + z N2 + N3 depends on this basis, and so do (a) the conditioning of near-degenerate samples and
+  // (b) the ORDER in which the roots of the degree-10 polynomial in z come out of the root finder, i.e. the order of
+  // the models of a hypothesis, which decides RANSAC ties.  cv2 (also when built with LAPACK: its HAL hands matrices
+  // this small to OpenCV's own one-sided Jacobi SVD) does not return a LAPACK basis: JacobiSVDImpl_ computes the five
+  // right singular vectors and FILLS the remaining four rows of Vt by Gram-Schmidt: row i = a fixed pseudo-random
+  // vector of +-1/9 (cv::RNG seeded 0x12345678 on every call, bit 8 of each draw), orthogonalised twice against all
+  // previous rows with an L1 rescale after every projection, then normalised.  Only the ROW SPACE of the system
+  // enters (projections onto a subspace do not depend on its basis), so any orthonormal basis of it will do: rows
+  // 0..4 of the Householder Q of A = L Q (dgelq2 / dlarfg reflectors).  Verified against cv2.SVDecomp: 1e-15; and
+  // against cv2's five-point solver: same models in the same order (tests/test_kernel_math_host.py).
   double Rw[5][9], tau[5];
   for (int i = 0; i < 5; ++i) {
     const double a = x1[2 * i], b = x1[2 * i + 1], c = x2[2 * i], d = x2[2 * i + 1];
@@ -251,10 +255,10 @@ RPE_HDN int five_point_solve(const double* x1, const double* x2, double* Eout) {
       for (int k = i + 1; k < 9; ++k) Rw[r][k] -= w * Rw[i][k];
     }
   }
-  double N[4][9];
-  for (int m = 0; m < 4; ++m) {                           // row 5 + m of Q = e' H5 H4 H3 H2 H1
+  double Vt[9][9];                                        // rows 0..4: row space; rows 5..8: cv2's null-space basis
+  for (int m = 0; m < 5; ++m) {                           // row m of Q = e_m' H5 H4 H3 H2 H1
     double v[9];
-    for (int k = 0; k < 9; ++k) v[k] = (k == 5 + m) ? 1.0 : 0.0;
+    for (int k = 0; k < 9; ++k) v[k] = (k == m) ? 1.0 : 0.0;
     for (int i = 4; i >= 0; --i) {
       if (tau[i] == 0) continue;
       double w = v[i];
@@ -263,10 +267,35 @@ RPE_HDN int five_point_solve(const double* x1, const double* x2, double* Eout) {
       v[i] -= w;
       for (int k = i + 1; k < 9; ++k) v[k] -= w * Rw[i][k];
     }
-    double nn = 0;
-    for (int k = 0; k < 9; ++k) { N[m][k] = v[k]; nn += v[k] * v[k]; }
-    if (!(nn > 0.25)) return 0;                           // NaN / inf guard (rows of Q have norm 1)
+    for (int k = 0; k < 9; ++k) Vt[m][k] = v[k];
   }
+  for (int i = 5; i < 9; ++i) {
+    // the 36 draws of cv::RNG(0x12345678): bit k of kSign[i - 5] set = +1/9, clear = -1/9
+    const unsigned kSign[4] = {0x184u, 0x17du, 0x1b1u, 0x0e9u};
+    double v[9];
+    for (int k = 0; k < 9; ++k) v[k] = ((kSign[i - 5] >> k) & 1u) ? (1.0 / 9.0) : -(1.0 / 9.0);
+    for (int iter = 0; iter < 2; ++iter)
+      for (int j = 0; j < i; ++j) {
+        double sd = 0;
+        for (int k = 0; k < 9; ++k) sd += v[k] * Vt[j][k];
+        double asum = 0;
+        for (int k = 0; k < 9; ++k) {
+          const double t = v[k] - sd * Vt[j][k];
+          v[k] = t;
+          asum += fabs(t);
+        }
+        asum = asum > 2.220446049250313e-16 * 10 * 100 ? 1.0 / asum : 0.0;
+        for (int k = 0; k < 9; ++k) v[k] *= asum;
+      }
+    double nn = 0;
+    for (int k = 0; k < 9; ++k) nn += v[k] * v[k];
+    if (!(nn > 0)) return 0;                              // NaN / degenerate guard
+    nn = 1.0 / sqrt(nn);
+    for (int k = 0; k < 9; ++k) Vt[i][k] = v[k] * nn;
+  }
+  double N[4][9];
+  for (int m = 0; m < 4; ++m)
+    for (int k = 0; k < 9; ++k) N[m][k] = Vt[5 + m][k];
   // --- 2. constraint matrix A (10 x 20): det(E) = 0 and E E' E - tr(E E')/2 E = 0
   double e[9][4];
   for (int k = 0; k < 9; ++k)

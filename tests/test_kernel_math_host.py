@@ -186,9 +186,9 @@ def test_hamming_carry_save_forms_are_exact():
 
 
 def test_five_point_matches_cv2_minimal_solver():
-    """The kernel's five-point solver (LAPACK-path null basis, Gauss-Jordan, Durand-Kerner + Newton)
+    """The kernel's five-point solver (cv2's Jacobi-SVD null basis, Gauss-Jordan, Durand-Kerner + Newton)
     against cv2's OWN minimal solver — cv2.findEssentialMat called with exactly five points returns
-    all its roots stacked — on a generic 3-D scene: same model sets."""
+    all its roots stacked — on a generic 3-D scene: same models, same order."""
     import cv2
     rng = np.random.default_rng(3)
     K = np.array([[800., 0, 320], [0, 800, 240], [0, 0, 1]])
@@ -211,8 +211,8 @@ def test_five_point_matches_cv2_minimal_solver():
                                      prob=0.999, threshold=1.0)
         want = [] if Es is None else [Es[3 * i:3 * i + 3] for i in range(Es.shape[0] // 3)]
         got = [e.reshape(3, 3) for e in hc.five_point(x1[s], x2[s])]
-        ok = len(want) == len(got) and all(
-            min(min(np.abs(a - b).max(), np.abs(a + b).max()) for b in want) < 1e-5 for a in got)
+        # same models IN THE SAME ORDER (the order decides RANSAC ties between the models of one hypothesis)
+        ok = len(want) == len(got) and all(min(np.abs(a - b).max(), np.abs(a + b).max()) < 1e-5 for a, b in zip(got, want))
         bad += not ok
         for e in got:                              # every model really is an essential matrix through the sample
             assert np.abs(2 * e @ e.T @ e - np.trace(e @ e.T) * e).max() < 1e-6

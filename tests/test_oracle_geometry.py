@@ -147,3 +147,34 @@ def test_cv2_tie_order_is_rounding_noise():
                 swapped += 1
                 break
     assert swapped >= 30, swapped
+
+
+def test_null_space_basis_and_model_order_are_cv2s():
+    """cv2's five-point solver parametrises E over the null-space basis its (Jacobi) SVD returns, and the order of
+    the models of a hypothesis is the order in which cv2.solvePoly finds the roots of the polynomial in the third
+    coordinate.  The restatement reproduces the basis (vs cv2.SVDecomp) and therefore the ORDER of the models (vs
+    cv2.findEssentialMat on exactly five points, which returns all models stacked in its own order)."""
+    rng = np.random.default_rng(3)
+    K = np.array([[800., 0, 320], [0, 800, 240], [0, 0, 1]])
+    n = 300
+    X = np.c_[rng.uniform(-2, 2, n), rng.uniform(-1.5, 1.5, n), rng.uniform(3, 9, n)]
+    R, _ = cv2.Rodrigues(np.array([0.02, -0.03, 0.01]))
+    t = np.array([0.3, 0.05, 0.1])
+    p1 = X @ K.T; p1 = p1[:, :2] / p1[:, 2:]
+    X2 = X @ R.T + t
+    p2 = X2 @ K.T; p2 = p2[:, :2] / p2[:, 2:]
+    x1, x2 = og.normalize_points(p1, K), og.normalize_points(p2, K)
+    same = 0
+    trials = 40
+    for _ in range(trials):
+        s = rng.choice(n, 5, replace=False)
+        a, b = x1[s], x2[s]
+        Q = np.stack([b[:, 0] * a[:, 0], b[:, 0] * a[:, 1], b[:, 0], b[:, 1] * a[:, 0], b[:, 1] * a[:, 1], b[:, 1],
+                      a[:, 0], a[:, 1], np.ones(5)], axis=1)
+        _, _, vt = cv2.SVDecomp(Q, flags=cv2.SVD_FULL_UV)
+        assert np.abs(og.cv2_null_space(Q) - vt[5:9]).max() < 1e-12
+        Es, _ = cv2.findEssentialMat(a, b, np.eye(3), method=cv2.RANSAC, prob=0.999, threshold=1.0)
+        want = [] if Es is None else [Es[3 * i:3 * i + 3] for i in range(Es.shape[0] // 3)]
+        got = og.five_point_models(a, b)
+        same += len(got) == len(want) and all(min(np.abs(g - w).max(), np.abs(g + w).max()) < 1e-6 for g, w in zip(got, want))
+    assert same >= trials - 1, same       # (a complex pair within 1e-10 of the real axis may be kept by one and not the other)

@@ -1,14 +1,15 @@
-"""Why a config-3 pair can land just outside the pose tolerance although keypoints, matches and the hypothesis stream
-are identical to cv2's (round 2: pair 18 of rank 0's bench batch: 0.14 deg / 1.4 deg).
+"""Which model of a hypothesis wins a RANSAC tie?  (round 2: pair 18 of rank 0's config-3 bench batch landed 0.14 deg /
+1.4 deg from cv2 although keypoints, matches and the hypothesis stream were identical.)
 
 CPU only.  Replays OpenCV's RANSAC loop (oracle/geometry.py: same RNG, same update rule) on the pair's matched points
 three times - with cv2's OWN minimal solver (cv2.findEssentialMat on exactly five points returns all its models,
 stacked, in its own order), with the kernel's solver (tests/hostcheck instantiation) and with the numpy restatement -
-and prints the per-hypothesis inlier counts side by side.  The model SETS agree; the ORDER of the models of one
-hypothesis does not (cv2's order is the root order of its solvePoly call on a polynomial the restatement does not
-reproduce), which only matters when two models of ONE hypothesis tie in inlier count and both beat the best so far:
-pair 18, hypothesis 6: counts [492, 492, 418, 409, 165, 268] (cv2) vs [268, 165, 418, 492, 492, 409] - a near-double
-root, two essential matrices 0.015 apart with the same 492 inliers; cv2 keeps one, the engine the other.
+and prints the per-hypothesis inlier counts side by side.  Finding: the model SETS always agreed; the ORDER of the
+models of one hypothesis did not, because cv2 parametrises E over the null-space basis its Jacobi SVD fills in by
+Gram-Schmidt of fixed pseudo-random vectors (not a LAPACK basis), and the order in which cv2.solvePoly returns the
+roots depends on that parametrisation.  With two models of ONE hypothesis tied at 492 inliers (a near-double root)
+cv2 kept one and the engine the other.  Since the solver uses cv2's basis (geom_math.cuh, oracle.cv2_null_space) the
+three columns printed here are identical.
 
     python tools/diag_model_order.py [pair_index]
 """
