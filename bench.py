@@ -177,6 +177,18 @@ def direction_angle_deg(ta, tb):
     return float(np.degrees(np.arccos(np.clip(a @ b / (np.linalg.norm(a) * np.linalg.norm(b)), -1.0, 1.0))))
 
 
+def h2d_ceiling(world):
+    """Upload-only ceiling of this rank count on the 8-GPU box (tools/h2d_ceiling.py, committed under profiles/)."""
+    try:
+        for ln in open(os.path.join(ROOT, "profiles", "r02_h2d_ceiling.jsonl")):
+            d = json.loads(ln)
+            if d["ranks"] == world and not d["write_combined"]:
+                return d
+    except Exception:
+        pass
+    return None
+
+
 def measured_peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -426,9 +438,18 @@ def measure_pairs(ctx: Ctx, cfg, B, n_batches, steps, warmup, with_cpu, name):
     if with_cpu and ctx.world == 1 and ctx.rank == 0 and not args.no_cpu_baseline:
         from bench_support import cpu_arm
         cpu = cpu_arm.cpu_baseline(cfg, name, args.cpu_pairs if cfg["synth_cfg"] == 3 else 2, 8 if cfg["synth_cfg"] == 3 else 1)
+    e2e = {"value": total_pairs / (ms_e2e * 1e-3), "unit": "pairs/s", "h2d_bytes_per_step": int(2 * B * H * W + 72),
+           "d2h_bytes_per_step": int(B * (15 * 8 + 7 * 4)), "ms_per_step": ms_e2e / steps,
+           "h2d_gbs_per_rank": 2 * B * H * W / (ms_e2e / steps * 1e-3) / 1e9}
+    ceil = h2d_ceiling(ctx.world)
+    if ceil is not None:
+        bound = ceil["gbs_per_rank_min"] * 1e9 / (2 * H * W) * ctx.world        # pairs/s the slowest rank's upload allows
+        e2e["h2d_ceiling"] = {"gbs_per_rank_min": ceil["gbs_per_rank_min"], "gbs_aggregate": ceil["gbs_aggregate"],
+                              "upload_bound_pairs_per_s": bound, "e2e_frac_of_upload_bound": e2e["value"] / bound,
+                              "source": "tools/h2d_ceiling.py on the 8xB200 box, copies only, no kernels "
+                                        "(profiles/r02_h2d_ceiling.jsonl)"}
     return {"value": total_pairs / (ms_dev * 1e-3), "ms_per_step": ms_dev / steps,
-            "e2e": {"value": total_pairs / (ms_e2e * 1e-3), "unit": "pairs/s", "h2d_bytes_per_step": int(2 * B * H * W + 72),
-                    "d2h_bytes_per_step": int(B * (15 * 8 + 7 * 4)), "ms_per_step": ms_e2e / steps},
+            "e2e": e2e,
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "stages": stages,
             "run": {"distinct_batches_cycled": n_batches, "image_bytes_per_step": int(2 * B * H * W),
                     "l2_policy": f"inputs larger than L2 ({2 * B * H * W / 1e6:.0f} MB of frames + "
