@@ -13,6 +13,11 @@ for what in "$@"; do
       # compute-sanitizer, which is closed on this pool)
       RPE_LIB_VARIANT=checked RPE_EXTRA_DEFS=-DRPE_CHECKED=1 timeout 1800 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu_checked.log 2>&1; echo "checked pytest rc=$?"; tail -6 gpurun_out/pytest_gpu_checked.log
       RPE_LIB_VARIANT=checked RPE_EXTRA_DEFS=-DRPE_CHECKED=1 timeout 600 python tools/sanitize_target.py > gpurun_out/checked_target.log 2>&1; echo "checked target rc=$?"; tail -2 gpurun_out/checked_target.log ;;
+    match_ab)
+      # cross-check matcher: this round's one-pass kernel against round 1's two-direction launch (a variant library
+      # linked here from round 1's kernels_match.cu: librpe_b200_r01match.so) on the simulator sequence (config 2)
+      for v in "" r01match; do
+        RPE_LIB_VARIANT=$v timeout 300 python tools/gpu_cfg2_time.py > gpurun_out/cfg2_time_${v:-r02}.log 2>&1; echo "cfg2 ${v:-r02} rc=$?"; sed -n 2p gpurun_out/cfg2_time_${v:-r02}.log; done ;;
     smoke)
       timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log ;;
     bench)
