@@ -33,6 +33,6 @@ for what in "$@"; do
       timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'k_fast|k_blur|k_hamming|k_resize|k_ransac_solve|k_describe|k_pose|k_select|k_build' --launch-skip 20 -c 24 -o gpurun_out/full -f python bench.py --steps 2 --warmup 1 --no-cpu-baseline --lean --batch 32 --inflight 1 > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?" ;;
     cfg2)
       timeout 300 python tools/gpu_cfg2_time.py > gpurun_out/cfg2_time.log 2>&1; echo "cfg2 rc=$?"; tail -5 gpurun_out/cfg2_time.log
-      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_ransac|k_hamming|k_pose' -c 3 -o gpurun_out/cfg2 -f python tools/gpu_cfg2_time.py > gpurun_out/ncu_cfg2.log 2>&1; echo "ncu cfg2 rc=$?" ;;
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_ransac_solve|k_ransac_score|k_hamming' --launch-skip 2 -c 9 -o gpurun_out/cfg2 -f python tools/gpu_cfg2_time.py > gpurun_out/ncu_cfg2.log 2>&1; echo "ncu cfg2 rc=$?" ;;
   esac
 done
