@@ -38,16 +38,16 @@ void launch_bgr2gray(const uint8_t* bgr, size_t src_stride, int src_pitch, uint8
 
 // ------------------------------------------------------------------ K1: pyramid level l from l-1
 __global__ void __launch_bounds__(256)
-k_resize(const __grid_constant__ OrbGeom g, const PyrView pv, const int2* __restrict__ taps,
-         int level) {
+k_resize(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ src0, size_t src_stride,
+         uint8_t* __restrict__ pyr, const int2* __restrict__ taps, int level) {
   const LevelGeom& d = g.lv[level];
   const LevelGeom& s = g.lv[level - 1];
   const int img = blockIdx.z;
   const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int y = blockIdx.y * 8 + threadIdx.y;
   if (y >= d.h || x4 >= d.pitch) return;
-  const uint8_t* src = pv.level(g, img, level - 1);
-  uint8_t* dst = pv.pyr + (size_t)img * g.pyr_stride + d.off;
+  const uint8_t* src = src0 + (size_t)img * src_stride;      // source level of this image (level 0 may be the caller's buffer)
+  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
   const int2 ty = taps[d.ytab + y];
   uint32_t out = 0;
 #pragma unroll
@@ -69,16 +69,16 @@ k_resize(const __grid_constant__ OrbGeom g, const PyrView pv, const int2* __rest
 constexpr int kResizeRows = 8;
 
 __global__ void __launch_bounds__(256)
-k_resize_strip(const __grid_constant__ OrbGeom g, const PyrView pv, const int2* __restrict__ taps,
-               int level) {
+k_resize_strip(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ src0, size_t src_stride,
+               uint8_t* __restrict__ pyr, const int2* __restrict__ taps, int level) {
   const LevelGeom& d = g.lv[level];
   const LevelGeom& s = g.lv[level - 1];
   const int img = blockIdx.z;
   const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int y_first = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
   if (y_first >= d.h || x4 >= d.pitch) return;
-  const uint8_t* src = pv.level(g, img, level - 1);
-  uint8_t* dst = pv.pyr + (size_t)img * g.pyr_stride + d.off;
+  const uint8_t* src = src0 + (size_t)img * src_stride;      // source level of this image (level 0 may be the caller's buffer)
+  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
   // horizontal taps of the four columns
   uint32_t sel[4], wgt[4];
   int xbase;
@@ -150,8 +150,8 @@ constexpr int kResizeSrcRows = 11;
 constexpr int kResizeStageBytes = kResizeSrcRows * 3 * 256 * 4;
 
 __global__ void __launch_bounds__(256)
-k_resize_staged(const __grid_constant__ OrbGeom g, const PyrView pv, const int2* __restrict__ taps,
-                int level) {
+k_resize_staged(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ src0, size_t src_stride,
+                uint8_t* __restrict__ pyr, const int2* __restrict__ taps, int level) {
   extern __shared__ uint32_t s_rows[];   // [kResizeSrcRows][3][256 threads]
   const LevelGeom& d = g.lv[level];
   const LevelGeom& s = g.lv[level - 1];
@@ -160,8 +160,8 @@ k_resize_staged(const __grid_constant__ OrbGeom g, const PyrView pv, const int2*
   const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int y_first = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
   if (y_first >= d.h || x4 >= d.pitch) return;
-  const uint8_t* src = pv.level(g, img, level - 1);
-  uint8_t* dst = pv.pyr + (size_t)img * g.pyr_stride + d.off;
+  const uint8_t* src = src0 + (size_t)img * src_stride;      // source level of this image (level 0 may be the caller's buffer)
+  uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
   const int y_end = min(y_first + kResizeRows, d.h);
   int2 ty = __ldg(&taps[d.ytab + y_first]);
   const int ra0 = ty.x;
@@ -225,19 +225,22 @@ k_resize_staged(const __grid_constant__ OrbGeom g, const PyrView pv, const int2*
 static PyrView pyr_view(const OrbBuffers& b) { return PyrView{b.pyr, b.lvl0, b.lvl0_stride}; }
 
 void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream_t s, int* launches) {
-  const PyrView pv = pyr_view(b);
   for (int l = 1; l < g.nlevels; ++l) {
     const LevelGeom& d = g.lv[l];
+    // the source level: inside the pyramid slab, or - level 0 of device-resident frames used in place - the caller's buffer
+    const bool ext = l == 1 && b.lvl0 != nullptr;
+    const uint8_t* src0 = ext ? b.lvl0 : b.pyr + g.lv[l - 1].off;
+    const size_t sst = ext ? b.lvl0_stride : g.pyr_stride;
     // B200, 256 pairs: k_resize_strip on every level 2.20 ms; k_resize_staged on every level 1.81 ms
     if (g.resize_strip_ok && g.resize_span <= kResizeSrcRows) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
-      k_resize_staged<<<grid, block, kResizeStageBytes, s>>>(g, pv, b.taps, l);
+      k_resize_staged<<<grid, block, kResizeStageBytes, s>>>(g, src0, sst, b.pyr, b.taps, l);
     } else if (g.resize_strip_ok) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
-      k_resize_strip<<<grid, block, 0, s>>>(g, pv, b.taps, l);
+      k_resize_strip<<<grid, block, 0, s>>>(g, src0, sst, b.pyr, b.taps, l);
     } else {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 7) / 8, n_img), block(32, 8);
-      k_resize<<<grid, block, 0, s>>>(g, pv, b.taps, l);
+      k_resize<<<grid, block, 0, s>>>(g, src0, sst, b.pyr, b.taps, l);
     }
     ++*launches;
   }
