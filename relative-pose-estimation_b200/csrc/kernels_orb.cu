@@ -371,15 +371,19 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
       const int v = __shfl_up_sync(0xffffffffu, inc, o);
       if (lane >= o) inc += v;
     }
+    // queue entry = band << 10 | lane << 5 | q with q = clz of the bit: the lanes' loops are divergent (they run to
+    // the worst lane's count), so they only find the bit and store this code; (row, column) are decoded by the
+    // consumer, where every lane is busy.  Bit 31 - q = pixel 3 - (q >> 3) of the quad, row 8 band + (q & 7)
     uint16_t* out = S.queue + (inc - c);
 #pragma unroll
     for (int b = 0; b < kFastBands; ++b) {
       uint32_t bits = mm[b];
+      const uint32_t code0 = (uint32_t)(b << 10) | (uint32_t)(lane << 5);
       while (bits) {
-        const int p = 31 - __clz(bits);                      // bit p: pixel p >> 3 of the quad, row 8 b + 7 - (p & 7)
-        bits ^= 1u << p;
+        const int q = __clz(bits);
+        bits &= ~(0x80000000u >> q);
         RPE_ASSERT(out >= S.queue && out < S.queue + kFastQueue);
-        *out++ = (uint16_t)(((8 * b + 7 - (p & 7)) << 7) | (4 * lane + (p >> 3)));
+        *out++ = (uint16_t)(code0 + q);
       }
     }
     __syncwarp();
@@ -393,7 +397,8 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
       const int i = base + lane;
       int e = 0, sc = 0;
       if (i < total) {
-        e = S.queue[i];
+        const int code = S.queue[i];
+        e = ((((code >> 10) << 3) | (code & 7)) << 7) | (4 * ((code >> 5) & 31) + 3 - ((code >> 3) & 3));   // row << 7 | column
         RPE_ASSERT(e < kFastSH * kFastSP && ((e >> 7) + 6) * kFastIP + ib + (e & 127) + 3 < kFastIH * kFastIP &&
                    (e >> 7) + 6 < n_rows);
         sc = fast9_score(&S.img[((e >> 7) + 3) * kFastIP + ib + (e & 127)], kFastIP, thr);
@@ -744,7 +749,10 @@ __device__ __forceinline__ void blur_rows_x2(const uint8_t* rowA, const uint8_t*
   for (int c = 0; c < 4; ++c) out[c] = blur_row7_x2(v + c);
 }
 
-__global__ void __launch_bounds__(128, 4)
+#ifndef RPE_BLUR_MINB
+#define RPE_BLUR_MINB 4
+#endif
+__global__ void __launch_bounds__(128, RPE_BLUR_MINB)
 k_blur(const __grid_constant__ OrbGeom g, const PyrView pv, uint8_t* __restrict__ blur,
        const uint32_t* __restrict__ btab) {
   extern __shared__ __align__(128) uint8_t s_blur[];
@@ -997,6 +1005,9 @@ k_describe(const __grid_constant__ OrbGeom g, const PyrView pv, const uint8_t* _
   //     (Staging the keypoint's 37 x 37 window in shared memory first - 13 row-contiguous word loads per lane, then
   //     LDS gathers - was measured and lost: 2.02 ms against 1.87 ms for 512 images x 5000 keypoints; the extra
   //     staging instructions and the lower occupancy, 80 registers, cost more than the scattered sectors.)
+#ifdef RPE_DESC_UNROLL
+#pragma unroll RPE_DESC_UNROLL
+#endif
   for (int k = warp; k < nk; k += 4) {
     const LevelGeom& L = g.lv[s_level[k]];
     const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];

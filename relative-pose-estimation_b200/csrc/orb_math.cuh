@@ -165,16 +165,16 @@ RPE_HD int fast9_score(const uint8_t* c, int pitch, int t) {
   RPE_LD(8, 0, -3); RPE_LD(9, -1, -3); RPE_LD(10, -2, -2); RPE_LD(11, -3, -1);
   RPE_LD(12, -3, 0); RPE_LD(13, -3, 1); RPE_LD(14, -2, 2); RPE_LD(15, -1, 3);
 #undef RPE_LD
-  uint32_t m2[16], m4[16];
+  // min over the 9 contiguous ring positions k .. k+8 = min3 of three windows of three (VIMNMX3.U16x2): 16 + 16
+  // three-input minima and 8 three-input maxima, 40 instructions for both polarities
+  uint32_t m3[16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) m2[k] = umin16x2(P[k], P[(k + 1) & 15]);
-#pragma unroll
-  for (int k = 0; k < 16; ++k) m4[k] = umin16x2(m2[k], m2[(k + 2) & 15]);
+  for (int k = 0; k < 16; ++k) m3[k] = umin3_16x2(P[k], P[(k + 1) & 15], P[(k + 2) & 15]);
   uint32_t best = 0;
 #pragma unroll
   for (int k = 0; k < 16; k += 2) {
-    const uint32_t m9a = umin3_16x2(m4[k], m4[(k + 4) & 15], P[(k + 8) & 15]);
-    const uint32_t m9b = umin3_16x2(m4[k + 1], m4[(k + 5) & 15], P[(k + 9) & 15]);
+    const uint32_t m9a = umin3_16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+    const uint32_t m9b = umin3_16x2(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]);
     best = umax3_16x2(best, m9a, m9b);
   }
   const int a = (int)(best & 0xffffu) - 256, b = (int)(best >> 16) - 256;
