@@ -1005,9 +1005,11 @@ k_describe(const __grid_constant__ OrbGeom g, const PyrView pv, const uint8_t* _
   //     (Staging the keypoint's 37 x 37 window in shared memory first - 13 row-contiguous word loads per lane, then
   //     LDS gathers - was measured and lost: 2.02 ms against 1.87 ms for 512 images x 5000 keypoints; the extra
   //     staging instructions and the lower occupancy, 80 registers, cost more than the scattered sectors.)
-#ifdef RPE_DESC_UNROLL
-#pragma unroll RPE_DESC_UNROLL
+#ifndef RPE_DESC_UNROLL
+#define RPE_DESC_UNROLL 1
 #endif
+  constexpr int kDescUnroll = RPE_DESC_UNROLL;             // keypoints of a warp in flight together
+#pragma unroll kDescUnroll
   for (int k = warp; k < nk; k += 4) {
     const LevelGeom& L = g.lv[s_level[k]];
     const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];

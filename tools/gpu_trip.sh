@@ -13,6 +13,11 @@ for what in "$@"; do
       # compute-sanitizer, which is closed on this pool)
       RPE_LIB_VARIANT=checked RPE_EXTRA_DEFS=-DRPE_CHECKED=1 timeout 1800 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu_checked.log 2>&1; echo "checked pytest rc=$?"; tail -6 gpurun_out/pytest_gpu_checked.log
       RPE_LIB_VARIANT=checked RPE_EXTRA_DEFS=-DRPE_CHECKED=1 timeout 600 python tools/sanitize_target.py > gpurun_out/checked_target.log 2>&1; echo "checked target rc=$?"; tail -2 gpurun_out/checked_target.log ;;
+    ab:*)
+      # A/B over variant libraries (RPE_LIB_VARIANT=x RPE_EXTRA_DEFS=-DX=1 python relative-pose-estimation_b200/build.py): ab:base,x,y
+      for v in $(echo "${what#ab:}" | tr ',' ' '); do
+        RPE_LIB_VARIANT=$v timeout 300 python bench.py --lean --no-cpu-baseline --steps 10 > gpurun_out/bench_ab_$v.json 2> gpurun_out/bench_ab.err || tail -3 gpurun_out/bench_ab.err
+        echo "A/B $v"; python tools/show_bench.py gpurun_out/bench_ab_$v.json | head -2; done ;;
     match_ab)
       # cross-check matcher: this round's one-pass kernel against round 1's two-direction launch (a variant library
       # linked here from round 1's kernels_match.cu: librpe_b200_r01match.so) on the simulator sequence (config 2)
