@@ -277,6 +277,7 @@ constexpr int kFastIPW = kFastIP / 4;
 constexpr int kFastBands = kFastSH / 8;
 static_assert(kFastSH % 8 == 0 && kFastTW + 8 == kFastSP, "score rows in bands of 8, 32 quads per row");
 constexpr int kFastWarps = 4;                // independent warps (tiles) per CTA
+constexpr int kFastRot = 5;                  // row sr's pass bits are held by lane (quad column + kFastRot * sr) % 32
 constexpr int kFastQueue = 512;              // queue entries per warp; a half-band of 4 rows x 128 px always fits
 
 // unpack a column word into its two u16x2 halves (volatile: keep the order of the window updates as written)
@@ -354,8 +355,12 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
     fast_unpack_keep(wimg[(sr + 6) * kFastIPW], wl[(sr + 6) % 7], wh[(sr + 6) % 7]);
     const uint32_t* row = wimg + (sr + 3) * kFastIPW;
     const uint32_t rmask = (uint32_t)(sr - sr_lo) < (uint32_t)sr_n ? vmask : 0u;
-    const uint32_t cw = fast_compass4_unpacked(wl[(sr + 3) % 7], wh[(sr + 3) % 7], wl[sr % 7], wh[sr % 7],
-                                               wl[(sr + 6) % 7], wh[(sr + 6) % 7], row[-1], row[0], row[1], kt) & rmask;
+    uint32_t cw = fast_compass4_unpacked(wl[(sr + 3) % 7], wh[(sr + 3) % 7], wl[sr % 7], wh[sr % 7],
+                                         wl[(sr + 6) % 7], wh[(sr + 6) % 7], row[-1], row[0], row[1], kt) & rmask;
+    // candidates cluster (the worst lane of a band held ~22 of the band's ~75): the pass bits of row sr go to lane
+    // (lane + 5 sr) % 32, so that a cluster spreads over many lanes and the lanes' expansion loops below, which run
+    // to the worst lane's count, stay short.  The consumer undoes the rotation when it decodes a queue entry
+    cw = __shfl_sync(0xffffffffu, cw, (lane - kFastRot * sr) & 31);
     m[sr >> 3] |= cw >> (sr & 7);
   }
 
@@ -373,7 +378,8 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
     }
     // queue entry = band << 10 | lane << 5 | q with q = clz of the bit: the lanes' loops are divergent (they run to
     // the worst lane's count), so they only find the bit and store this code; (row, column) are decoded by the
-    // consumer, where every lane is busy.  Bit 31 - q = pixel 3 - (q >> 3) of the quad, row 8 band + (q & 7)
+    // consumer, where every lane is busy.  Bit 31 - q = pixel 3 - (q >> 3) of a quad, row 8 band + (q & 7); the
+    // quad's column is (lane - kFastRot * row) % 32
     uint16_t* out = S.queue + (inc - c);
 #pragma unroll
     for (int b = 0; b < kFastBands; ++b) {
@@ -398,7 +404,8 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
       int e = 0, sc = 0;
       if (i < total) {
         const int code = S.queue[i];
-        e = ((((code >> 10) << 3) | (code & 7)) << 7) | (4 * ((code >> 5) & 31) + 3 - ((code >> 3) & 3));   // row << 7 | column
+        const int row = ((code >> 10) << 3) | (code & 7);
+        e = (row << 7) | (4 * (((code >> 5) - kFastRot * row) & 31) + 3 - ((code >> 3) & 3));          // row << 7 | column
         RPE_ASSERT(e < kFastSH * kFastSP && ((e >> 7) + 6) * kFastIP + ib + (e & 127) + 3 < kFastIH * kFastIP &&
                    (e >> 7) + 6 < n_rows);
         sc = fast9_score(&S.img[((e >> 7) + 3) * kFastIP + ib + (e & 127)], kFastIP, thr);
@@ -417,16 +424,19 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
   uint32_t* keep_keys = reinterpret_cast<uint32_t*>(S.img);  // (all scores are in the score tile by now)
   auto nms = [&](int e) {
     const int sr = e >> 7, c = e & 127;
-    if (sr < 1 || sr > kFastTH || c < 4 || c >= 4 + kFastTW) return;
     const int x = x0 - 4 + c, y = y0 - 1 + sr;
-    if (x < 31 || x >= lw - 31 || y < 31 || y >= lh - 31) return;
+    // inside the tile proper (not its 1-px NMS rim) and at least 31 px from the level border; straight-line
+    const bool inside = (unsigned)(sr - 1) < (unsigned)kFastTH && (unsigned)(c - 4) < (unsigned)kFastTW &&
+                        (unsigned)(x - 31) < (unsigned)(lw - 62) && (unsigned)(y - 31) < (unsigned)(lh - 62);
+    if (!inside) return;
+    RPE_ASSERT(e - kFastSP - 1 >= 0 && e + kFastSP + 1 < kFastSH * kFastSP);
     const uint8_t* p = &S.score[e];
     const int s = p[0];
-    const bool keep = s > p[-kFastSP - 1] && s > p[-kFastSP] && s > p[-kFastSP + 1] && s > p[-1] &&
-                      s > p[1] && s > p[kFastSP - 1] && s > p[kFastSP] && s > p[kFastSP + 1];
-    if (keep) {
+    const int hi = max(max(max(p[-kFastSP - 1], p[-kFastSP]), max(p[-kFastSP + 1], p[-1])),
+                       max(max(p[1], p[kFastSP - 1]), max(p[kFastSP], p[kFastSP + 1])));
+    if (s > hi) {                                            // strict maximum of its 3 x 3 neighbourhood
       const uint32_t slot = atomicAdd(&S.n_keep, 1u);
-      RPE_ASSERT(4 * (slot + 1) <= (uint32_t)(kFastIH * kFastIP) && e - kFastSP - 1 >= 0 && e + kFastSP + 1 < kFastSH * kFastSP);
+      RPE_ASSERT(4 * (slot + 1) <= (uint32_t)(kFastIH * kFastIP));
       keep_keys[slot] = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
     }
   };
@@ -749,10 +759,9 @@ __device__ __forceinline__ void blur_rows_x2(const uint8_t* rowA, const uint8_t*
   for (int c = 0; c < 4; ++c) out[c] = blur_row7_x2(v + c);
 }
 
-#ifndef RPE_BLUR_MINB
-#define RPE_BLUR_MINB 4
-#endif
-__global__ void __launch_bounds__(128, RPE_BLUR_MINB)
+// (128 registers, 4 CTAs per SM.  Capping the registers for 5 / 6 CTAs per SM spills the 7-row window: 2.48 / 2.74 ms
+// against 2.21 ms; B200, 512 images 1280x720.)
+__global__ void __launch_bounds__(128, 4)
 k_blur(const __grid_constant__ OrbGeom g, const PyrView pv, uint8_t* __restrict__ blur,
        const uint32_t* __restrict__ btab) {
   extern __shared__ __align__(128) uint8_t s_blur[];
@@ -1005,11 +1014,7 @@ k_describe(const __grid_constant__ OrbGeom g, const PyrView pv, const uint8_t* _
   //     (Staging the keypoint's 37 x 37 window in shared memory first - 13 row-contiguous word loads per lane, then
   //     LDS gathers - was measured and lost: 2.02 ms against 1.87 ms for 512 images x 5000 keypoints; the extra
   //     staging instructions and the lower occupancy, 80 registers, cost more than the scattered sectors.)
-#ifndef RPE_DESC_UNROLL
-#define RPE_DESC_UNROLL 1
-#endif
-  constexpr int kDescUnroll = RPE_DESC_UNROLL;             // keypoints of a warp in flight together
-#pragma unroll kDescUnroll
+  //     Two / four keypoints of a warp in flight together (loop unrolled): 1.92 / 1.95 ms.
   for (int k = warp; k < nk; k += 4) {
     const LevelGeom& L = g.lv[s_level[k]];
     const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];
