@@ -1,6 +1,9 @@
 """Print the interesting parts of a bench.py JSON line."""
 import json
+import signal
 import sys
+
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)
 
 d = json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
 if "value" in d:
