@@ -266,9 +266,12 @@ void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream
 //      waiting on L2 round trips: 30 % of the stall samples of the first version of this kernel), + histogram.
 // A tile with more candidates than the queue holds (dense noise) is processed in half-bands of 4 rows and its NMS
 // scans the score tile instead of a corner list.
-// Measured on B200, 512 images 1280x720, 12 levels (profiles/): one CTA of 8 warps per 120x30 tile (round 1)
-// 3.78 ms at 44.6 thread-instructions per pixel; one warp per 120x30 tile 5.67 ms (33.7 instructions per pixel but 12
-// warps per SM); this form: see DESIGN.md.
+// Measured on B200, 512 images 1280x720, 12 levels (profiles/): one CTA of 8 warps per 120x30 tile, per-pixel
+// predicated queue stores (round 1): 3.78 ms at 44.6 thread-instructions per pixel.  One warp per tile, round 2:
+// 120x30 tiles (12 warps / SM) with a returning global atomic per corner 5.67 ms; 120x14 tiles (32 warps / SM), one
+// slot reservation per tile 3.83 ms; + three-input minima in the score network, queue codes decoded by the consumer
+// 3.55 ms; + pass bits rotated across lanes, straight-line NMS 3.32 ms.  Tile height with everything else equal:
+// 14 / 22 / 30 rows (32 / 24 / 20 warps per SM) 3.32 / 3.43 / 3.86 ms: occupancy outweighs the smaller halo.
 constexpr int kFastIP = 144;                 // staged bytes per image row (16-B aligned start; columns ib-3 .. ib+130 used)
 constexpr int kFastIH = kFastTH + 8;         // image rows y0-4 .. y0+TH+3
 constexpr int kFastSP = 128;                 // score tile pitch: x0-4 .. x0+123
@@ -324,8 +327,7 @@ k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __re
   __syncwarp();
   RPE_ASSERT(level < g.nlevels && n_rows > 0 && row_bytes > 0 && row_bytes % 16 == 0 && y0 - 4 >= 0 && astart >= 0 &&
              astart + (int)row_bytes <= pitch && (x0 - 4 - astart == 4 || x0 - 4 - astart == 12));
-  if (lane < n_rows) bulk_copy_g2s(S.img + lane * kFastIP, src + (size_t)lane * pitch, row_bytes, &S.bar);
-  static_assert(kFastIH <= 32, "one staged row per lane");
+  for (int r = lane; r < n_rows; r += 32) bulk_copy_g2s(S.img + r * kFastIP, src + (size_t)r * pitch, row_bytes, &S.bar);
 #pragma unroll
   for (int i = 0; i < kFastSH * kFastSP / (16 * 32); ++i) reinterpret_cast<uint4*>(S.score)[i * 32 + lane] = make_uint4(0, 0, 0, 0);
   const int thr = g.fast_threshold;
