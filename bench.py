@@ -465,6 +465,19 @@ def measure_pairs(ctx: Ctx, cfg, B, n_batches, steps, warmup, with_cpu, name):
 
 
 # ------------------------------------------------------------------------------------------ line item: config 5
+def stream_calls(per_rank, ring_pairs, C):
+    """Schedule of chained sequence calls over a ring of ring_pairs + 1 frames: (first frame in the ring, pairs).
+    A call starts at the previous call's last frame; at the end of the ring the walk restarts at frame 0 (the pair
+    last frame -> frame 0 is not a pair of the stream and is never formed)."""
+    calls, done = [], 0
+    while done < per_rank:
+        pos = done % ring_pairs
+        n = min(C, per_rank - done, ring_pairs - pos)
+        calls.append((pos, n))
+        done += n
+    return calls
+
+
 def run_stream(ctx: Ctx, cfg):
     """BASELINE config 5: `--pairs` consecutive frame pairs of one synthetic 1280x720 video stream (cfg3 parameters),
     sharded over the ranks in contiguous blocks (boundary frame duplicated, no exchange), every rank feeding chained
@@ -487,13 +500,7 @@ def run_stream(ctx: Ctx, cfg):
     dring = ring.cuda(non_blocking=False)
     eng = ctx.engine(cfg, C)
     eng.set_pipeline(args.chunk, args.streams)
-    # schedule of calls: (first frame in the ring, pairs)
-    calls, done = [], 0
-    while done < per_rank:
-        pos = done % ring_pairs
-        n = min(C, per_rank - done, ring_pairs - pos)
-        calls.append((pos, n))
-        done += n
+    calls = stream_calls(per_rank, ring_pairs, C)
     sub_dev = lambda e, i: e.submit_sequence_device(dring[calls[i][0]].data_ptr(), H * W, calls[i][1] + 1, H, W, W, K)
     sub_host = lambda e, i: e.submit_sequence(ring_np[calls[i][0]:calls[i][0] + calls[i][1] + 1], K)
     lap = min(len(calls), ring_pairs // C)

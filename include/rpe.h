@@ -126,7 +126,10 @@ int rpe_wait_batch(rpe_handle* h);
 
 /* same, inputs already resident in device memory: d_images holds 2*B images, image 2*i is
  * view 1 of pair i and 2*i+1 is view 2, each H rows of `pitch` bytes, consecutive images
- * `img_stride` bytes apart.  Results are copied to the host pointers as above. */
+ * `img_stride` bytes apart.  Results are copied to the host pointers as above.
+ * Gray frames whose layout already is the pyramid's (pitch == (W + 15) / 16 * 16, base and img_stride multiples
+ * of 16) are read IN PLACE as pyramid level 0 (no copy); any other layout is copied first.  Either way the frames
+ * must stay valid and unchanged until the call (or, for the submit forms, rpe_wait_batch) returns. */
 int rpe_estimate_batch_device(rpe_handle* h, const uint8_t* d_images, size_t img_stride,
                               int32_t B, int32_t H, int32_t W, size_t pitch, const double K[9],
                               double* R, double* t, double* euler, int32_t* status, int32_t* info);
