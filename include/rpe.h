@@ -216,6 +216,24 @@ int rpe_evaluate_sequence(rpe_handle* h, int32_t n, const double* est_R, const d
  * host errors[n*5] table laid out as above */
 int rpe_summarize_errors(rpe_handle* h, int32_t n, const double* errors, double* summary);
 
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * rpe_evaluate_sequence without any allocation and without a handle: same kernels, same arithmetic, but the
+ * per-frame error table (the scratch of that call) lives in a file-scope static __device__ array of
+ * RPE_NOALLOC_MAX_FRAMES x 5 doubles (640 KiB, held by every GPU that loads the library until the process exits).
+ * Runs on the CURRENT device; ALL pointers are DEVICE pointers owned by the caller: inputs laid out as for
+ * rpe_evaluate_sequence, d_summary[25] as its `summary`.  The work is enqueued on `cuda_stream` (cudaStream_t; NULL =
+ * the default stream) and the call returns without synchronising; it calls no cudaMalloc / cudaFree / allocating
+ * library routine.  n > RPE_NOALLOC_MAX_FRAMES -> RPE_ERR_CAPACITY (rpe_last_error names the limit); host pointers
+ * -> RPE_ERR_INVALID.  Every call on a device shares the one array (it keeps the last call's table; nothing in it
+ * needs clearing, rows beyond n are never read): calls that overlap on the GPU — different streams without a
+ * dependency, or two threads — race; serialise them on one stream or with events.  The first call on a device
+ * resolves the array's address (cudaGetSymbolAddress): make it outside a stream capture. */
+#define RPE_NOALLOC_MAX_FRAMES 16384
+int rpe_evaluate_sequence_noalloc(int32_t n, const double* d_est_R, const double* d_est_t, const double* d_est_euler,
+                                  const double* d_gt_euler, const double* d_gt_pos, int32_t euler_convention,
+                                  double* d_summary, void* cuda_stream);
+
 /* intermediate results of the LAST batch call, for stage-wise parity:
  * copies up to *n bytes to `out` and stores the byte count in *n.  `view` selects frame pair + view of a
  * sequence call (image slot pair + view) or view 1 / 2 of a pair-batch call (slot 2*pair + view). */

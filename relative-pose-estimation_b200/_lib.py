@@ -68,6 +68,7 @@ _SIGNATURES = [
     ("rpe_estimate_from_matches", C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P]),
     ("rpe_evaluate_sequence", C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P, C.c_int32, _P, _P]),
     ("rpe_summarize_errors", C.c_int, [_P, C.c_int32, _P, _P]),
+    ("rpe_evaluate_sequence_noalloc", C.c_int, [C.c_int32, _P, _P, _P, _P, _P, C.c_int32, _P, _P]),
     ("rpe_get_stage", C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, C.POINTER(C.c_size_t)]),
     ("rpe_set_profiling", C.c_int, [_P, C.c_int32]),
     ("rpe_get_stage_times", C.c_int, [_P, _P, _P]),

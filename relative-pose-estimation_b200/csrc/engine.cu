@@ -33,6 +33,8 @@ static int fail(int code, const char* msg) {
   g_last_error = msg;
   return code;
 }
+// for the entry points that live beside their kernels (kernels_eval.cu): same thread-local message as above
+int rpe::report_error(int code, const char* msg) { return fail(code, msg); }
 
 static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
 static inline int pow2_ge(int v) {

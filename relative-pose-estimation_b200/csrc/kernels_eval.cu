@@ -9,6 +9,9 @@
 //   k_eval_summary : one CTA per metric: mean, population std, median (exact: 64-bit radix select on the
 //                    orderable bit pattern, 8 passes of 8 bits), max, min.  A NaN anywhere in a metric makes all
 //                    five of its statistics NaN, as numpy does.
+#include <cstdio>
+#include <mutex>
+
 #include "rpe_device.cuh"
 
 namespace rpe {
@@ -184,3 +187,77 @@ void launch_eval_summary(int n, const double* errors, double* summary, cudaStrea
 }
 
 }  // namespace rpe
+
+// ---------------------------------------------------------------------------------------------------------------
+// rpe_evaluate_sequence_noalloc: the evaluation above for callers that may not allocate (include/rpe.h).
+// The per-frame error table [n][5] — the scratch rpe_evaluate_sequence keeps in a cudaMalloc'ed, grown-on-demand
+// buffer — lives here in a file-scope device array instead.  Every GPU that loads the library holds these
+// RPE_NOALLOC_MAX_FRAMES * 5 * 8 bytes (640 KiB) until the process exits.
+//
+// `g_noalloc_errors` below is, in HOST code, only the host-side stand-in of the symbol: its device address is asked
+// for once per device (cudaGetSymbolAddress with that device current) and that pointer is what the kernels get.
+// All calls on one device share the array; it keeps the previous call's table.  Nothing in it has to start at
+// zero: k_eval_errors writes rows 0 .. n-1 before k_eval_summary (next on the same stream) reads exactly those
+// rows, so rows >= n left by a longer earlier call are never read.  Two calls that overlap on the GPU (different
+// streams, no dependency) race on the array.
+static __device__ __align__(256) double g_noalloc_errors[(size_t)RPE_NOALLOC_MAX_FRAMES * 5];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+double* g_noalloc_ptr[kMaxDevices] = {};   // device address of g_noalloc_errors on device d (nullptr: not asked yet)
+
+bool is_device_pointer(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+}  // namespace
+
+extern "C" int rpe_evaluate_sequence_noalloc(int32_t n, const double* d_est_R, const double* d_est_t,
+                                             const double* d_est_euler, const double* d_gt_euler,
+                                             const double* d_gt_pos, int32_t euler_convention, double* d_summary,
+                                             void* cuda_stream) {
+  char msg[256];
+  if (n < 1) return rpe::report_error(RPE_ERR_INVALID, "rpe_evaluate_sequence_noalloc: n must be >= 1");
+  if (n > RPE_NOALLOC_MAX_FRAMES) {
+    snprintf(msg, sizeof msg, "rpe_evaluate_sequence_noalloc: n = %d exceeds RPE_NOALLOC_MAX_FRAMES = %d (the static "
+             "scratch is not grown; use rpe_evaluate_sequence for longer sequences)", (int)n, (int)RPE_NOALLOC_MAX_FRAMES);
+    return rpe::report_error(RPE_ERR_CAPACITY, msg);
+  }
+  if (euler_convention != RPE_EULER_YUP && euler_convention != RPE_EULER_ZYX)
+    return rpe::report_error(RPE_ERR_INVALID, "rpe_evaluate_sequence_noalloc: bad euler convention");
+  const void* ptrs[6] = {d_est_R, d_est_t, d_est_euler, d_gt_euler, d_gt_pos, d_summary};
+  for (const void* p : ptrs)
+    if (!p || !is_device_pointer(p))
+      return rpe::report_error(RPE_ERR_INVALID, "rpe_evaluate_sequence_noalloc: inputs and d_summary must be device pointers");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    snprintf(msg, sizeof msg, "rpe_evaluate_sequence_noalloc: cudaGetDevice -> %s (device %d)", cudaGetErrorString(e), dev);
+    return rpe::report_error(RPE_ERR_NO_DEVICE, msg);
+  }
+  double* scratch;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {                 // set-up, once per device, that device current
+      double* p = nullptr;
+      e = cudaGetSymbolAddress((void**)&p, g_noalloc_errors);
+      if (e != cudaSuccess || !p) {
+        snprintf(msg, sizeof msg, "rpe_evaluate_sequence_noalloc: cudaGetSymbolAddress(g_noalloc_errors) on device %d -> %s",
+                 dev, cudaGetErrorString(e));
+        return rpe::report_error(RPE_ERR_CUDA, msg);
+      }
+      g_noalloc_ptr[dev] = p;
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  rpe::launch_evaluate(n, d_est_R, d_est_t, d_est_euler, d_gt_euler, d_gt_pos, euler_convention, scratch, d_summary,
+                       (cudaStream_t)cuda_stream);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(msg, sizeof msg, "rpe_evaluate_sequence_noalloc: launch -> %s", cudaGetErrorString(e));
+    return rpe::report_error(RPE_ERR_CUDA, msg);
+  }
+  return RPE_OK;
+}

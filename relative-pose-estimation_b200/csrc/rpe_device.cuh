@@ -176,6 +176,7 @@ void launch_pose(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int n_
 void launch_evaluate(int n, const double* est_R, const double* est_t, const double* est_euler, const double* gt_euler,
                      const double* gt_pos, int convention, double* errors, double* summary, cudaStream_t s);
 void launch_eval_summary(int n, const double* errors, double* summary, cudaStream_t s);
+int report_error(int code, const char* msg);   // sets rpe_last_error() of the calling thread, returns code (engine.cu)
 int setup_orb_attributes(int sort_cap);
 int setup_match_attributes(int sort_cap);
 int setup_geom_attributes();
