@@ -299,7 +299,10 @@ struct __align__(16) FastWarpSmem {
 static_assert(sizeof(FastWarpSmem) % 16 == 0, "warp slices stay 16-byte aligned");
 static_assert(kFastIH * kFastIP >= 4 * ((kFastTH + 1) / 2) * ((kFastTW + 1) / 2), "kept keys (NMS maxima: at most one pixel in four) fit over the image rows");
 
-__global__ void __launch_bounds__(kFastWarps * 32, 8)
+#ifndef RPE_FAST_MINB
+#define RPE_FAST_MINB 8
+#endif
+__global__ void __launch_bounds__(kFastWarps * 32, RPE_FAST_MINB)
 k_fast(const __grid_constant__ OrbGeom g, const PyrView pv, const uint32_t* __restrict__ ftab,
        uint32_t* __restrict__ cand_key, uint32_t* __restrict__ cand_cnt, uint32_t* __restrict__ hist) {
   extern __shared__ __align__(128) uint8_t s_fast[];
@@ -895,7 +898,10 @@ static void build_ori_table(uint2* tab) {
       }
 }
 
-__global__ void __launch_bounds__(128)
+#ifndef RPE_DESC_MINB
+#define RPE_DESC_MINB 8
+#endif
+__global__ void __launch_bounds__(128, RPE_DESC_MINB)
 k_describe(const __grid_constant__ OrbGeom g, const PyrView pv, const uint8_t* __restrict__ blur,
            const uint32_t* __restrict__ lvl_key, const float* __restrict__ lvl_resp,
            const uint32_t* __restrict__ lvl_cnt, float* __restrict__ kp_x, float* __restrict__ kp_y,

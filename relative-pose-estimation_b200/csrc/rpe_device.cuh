@@ -63,7 +63,10 @@ constexpr int kTileW = 64;
 constexpr int kTileH = 32;
 constexpr int kFastTW = 120;
 constexpr int kFastTH = 14;     // tile rows; + 2 = 16 score rows = two bands of 8 (k_fast: one warp per tile)
-constexpr int kBlurRows = 32;    // blur work item = 128 columns x two strips of kBlurRows rows (one warp)
+#ifndef RPE_BLUR_ROWS
+#define RPE_BLUR_ROWS 35
+#endif
+constexpr int kBlurRows = RPE_BLUR_ROWS;   // blur work item = 128 columns x two strips of kBlurRows rows (one warp)
 constexpr int kFastOrigin = 24;  // FAST tiles start at x = y = 24 (a multiple of 4): only scores in [30, size-30) can matter
 
 // Where the pyramid levels of image slot `img` live: level l >= 1 inside the handle's pyramid slab; level 0 there too
