@@ -3,6 +3,7 @@
 //   H2D -> pyramid -> FAST+NMS -> retainBest/Harris -> blur -> orientation+rBRIEF
 //       -> Hamming k-NN -> cross-check|ratio + stable sort + cut -> 5-pt RANSAC -> recoverPose -> D2H
 // on one CUDA stream, with no host synchronisation between stages.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -1158,7 +1159,14 @@ int rpe_get_stage(rpe_handle* h, int32_t pair, int32_t view, int32_t stage, int3
         base = h->lvl0[h->last_set] + img * h->lvl0_stride[h->last_set];
       const size_t bytes = (size_t)L.w * L.h;
       if (cap < bytes) return fail(RPE_ERR_INVALID, "buffer too small");
-      RPE_CK(cudaMemcpy2D(out, L.w, base, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost));
+      if (stage == RPE_STAGE_BLURRED_LEVEL) {
+        // blurred levels are stored in 16-column strips (rpe_device.cuh: blur_strip_offset): one strided copy per strip
+        for (int x = 0; x < L.w; x += kBlurStripW)
+          RPE_CK(cudaMemcpy2D((uint8_t*)out + x, L.w, base + blur_strip_offset(x, 0, L.h), kBlurStripW,
+                              std::min(kBlurStripW, L.w - x), L.h, cudaMemcpyDeviceToHost));
+      } else {
+        RPE_CK(cudaMemcpy2D(out, L.w, base, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost));
+      }
       *n = bytes;
       return RPE_OK;
     }

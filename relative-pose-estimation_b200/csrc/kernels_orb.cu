@@ -818,8 +818,10 @@ k_blur(const __grid_constant__ OrbGeom g, const PyrView pv, uint8_t* __restrict_
   const int x = x0 + 4 * lane;
   const uint8_t* pA = sA + 12 + 4 * lane;                  // pixels x - 4 .. x + 7 of a staged row
   const uint8_t* pB = sB + 12 + 4 * lane;
-  uint8_t* dA = blur + (size_t)img * g.pyr_stride + L.off + (size_t)yA * pitch + x;
-  uint8_t* dB = dA + (size_t)kBlurRows * pitch;
+  // the blurred level is stored in STRIPS (kBlurStripW columns x all rows, strip after strip; a 128-byte line = 8 rows
+  // of one strip) for k_describe's rotated gathers: see blur_strip_offset
+  uint8_t* dA = blur + (size_t)img * g.pyr_stride + L.off + blur_strip_offset(x, yA, h);
+  uint8_t* dB = dA + (size_t)kBlurRows * kBlurStripW;
   const bool col_ok = x < w;
   float2 win[7][4];
 #pragma unroll
@@ -843,11 +845,11 @@ k_blur(const __grid_constant__ OrbGeom g, const PyrView pv, uint8_t* __restrict_
       }
       if (col_ok && o < nA) {
         const uint32_t lo = __byte_perm(oa[0], oa[1], 0x0040), hi = __byte_perm(oa[2], oa[3], 0x0040);
-        *reinterpret_cast<uint32_t*>(dA + (size_t)o * pitch) = __byte_perm(lo, hi, 0x5410);
+        *reinterpret_cast<uint32_t*>(dA + o * kBlurStripW) = __byte_perm(lo, hi, 0x5410);
       }
       if (col_ok && o < nB) {
         const uint32_t lo = __byte_perm(ob[0], ob[1], 0x0040), hi = __byte_perm(ob[2], ob[3], 0x0040);
-        *reinterpret_cast<uint32_t*>(dB + (size_t)o * pitch) = __byte_perm(lo, hi, 0x5410);
+        *reinterpret_cast<uint32_t*>(dB + o * kBlurStripW) = __byte_perm(lo, hi, 0x5410);
       }
     }
   }
@@ -896,6 +898,23 @@ static void build_ori_table(uint2* tab) {
         }
         tab[(sh * 31 + r) * 10 + w] = make_uint2(cu, cm);
       }
+}
+
+// brief_test (orb_math.cuh) against the strip layout of the blurred level.  Same non-fused rotation; cvRound by the
+// 1.5 * 2^23 trick (the low mantissa bits of d + 1.5 * 2^23 are rint(d), ties to even, in two's complement: no F2I on
+// the XU pipe), so X = cx + ix is one integer add on the float's bits (cxm = cx - kRintBits).
+constexpr int kRintBits = 0x4B400000;             // bits of 12582912.0f = 1.5 * 2^23
+__device__ __forceinline__ uint32_t brief_test_strips(const uint8_t* base, int strip_bytes, int cxm, int cym, float a,
+                                                      float b, uint32_t t) {
+  const float xa = (float)(int8_t)(t & 0xff), ya = (float)(int8_t)((t >> 8) & 0xff);
+  const float xb = (float)(int8_t)((t >> 16) & 0xff), yb = (float)(int8_t)(t >> 24);
+  const int Xa = __float_as_int(f32_add(f32_sub(f32_mul(xa, a), f32_mul(ya, b)), 12582912.0f)) + cxm;
+  const int Ya = __float_as_int(f32_add(f32_add(f32_mul(xa, b), f32_mul(ya, a)), 12582912.0f)) + cym;
+  const int Xb = __float_as_int(f32_add(f32_sub(f32_mul(xb, a), f32_mul(yb, b)), 12582912.0f)) + cxm;
+  const int Yb = __float_as_int(f32_add(f32_add(f32_mul(xb, b), f32_mul(yb, a)), 12582912.0f)) + cym;
+  const int va = base[(Xa >> kBlurStripLog) * strip_bytes + Ya * kBlurStripW + (Xa & (kBlurStripW - 1))];
+  const int vb = base[(Xb >> kBlurStripLog) * strip_bytes + Yb * kBlurStripW + (Xb & (kBlurStripW - 1))];
+  return (uint32_t)(va < vb);
 }
 
 #ifndef RPE_DESC_MINB
@@ -1025,12 +1044,14 @@ k_describe(const __grid_constant__ OrbGeom g, const PyrView pv, const uint8_t* _
   //     Two / four keypoints of a warp in flight together (loop unrolled): 1.92 / 1.95 ms.
   for (int k = warp; k < nk; k += 4) {
     const LevelGeom& L = g.lv[s_level[k]];
-    const uint8_t* c = blur + (size_t)img * g.pyr_stride + L.off + (size_t)s_cy[k] * L.pitch + s_cx[k];
+    const uint8_t* base = blur + (size_t)img * g.pyr_stride + L.off;
     RPE_ASSERT(s_cx[k] >= 19 && s_cx[k] < L.w - 19 && s_cy[k] >= 19 && s_cy[k] < L.h - 19);   // pattern radius 18.4
     const float a = s_a[k], b = s_b[k];
+    const int strip_bytes = L.h * kBlurStripW;
+    const int cxm = s_cx[k] - kRintBits, cym = s_cy[k] - kRintBits;
     uint32_t byte = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) byte |= brief_test(c, L.pitch, a, b, pat[j]) << j;
+    for (int j = 0; j < 8; ++j) byte |= brief_test_strips(base, strip_bytes, cxm, cym, a, b, pat[j]) << j;
     desc[((size_t)img * g.kp_stride + i0 + k) * 32 + lane] = (uint8_t)byte;
   }
 }
