@@ -199,6 +199,23 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
     for (int y = 0; y < h[l]; y += 8)
       g.resize_span = std::max(g.resize_span, yt[std::min(y + 7, h[l] - 1)].x + 2 - yt[y].x);
   }
+  // source bytes a group of 128 output columns needs, counted from the 16-byte-aligned column at or left of its first
+  // tap: the last lane (4 columns from x & ~3 <= w - 1) reads three words from its own aligned tap
+  g.resize_rows_strict = 1;
+  for (int l = 1; l < c.nlevels; ++l) {
+    const int2* yt = G.taps.data() + g.lv[l].ytab;
+    for (int y = 1; y < h[l]; ++y)
+      if (yt[y].x <= yt[y - 1].x) g.resize_rows_strict = 0;
+  }
+  g.resize_xspan = 0;
+  for (int l = 1; l < c.nlevels; ++l) {
+    const int2* xt = G.taps.data() + g.lv[l].xtab;
+    for (int x = 0; x < g.lv[l].pitch; x += 128) {
+      const int astart = xt[std::min(x, w[l] - 1)].x & ~15;
+      for (int q = x; q <= std::min(x + 124, g.lv[l].pitch - 4); q += 4)
+        g.resize_xspan = std::max(g.resize_xspan, (xt[std::min(q, w[l] - 1)].x & ~3) + 12 - astart);
+    }
+  }
   g.total_tiles = tile0;
   g.total_ftiles = ftile0;
   g.total_bitems = (int)G.btab.size();

@@ -139,50 +139,52 @@ k_resize_strip(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ sr
 }
 
 
-// Same strip, source rows staged first: the thread requests ALL source rows of its strip (<= kResizeSrcRows rows x
-// three words) up front, parks them in its own shared-memory column and only then walks down the strip, reading rows
-// back with LDS.  k_resize_strip keeps one row in flight per thread and waits on it row after row (ncu: 37 % of its
-// stall samples on the row-advance); here one round trip covers the strip.  A thread reads only what it staged
-// itself, so no barrier is needed.  Chosen on the host when every strip of the level chain spans <= kResizeSrcRows
-// source rows (scale <= ~1.25), else k_resize_strip.  (Staging with 4-byte cp.async instead of LDG + STS was equally
-// fast alone and 3 % slower end to end with the next batch uploading beside it: B200, 256 pairs, 1.89 vs 1.81 ms.)
-constexpr int kResizeSrcRows = 11;
-constexpr int kResizeStageBytes = kResizeSrcRows * 3 * 256 * 4;
+constexpr int kResizeSrcRows = 11;          // source rows of an 8-row output strip at scale <= ~1.25
+
+// Same strip, source rows staged by the TMA engine: one WARP = 128 output columns x kResizeRows output rows; its
+// <= kResizeSrcRows source rows (<= kResizeTmaW bytes each, from the 16-byte-aligned column at or left of lane 0's
+// first tap) arrive by bulk copies on the warp's own mbarrier; the horizontal pass reads its three words of a row at
+// the lane's own offset.  No CTA-wide barrier.  History (B200, 256 pairs, 11 launches): k_resize_strip on every level
+// 2.20 ms; rows staged per thread with 33 LDG + 33 STS and two horizontal passes per output row 1.82 ms (bound by just
+// that: l1tex 78 %, LSU pipe 56 %, ncu; 4-byte cp.async instead of LDG + STS: no better); TMA rows 1.68 ms; + one
+// horizontal pass per staged row (40 registers instead of 60) 1.46 ms.
+constexpr int kResizeTmaW = 192;
+struct __align__(16) ResizeWarpSmem {
+  uint8_t rows[kResizeSrcRows][kResizeTmaW];
+  uint64_t bar;
+  uint64_t pad;
+};
 
 __global__ void __launch_bounds__(256)
-k_resize_staged(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ src0, size_t src_stride,
-                uint8_t* __restrict__ pyr, const int2* __restrict__ taps, int level) {
-  extern __shared__ uint32_t s_rows[];   // [kResizeSrcRows][3][256 threads]
+k_resize_tma(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ src0, size_t src_stride,
+             uint8_t* __restrict__ pyr, const int2* __restrict__ taps, int level) {
+  __shared__ ResizeWarpSmem s_rz[8];
   const LevelGeom& d = g.lv[level];
   const LevelGeom& s = g.lv[level - 1];
-  const int img = blockIdx.z;
-  const int tid = threadIdx.y * 32 + threadIdx.x;
-  const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
-  const int y_first = (blockIdx.y * 8 + threadIdx.y) * kResizeRows;
-  if (y_first >= d.h || x4 >= d.pitch) return;
-  const uint8_t* src = src0 + (size_t)img * src_stride;      // source level of this image (level 0 may be the caller's buffer)
+  const int img = blockIdx.z, lane = threadIdx.x, warp = threadIdx.y;
+  const int x4 = (blockIdx.x * 32 + lane) * 4;
+  const int y_first = (blockIdx.y * 8 + warp) * kResizeRows;
+  if (y_first >= d.h) return;                                  // the whole warp
+  ResizeWarpSmem& S = s_rz[warp];
+  const uint8_t* src = src0 + (size_t)img * src_stride;
   uint8_t* dst = pyr + (size_t)img * g.pyr_stride + d.off;
   const int y_end = min(y_first + kResizeRows, d.h);
   int2 ty = __ldg(&taps[d.ytab + y_first]);
   const int ra0 = ty.x;
   const int n_src = __ldg(&taps[d.ytab + y_end - 1]).x + 2 - ra0;      // <= kResizeSrcRows (host-checked)
-  const int xbase = __ldg(&taps[d.xtab + min(x4, d.w - 1)]).x;
-  const int abase = xbase & ~3, sh8 = (xbase & 3) * 8;
   const int sp = s.pitch, last_row = s.h - 1;
-  {
-    uint32_t rr[kResizeSrcRows][3];
-#pragma unroll
-    for (int i = 0; i < kResizeSrcRows; ++i) {
-      const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (size_t)min(ra0 + min(i, n_src - 1), last_row) * sp + abase);
-#pragma unroll
-      for (int k = 0; k < 3; ++k) rr[i][k] = __ldg(p + k);
-    }
-#pragma unroll
-    for (int i = 0; i < kResizeSrcRows; ++i)
-#pragma unroll
-      for (int k = 0; k < 3; ++k) s_rows[(i * 3 + k) * 256 + tid] = rr[i][k];
+  const int astart = __ldg(&taps[d.xtab + min(blockIdx.x * 128, d.w - 1)]).x & ~15;   // lane 0's first tap, aligned down
+  const uint32_t row_bytes = (uint32_t)min(kResizeTmaW, sp - astart);
+  if (lane == 0) {
+    mbar_init(&S.bar, 1);
+    mbar_arrive_expect_tx(&S.bar, row_bytes * (uint32_t)n_src);
   }
-  // horizontal taps of the four columns (while the rows are in flight)
+  __syncwarp();
+  RPE_ASSERT(n_src <= kResizeSrcRows && row_bytes % 16 == 0 && row_bytes > 0);
+  if (lane < n_src) bulk_copy_g2s(S.rows[lane], src + (size_t)min(ra0 + lane, last_row) * sp + astart, row_bytes, &S.bar);
+  // horizontal / vertical taps while the rows are in flight
+  const int xbase = __ldg(&taps[d.xtab + min(x4, d.w - 1)]).x;
+  const int aoff = (xbase & ~3) - astart, sh8 = (xbase & 3) * 8;
   uint32_t sel[4], wgt[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -191,35 +193,42 @@ k_resize_staged(const __grid_constant__ OrbGeom g, const uint8_t* __restrict__ s
     sel[k] = r | ((r + 1u) << 4) | 0x8800u;
     wgt[k] = (256u - (uint32_t)t.y) | ((uint32_t)t.y << 16);
   }
-  auto hpass = [&](int i, uint32_t* h) {                 // staged row i of this thread
-    const uint32_t* r = s_rows + i * 3 * 256 + tid;
-    const uint32_t r0 = r[0], r1 = r[256], r2 = r[512];
+  mbar_wait(&S.bar, 0);
+  if (x4 >= d.pitch) return;
+  // (bytes past row_bytes - at the right edge of the source level - are only ever multiplied into columns >= d.w)
+  RPE_ASSERT(aoff >= 0 && aoff + 12 <= kResizeTmaW);
+  auto hpass = [&](int i, uint32_t* h) {
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(S.rows[i] + aoff);
+    const uint32_t r0 = r[0], r1 = r[1], r2 = r[2];
     const uint32_t lo = __funnelshift_r(r0, r1, sh8), hi = __funnelshift_r(r1, r2, sh8);
 #pragma unroll
     for (int k = 0; k < 4; ++k) h[k] = __dp2a_lo(wgt[k], __byte_perm(lo, hi, sel[k]), 0u);
   };
-  // straight-line: the row index into the staged rows is free to be dynamic, so every output row takes its own two
-  // source rows (no walk, no register moves, no data-dependent loop); the vertical taps are loaded up front
-  int2 tys[kResizeRows];
-#pragma unroll
-  for (int j = 0; j < kResizeRows; ++j) tys[j] = __ldg(&taps[d.ytab + min(y_first + j, d.h - 1)]);
+  // Every staged row takes ONE horizontal pass (not two per output row: 16 for <= 11 rows).  The walk is
+  // static over the staged rows; the first tap row of the output rows is strictly increasing (host-checked:
+  // resize_rows_strict), so staged row i closes at most one output row, the one whose first tap is i - 1.  All
+  // decisions are warp-uniform.
   uint8_t* out = dst + (size_t)y_first * d.pitch + x4;
+  uint32_t hrow[2][4];
+  hpass(0, hrow[0]);
+  int y = y_first;                                           // next output row
 #pragma unroll
-  for (int j = 0; j < kResizeRows; ++j) {
-    if (y_first + j < y_end) {
-      uint32_t hA[4], hB[4];
-      const int rel = tys[j].x - ra0;
-      RPE_ASSERT(rel >= 0 && rel + 1 < kResizeSrcRows && n_src <= kResizeSrcRows);
-      hpass(rel, hA);
-      hpass(rel + 1, hB);
-      const uint32_t cy1 = (uint32_t)tys[j].y, cy0 = 256u - cy1;
-      uint32_t v[4];
+  for (int i = 1; i < kResizeSrcRows; ++i) {
+    if (i < n_src) {
+      hpass(i, hrow[i & 1]);
+      if (y < y_end && ty.x - ra0 == i - 1) {
+        const uint32_t cy1 = (uint32_t)ty.y, cy0 = 256u - cy1;
+        uint32_t v[4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) v[k] = cy0 * hA[k] + (cy1 * hB[k] + 32768u);
-      *reinterpret_cast<uint32_t*>(out + (size_t)j * d.pitch) =
-          __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+        for (int k = 0; k < 4; ++k) v[k] = cy0 * hrow[(i - 1) & 1][k] + (cy1 * hrow[i & 1][k] + 32768u);
+        *reinterpret_cast<uint32_t*>(out) = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+        out += d.pitch;
+        ++y;
+        ty = __ldg(&taps[d.ytab + min(y, d.h - 1)]);
+      }
     }
   }
+  RPE_ASSERT(y == y_end);
 }
 
 static PyrView pyr_view(const OrbBuffers& b) { return PyrView{b.pyr, b.lvl0, b.lvl0_stride}; }
@@ -231,10 +240,9 @@ void launch_pyramid(const OrbGeom& g, const OrbBuffers& b, int n_img, cudaStream
     const bool ext = l == 1 && b.lvl0 != nullptr;
     const uint8_t* src0 = ext ? b.lvl0 : b.pyr + g.lv[l - 1].off;
     const size_t sst = ext ? b.lvl0_stride : g.pyr_stride;
-    // B200, 256 pairs: k_resize_strip on every level 2.20 ms; k_resize_staged on every level 1.81 ms
-    if (g.resize_strip_ok && g.resize_span <= kResizeSrcRows) {
+    if (g.resize_strip_ok && g.resize_span <= kResizeSrcRows && g.resize_xspan <= kResizeTmaW && g.resize_rows_strict) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
-      k_resize_staged<<<grid, block, kResizeStageBytes, s>>>(g, src0, sst, b.pyr, b.taps, l);
+      k_resize_tma<<<grid, block, 0, s>>>(g, src0, sst, b.pyr, b.taps, l);
     } else if (g.resize_strip_ok) {
       dim3 grid((d.pitch / 4 + 31) / 32, (d.h + 8 * kResizeRows - 1) / (8 * kResizeRows), n_img), block(32, 8);
       k_resize_strip<<<grid, block, 0, s>>>(g, src0, sst, b.pyr, b.taps, l);

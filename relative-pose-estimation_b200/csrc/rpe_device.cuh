@@ -53,7 +53,9 @@ struct OrbGeom {
   int cand_stride;
   int kp_stride;
   int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)
-  int resize_span;         // most source rows any 8-row output strip needs (k_resize_staged stages them all)
+  int resize_span;         // most source rows any 8-row output strip needs (k_resize_tma stages them all)
+  int resize_xspan;        // most source bytes (from the aligned start) any 128-column output group taps (k_resize_tma stages them)
+  int resize_rows_strict;  // the first vertical tap row is strictly increasing over the output rows of every level (k_resize_tma's walk)
   int resize_strip_ok;     // every aligned group of 4 output columns taps <= 8 consecutive source bytes
   size_t pyr_stride;
   LevelGeom lv[RPE_MAX_LEVELS];
@@ -72,7 +74,10 @@ constexpr int kBlurRows = RPE_BLUR_ROWS;   // blur work item = 128 columns x two
 // columns of one row, and the 32 rotated pattern points of one gather instruction fall into ~6 lines instead of ~11
 // (tools/gather_bench.cu: 0.197 -> 0.138 ms for 320 000 keypoints; surface / texture reads of a block-linear array:
 // 0.277 ms).  Level size is unchanged: ceil(w / 16) * 16 * h = pitch * h.
-constexpr int kBlurStripLog = 4, kBlurStripW = 1 << kBlurStripLog;
+#ifndef RPE_BLUR_STRIP_LOG
+#define RPE_BLUR_STRIP_LOG 4
+#endif
+constexpr int kBlurStripLog = RPE_BLUR_STRIP_LOG, kBlurStripW = 1 << kBlurStripLog;
 __host__ __device__ inline size_t blur_strip_offset(int x, int y, int h) {
   return (size_t)(x >> kBlurStripLog) * ((size_t)h * kBlurStripW) + (size_t)y * kBlurStripW + (size_t)(x & (kBlurStripW - 1));
 }

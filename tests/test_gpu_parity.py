@@ -409,3 +409,33 @@ def test_orb_ragged_sizes_bit_exact(engine, size):
     assert all(v == 0 for k, v in d.items() if k not in ("n_gpu", "n_ref")), (size, d)
     if min(w, h) < 63:
         assert d["n_gpu"] == 0
+
+
+@pytest.mark.parametrize("scale,nlevels", [(1.2, 8), (1.3, 6), (1.5, 5), (2.0, 4)])
+def test_orb_other_scale_factors_bit_exact(scale, nlevels):
+    """The reference hard-codes scaleFactor 1.1 (pose_estimator.py:85-91), which takes the TMA-staged resize kernel;
+    rpe_config.scale_factor is a parameter, though, and larger factors take the other two resize kernels
+    (k_resize_strip up to 4/3, the generic k_resize beyond).  Same bar: pyramid levels and ORB output bit-exact
+    against the oracle, and the oracle's keypoint count against live cv2."""
+    import rpe_b200
+    import rpe_b200._lib as L
+    img = load_gray("salah_000000.png")
+    h, w = img.shape
+    eng = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=w, max_height=h, max_pairs=1, scale_factor=scale, nlevels=nlevels))
+    try:
+        p = oo.OrbParams(scale_factor=scale, nlevels=nlevels)
+        ref, levels, pyr, blurred = oo.orb_detect_and_compute(img, p, return_pyramid=True)
+        kps, _ = cv2.ORB_create(nfeatures=4000, scaleFactor=scale, nlevels=nlevels, fastThreshold=15,
+                                scoreType=cv2.ORB_HARRIS_SCORE).detectAndCompute(img, None)
+        assert len(ref) == len(kps)
+        eng.estimate_batch([img], [img], default_K(w, h))
+        for l, lv in enumerate(levels):
+            got = eng.get_stage(0, 0, L.STAGE_PYRAMID_LEVEL, l).reshape(lv.h, lv.w)
+            assert np.array_equal(got, pyr[l]), f"scale {scale}: pyramid level {l}: {(got != pyr[l]).sum()} px differ"
+            got = eng.get_stage(0, 0, L.STAGE_BLURRED_LEVEL, l).reshape(lv.h, lv.w)
+            assert np.array_equal(got, blurred[l]), f"scale {scale}: blur level {l}"
+        d = _orb_diff(eng.orb_detect(img), ref)
+        assert d["n_gpu"] == d["n_ref"], (scale, d)
+        assert all(v == 0 for k, v in d.items() if k not in ("n_gpu", "n_ref")), (scale, d)
+    finally:
+        eng.close()
