@@ -300,7 +300,7 @@ void launch_ransac(const MatchBuffers& mb, const GeomBuffers& gb, int mcap, int 
 }
 
 // ------------------------------------------------------------------ K12/K13: recoverPose + Euler
-constexpr int kPoseThreads = 128;
+constexpr int kPoseThreads = 512;        // 128 points x 4 candidates per pass (launch bound caps the registers at 128)
 
 __global__ void __launch_bounds__(kPoseThreads)
 k_pose(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npts, const double* __restrict__ E_in,
@@ -334,25 +334,28 @@ k_pose(const int32_t* __restrict__ m_n, int mcap, const double* __restrict__ npt
   __syncthreads();
   const double4* P = reinterpret_cast<const double4*>(npts) + (size_t)pair * mcap;
   uint8_t* pm = pmask + (size_t)pair * mcap;
-  const double tp[3] = {st[0], st[1], st[2]}, tn[3] = {-st[0], -st[1], -st[2]};
-  int local[4] = {0, 0, 0, 0};
-  for (int i = tid; i < M; i += kPoseThreads) {
-    const double4 p = P[i];
-    uint8_t bits = 0;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const bool ok = triangulate_cheirality(sR[c & 1], (c & 2) ? tn : tp, p.x, p.y, p.z, p.w, 50.0);
-      bits |= (uint8_t)ok << c;
-      local[c] += ok;
+  // one thread per (point, candidate): the four candidates of a point sit in four adjacent lanes (a 4 x 4 Jacobi SVD in
+  // FP64 per thread is a long dependent chain; with all four candidates of four points in one thread, as first written,
+  // recoverPose was a quarter of the latency of a single-pair call)
+  const int c = tid & 3;
+  const double tc[3] = {(c & 2) ? -st[0] : st[0], (c & 2) ? -st[1] : st[1], (c & 2) ? -st[2] : st[2]};
+  int local = 0;
+  for (int i0 = 0; i0 < M; i0 += kPoseThreads / 4) {        // warp-uniform trip count
+    const int i = i0 + (tid >> 2);
+    bool ok = false;
+    if (i < M) {
+      const double4 p = P[i];
+      ok = triangulate_cheirality(sR[c & 1], tc, p.x, p.y, p.z, p.w, 50.0);
     }
-    pm[i] = bits;
+    local += ok;
+    uint32_t bits = (uint32_t)ok << c;
+    bits |= __shfl_xor_sync(0xffffffffu, bits, 1);
+    bits |= __shfl_xor_sync(0xffffffffu, bits, 2);
+    if (c == 0 && i < M) pm[i] = (uint8_t)bits;
   }
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    int v = local[c];
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((tid & 31) == 0) atomicAdd(&s_good[c], v);
-  }
+  // per-candidate counts: lanes with equal (lane & 3) hold the same candidate
+  for (int o = 16; o >= 4; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((tid & 31) < 4) atomicAdd(&s_good[c], local);
   __syncthreads();
   if (tid == 0) {
     const int g1 = s_good[0], g2 = s_good[1], g3 = s_good[2], g4 = s_good[3];
