@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
@@ -34,6 +35,19 @@ static int fail(int code, const char* msg) {
   g_last_error = msg;
   return code;
 }
+int rpe::raise_dynamic_smem_limit(const void* func, int bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<int, const void*>, int> limit;   // (device, function) -> bytes set so far
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 1;
+  std::lock_guard<std::mutex> lock(mu);
+  int& cur = limit[std::make_pair(dev, func)];
+  if (bytes <= cur) return 0;
+  if (cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return 1;
+  cur = bytes;
+  return 0;
+}
+
 // for the entry points that live beside their kernels (kernels_eval.cu): same thread-local message as above
 int rpe::report_error(int code, const char* msg) { return fail(code, msg); }
 
@@ -221,7 +235,8 @@ static void build_geometry(const rpe_config& c, int W, int H, Geometry& G) {
   g.total_bitems = (int)G.btab.size();
   g.cand_stride = cand_off;
   g.kp_stride = kp_off;
-  g.sort_cap = pow2_ge(max_kp_cap);
+  g.sort_cap = align_up(max_kp_cap, 8);   // (no power of two needed: k_select orders by rows, not by a bitonic network)
+  g.sel_row_cap = H;
   g.pyr_stride = off;
 }
 
@@ -252,6 +267,7 @@ static int get_geometry(rpe_handle* h, int W, int H, const Geometry** out) {
     G.g.cand_stride = h->cand_stride;
     G.g.kp_stride = h->kp_stride;
     G.g.sort_cap = h->sort_cap_orb;
+    G.g.sel_row_cap = h->cfg.max_height;
     RPE_CK(cudaMalloc((void**)&G.d_taps, std::max<size_t>(G.taps.size(), 1) * sizeof(int2)));
     RPE_CK(cudaMemcpy(G.d_taps, G.taps.data(), G.taps.size() * sizeof(int2), cudaMemcpyHostToDevice));
     RPE_CK(cudaMalloc((void**)&G.d_ftab, std::max<size_t>(G.ftab.size(), 1) * sizeof(uint32_t)));
@@ -308,7 +324,8 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out) {
   if (h->kp_stride >= (1 << 20)) { delete h; return fail(RPE_ERR_INVALID, "nfeatures too large (index packs in 20 bits)"); }
   h->mcap = cfg->max_matches > 0 ? std::min(cfg->max_matches, h->kp_stride) : h->kp_stride;
   h->sort_cap_match = pow2_ge(h->mcap);
-  if ((size_t)h->sort_cap_match * 4 > 200 * 1024 || (size_t)h->sort_cap_orb * 8 > 200 * 1024) {
+  if ((size_t)h->sort_cap_match * 4 > 200 * 1024 || h->sort_cap_orb > 65536 ||
+      select_smem_bytes(h->sort_cap_orb, cfg->max_height) > 200 * 1024) {
     delete h;
     return fail(RPE_ERR_INVALID, "max_matches / nfeatures exceed the shared-memory sort capacity");
   }
@@ -375,7 +392,7 @@ int rpe_create(const rpe_config* cfg, int device, rpe_handle** out) {
     for (int i = 0; i <= RPE_T_COUNT; ++i)
       if (cudaEventCreate(&h->ev[i]) != cudaSuccess) rc = fail(RPE_ERR_CUDA, "cudaEventCreate failed");
   }
-  if (rc == RPE_OK && (setup_orb_attributes(h->sort_cap_orb) || setup_match_attributes(h->sort_cap_match) || setup_geom_attributes()))
+  if (rc == RPE_OK && (setup_orb_attributes((int)select_smem_bytes(h->sort_cap_orb, h->cfg.max_height)) || setup_match_attributes(h->sort_cap_match) || setup_geom_attributes()))
     rc = fail(RPE_ERR_CUDA, "cudaFuncSetAttribute failed");
   if (rc != RPE_OK) {
     std::string keep = g_last_error;

@@ -340,8 +340,7 @@ void launch_build_matches(const OrbBuffers& ob, const MatchBuffers& mb, int kp_s
 }
 
 int setup_match_attributes(int sort_cap_match) {
-  return (int)cudaFuncSetAttribute(k_build_matches, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   sort_cap_match * 4);
+  return raise_dynamic_smem_limit((const void*)k_build_matches, sort_cap_match * 4);
 }
 
 }  // namespace rpe

@@ -52,7 +52,8 @@ struct OrbGeom {
   int total_bitems;        // blur work items (one warp each): 128 columns x two kBlurRows-row strips
   int cand_stride;
   int kp_stride;
-  int sort_cap;            // power of two >= max kp_cap (select kernel sort buffer)
+  int sort_cap;            // >= max kp_cap (select kernel: kept-keypoint buffer)
+  int sel_row_cap;         // rows of the tallest level (select kernel: per-row tables of the (y, x) ordering)
   int resize_span;         // most source rows any 8-row output strip needs (k_resize_tma stages them all)
   int resize_xspan;        // most source bytes (from the aligned start) any 128-column output group taps (k_resize_tma stages them)
   int resize_rows_strict;  // the first vertical tap row is strictly increasing over the output rows of every level (k_resize_tma's walk)
@@ -194,7 +195,12 @@ void launch_evaluate(int n, const double* est_R, const double* est_t, const doub
                      const double* gt_pos, int convention, double* errors, double* summary, cudaStream_t s);
 void launch_eval_summary(int n, const double* errors, double* summary, cudaStream_t s);
 int report_error(int code, const char* msg);   // sets rpe_last_error() of the calling thread, returns code (engine.cu)
-int setup_orb_attributes(int sort_cap);
+size_t select_smem_bytes(int sort_cap, int row_cap);   // dynamic shared memory of k_select
+int setup_orb_attributes(int select_smem);
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of the FUNCTION (per device), not of a handle: a second handle
+// with a smaller configuration must not lower it under the first.  Raises the limit of `func` on the current device to
+// at least `bytes` (never lowers it); returns 0 on success.  (engine.cu)
+int raise_dynamic_smem_limit(const void* func, int bytes);
 int setup_match_attributes(int sort_cap);
 int setup_geom_attributes();
 constexpr int kRansacSuperRoundCap = 8 * 64;   // kMaxChunks * kChunk (kernels_geom.cu)

@@ -284,3 +284,25 @@ def test_device_resident_frames_are_used_in_place_or_copied_with_identical_resul
         assert torch.equal(dev, keep)
     finally:
         eng.close()
+
+
+def test_a_second_smaller_handle_does_not_break_the_first():
+    """The dynamic shared-memory limit of a kernel belongs to the function, not to a handle: creating a handle with a
+    smaller configuration (fewer features, lower images, fewer matches) must not lower the limit under a larger handle
+    created before it."""
+    import rpe_b200
+    big_img = load_gray("salah_000000.png")                 # 1920 x 1080
+    big = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=1920, max_height=1080, max_pairs=1, nfeatures=8000, max_matches=None))
+    try:
+        first = big.orb_detect(big_img)
+        small = rpe_b200.Engine(rpe_b200.EngineConfig(max_width=320, max_height=240, max_pairs=1, nfeatures=500, max_matches=100))
+        try:
+            small.orb_detect(np.ascontiguousarray(big_img[:240, :320]))
+            again = big.orb_detect(big_img)
+            out = big.estimate_batch([big_img], [big_img], default_K(1920, 1080))
+        finally:
+            small.close()
+        assert np.array_equal(first["desc"], again["desc"]) and len(first["x"]) > 4000
+        assert out["status"][0] == 0 and out["info"][0, 0] > 4000
+    finally:
+        big.close()
