@@ -66,19 +66,15 @@ constexpr int kTileW = 64;
 constexpr int kTileH = 32;
 constexpr int kFastTW = 120;
 constexpr int kFastTH = 14;     // tile rows; + 2 = 16 score rows = two bands of 8 (k_fast: one warp per tile)
-#ifndef RPE_BLUR_ROWS
-#define RPE_BLUR_ROWS 35
-#endif
-constexpr int kBlurRows = RPE_BLUR_ROWS;   // blur work item = 128 columns x two strips of kBlurRows rows (one warp)
+// (strip height, 512 images 1280x720: 28 / 32 / 35 / 42 / 49 rows 2.08 / 2.20 / 2.06 / 2.30 / 2.17 ms: whole groups of 7 rows
+// waste nothing, taller strips cost occupancy)
+constexpr int kBlurRows = 35;   // blur work item = 128 columns x two strips of kBlurRows rows (one warp)
 // Layout of a BLURRED level (k_blur writes it, k_describe gathers from it): vertical strips of kBlurStripW columns,
 // each strip all h rows of 16 bytes, strip after strip.  A 128-byte line is then 8 rows x 16 columns instead of 128
 // columns of one row, and the 32 rotated pattern points of one gather instruction fall into ~6 lines instead of ~11
 // (tools/gather_bench.cu: 0.197 -> 0.138 ms for 320 000 keypoints; surface / texture reads of a block-linear array:
 // 0.277 ms).  Level size is unchanged: ceil(w / 16) * 16 * h = pitch * h.
-#ifndef RPE_BLUR_STRIP_LOG
-#define RPE_BLUR_STRIP_LOG 4
-#endif
-constexpr int kBlurStripLog = RPE_BLUR_STRIP_LOG, kBlurStripW = 1 << kBlurStripLog;
+constexpr int kBlurStripLog = 4, kBlurStripW = 1 << kBlurStripLog;   // (8-column strips: k_describe the same, k_blur 6 % slower)
 __host__ __device__ inline size_t blur_strip_offset(int x, int y, int h) {
   return (size_t)(x >> kBlurStripLog) * ((size_t)h * kBlurStripW) + (size_t)y * kBlurStripW + (size_t)(x & (kBlurStripW - 1));
 }
