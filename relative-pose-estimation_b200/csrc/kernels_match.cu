@@ -19,8 +19,10 @@
 namespace rpe {
 
 constexpr int kMatchThreads = 128;
-constexpr int kQPT = 2;                       // queries per thread
-constexpr int kQPB = kMatchThreads * kQPT;    // queries per block
+// (queries per thread, ratio mode, this kernel form, B200, 256 pairs x 5000 x 5000: 2 / 3 / 4 -> 6.73 / 7.03 / 6.91 ms at
+// 56 / 72 / 80 registers: fewer shared-memory reads per distance do not pay for the lost occupancy)
+constexpr int kQptTop2 = 2;                   // queries per thread, ratio mode
+constexpr int kQptCross = 2;                  // queries per thread, cross-check mode (the column-minimum code is written for two)
 constexpr int kTrainTile = 128;               // train descriptors per shared-memory tile
 
 __device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) {
@@ -34,12 +36,14 @@ __device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) {
 // REDUX.MIN per warp and train descriptor - kept by lane t % 32, folded into a shared-memory minimum per tile slot
 // (one atomicMin per lane and 32 train descriptors) and flushed to bwd1 with one global atomicMin per CTA and train
 // descriptor.  Keys carry the index in the low bits, so ties go to the lowest index in both directions, as cv2's.
-template <bool kTop2>
+template <bool kTop2, int kQPT>
 __global__ void __launch_bounds__(kMatchThreads)
 k_hamming(const uint8_t* __restrict__ desc, const int32_t* __restrict__ kp_n, int kp_stride, int pstep, uint32_t m20,
           int nsplit, uint32_t* __restrict__ fwd1, uint32_t* __restrict__ fwd2, uint32_t* __restrict__ bwd1) {
   __shared__ uint4 s_train[kTrainTile * 2];
   __shared__ uint32_t s_col[kTrainTile];
+  constexpr int kQPB = kMatchThreads * kQPT;
+  static_assert(kTop2 || kQPT == 2, "cross-check path handles two queries per thread");
   const int pair = blockIdx.y;
   // image slots of the two views: pstep = 2 (pair batch: 2p, 2p+1) or 1 (consecutive frames: p, p+1)
   const int qi = pstep * pair, ti = pstep * pair + 1;
@@ -186,16 +190,17 @@ static int pick_nsplit(int nfeatures) { return max(1, min(32, (nfeatures + 5 * k
 
 void launch_match(const OrbBuffers& ob, const MatchBuffers& mb, int kp_stride, int nfeatures, int n_pairs, int pstep,
                   int mode, cudaStream_t s, int* launches) {
-  const int qblocks = (kp_stride + kQPB - 1) / kQPB;
   const bool top2 = mode == RPE_MATCH_RATIO;
+  const int qpb = kMatchThreads * (top2 ? kQptTop2 : kQptCross);
+  const int qblocks = (kp_stride + qpb - 1) / qpb;
   const int nsplit = pick_nsplit(min(nfeatures, kp_stride));
   const size_t bytes = (size_t)n_pairs * kp_stride * sizeof(uint32_t);
   if (nsplit > 1) cudaMemsetAsync(mb.fwd1, 0xff, bytes, s);
   if (top2 && nsplit > 1) cudaMemsetAsync(mb.fwd2, 0xff, bytes, s);
   if (!top2) cudaMemsetAsync(mb.bwd1, 0xff, bytes, s);       // column minima always arrive through atomicMin
   dim3 grid(qblocks * nsplit, n_pairs);
-  if (top2) k_hamming<true><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, nsplit, mb.fwd1, mb.fwd2, mb.bwd1);
-  else k_hamming<false><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, nsplit, mb.fwd1, mb.fwd2, mb.bwd1);
+  if (top2) k_hamming<true, kQptTop2><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, nsplit, mb.fwd1, mb.fwd2, mb.bwd1);
+  else k_hamming<false, kQptCross><<<grid, kMatchThreads, 0, s>>>(ob.desc, ob.kp_n, kp_stride, pstep, 1u << 20, nsplit, mb.fwd1, mb.fwd2, mb.bwd1);
   ++*launches;
 }
 
