@@ -935,7 +935,7 @@ static void build_ori_table(uint2* tab) {
 // 1.5 * 2^23 trick (the low mantissa bits of d + 1.5 * 2^23 are rint(d), ties to even, in two's complement: no F2I on
 // the XU pipe), so X = cx + ix is one integer add on the float's bits (cxm = cx - kRintBits).
 constexpr int kRintBits = 0x4B400000;             // bits of 12582912.0f = 1.5 * 2^23
-__device__ __forceinline__ uint32_t brief_test_strips(const uint8_t* base, int strip_bytes, int cxm, int cym, float a,
+__device__ __forceinline__ uint32_t brief_test_strips(const uint8_t* base, int strip_skip, int cxm, int cym, float a,
                                                       float b, uint32_t t) {
   const float xa = (float)(int8_t)(t & 0xff), ya = (float)(int8_t)((t >> 8) & 0xff);
   const float xb = (float)(int8_t)((t >> 16) & 0xff), yb = (float)(int8_t)(t >> 24);
@@ -943,8 +943,9 @@ __device__ __forceinline__ uint32_t brief_test_strips(const uint8_t* base, int s
   const int Ya = __float_as_int(f32_add(f32_add(f32_mul(xa, b), f32_mul(ya, a)), 12582912.0f)) + cym;
   const int Xb = __float_as_int(f32_add(f32_sub(f32_mul(xb, a), f32_mul(yb, b)), 12582912.0f)) + cxm;
   const int Yb = __float_as_int(f32_add(f32_add(f32_mul(xb, b), f32_mul(yb, a)), 12582912.0f)) + cym;
-  const int va = base[(Xa >> kBlurStripLog) * strip_bytes + Ya * kBlurStripW + (Xa & (kBlurStripW - 1))];
-  const int vb = base[(Xb >> kBlurStripLog) * strip_bytes + Yb * kBlurStripW + (Xb & (kBlurStripW - 1))];
+  // (X >> 4) * strip_bytes + (X & 15) = X + (X >> 4) * (strip_bytes - 16): strip_skip = strip_bytes - kBlurStripW
+  const int va = base[(Xa >> kBlurStripLog) * strip_skip + Xa + Ya * kBlurStripW];
+  const int vb = base[(Xb >> kBlurStripLog) * strip_skip + Xb + Yb * kBlurStripW];
   return (uint32_t)(va < vb);
 }
 
@@ -1077,11 +1078,11 @@ k_describe(const __grid_constant__ OrbGeom g, const PyrView pv, const uint8_t* _
     const uint8_t* base = blur + (size_t)img * g.pyr_stride + L.off;
     RPE_ASSERT(s_cx[k] >= 19 && s_cx[k] < L.w - 19 && s_cy[k] >= 19 && s_cy[k] < L.h - 19);   // pattern radius 18.4
     const float a = s_a[k], b = s_b[k];
-    const int strip_bytes = L.h * kBlurStripW;
+    const int strip_skip = (L.h - 1) * kBlurStripW;
     const int cxm = s_cx[k] - kRintBits, cym = s_cy[k] - kRintBits;
     uint32_t byte = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) byte |= brief_test_strips(base, strip_bytes, cxm, cym, a, b, pat[j]) << j;
+    for (int j = 0; j < 8; ++j) byte |= brief_test_strips(base, strip_skip, cxm, cym, a, b, pat[j]) << j;
     desc[((size_t)img * g.kp_stride + i0 + k) * 32 + lane] = (uint8_t)byte;
   }
 }
