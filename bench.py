@@ -417,11 +417,12 @@ def measure_pairs(ctx: Ctx, cfg, B, n_batches, steps, warmup, with_cpu, name):
     popc_lanes = rates.get("popc", 16.0)
     sm_hz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
     popc_peak = 148 * popc_lanes * sm_hz * 1e6
-    # the kernel issues 4.5 POPC per 256-bit distance (carry-save adders fold the 8 xor words into 5 / 4 words on
-    # alternate train descriptors), not 8: the pipe fraction counts ISSUED popcounts
-    popc_issued = 4.5 / 8.0 * (stages["match"].get("popc32_per_s") or 0.0)
+    # the kernel issues 4.25 POPC per 256-bit distance (carry-save adders fold the 8 xor words into 4 words, into 5 on
+    # one train descriptor in four), not 8: the pipe fraction counts ISSUED popcounts
+    POPC_PER_DISTANCE = 4.25
+    popc_issued = POPC_PER_DISTANCE / 8.0 * (stages["match"].get("popc32_per_s") or 0.0)
     xu = {"kernel": "match", "distances_per_s": (stages["match"].get("popc32_per_s") or 0.0) / 8.0,
-          "popc_issued_per_distance": 4.5, "achieved_popc32_per_s": popc_issued,
+          "popc_issued_per_distance": POPC_PER_DISTANCE, "achieved_popc32_per_s": popc_issued,
           "plain_form_equivalent_popc32_per_s": stages["match"].get("popc32_per_s"),
           "peak_popc32_per_s": popc_peak, "frac": popc_issued / popc_peak,
           "peak_source": ((f"tools/pipe_rates.cu on a B200 (profiles/r02_pipe_rates.json): {popc_lanes:.2f} POPC / clk / SM"
